@@ -1,0 +1,521 @@
+/* grl_oracle_agent.c -- oracle agent loop: Q policy, samplers, SARSA(lambda)/TD(lambda),
+ * enumerated traces, actor-critic, experiment episode loop.
+ * TEST INFRASTRUCTURE ONLY (see grl_oracle.h).  Citations: /root/reference/base. */
+#define _DEFAULT_SOURCE
+#define _XOPEN_SOURCE 600
+#include "grl_oracle.h"
+#include <math.h>
+#include <float.h>
+#include <stdlib.h>
+#include <string.h>
+
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
+
+#define INVALID_INDEX 0xFFFFFFFFu   /* stands for (size_t)-1, projection.h:73-76 */
+
+/* RNG stream ids for Philox mode (counter word 2) */
+enum { STREAM_ACT = 0, STREAM_START = 1, STREAM_TABLE = 2, STREAM_TEST_ACT = 3,
+       STREAM_ACTOR_TABLE = 4, STREAM_NOISE = 5 };
+
+typedef struct
+{
+  int      len;                       /* entries, [0] oldest .. [len-1] newest */
+  double   total_decay;
+  double   decay[ORC_TRACE_STORE];
+  uint32_t idx[ORC_TRACE_STORE][ORC_MAX_TILINGS];
+} orc_trace;
+
+struct orc_agent
+{
+  orc_config c;
+  uint64_t id;
+  int S;                              /* state dims */
+  double alpha, lambda, epsilon;      /* per-agent (sweep) */
+  double *table;                      /* Q (SARSA) or V (AC critic) */
+  double *actor;                      /* AC actor table */
+  /* glibc mode streams (utils.h:84-137) */
+  struct drand48_data randgen;        /* thread-local RandGen: table init + task start */
+  struct drand48_data sampler;        /* EpsilonGreedySampler::rand_ */
+  struct drand48_data test_sampler;   /* GreedySampler::rand_ of test_agent */
+  /* philox counters */
+  uint64_t act_counter, test_act_counter, episode_counter;
+  /* environment (modeled.cpp) */
+  double state[ORC_MAX_STATE];
+  double action;                      /* action to apply at the next env step */
+  /* TDAgent state (agents/td.cpp) */
+  double prev_obs[ORC_MAX_DIMS];
+  double prev_action;
+  uint32_t prev_idx[ORC_MAX_TILINGS]; /* projection of (prev_obs, prev_action) */
+  orc_trace trace;
+  /* experiment (online_learning.cpp) */
+  int in_episode, test;
+  uint64_t tt, ss, episodes, swept_total;
+  double total_reward, last_return, last_test_return;
+};
+
+/* ---- RNG ---------------------------------------------------------------- */
+
+static double u53(uint32_t hi, uint32_t lo)
+{
+  uint64_t x = ((uint64_t)hi << 32) | lo;
+  return (double)(x >> 11) * (1.0 / 9007199254740992.0);
+}
+
+static void philox_for(const orc_agent *a, int stream, uint64_t ctr, uint32_t out[4])
+{
+  orc_philox((uint32_t)ctr, (uint32_t)(ctr >> 32), (uint32_t)stream, (uint32_t)(a->c.seed >> 32),
+             (uint32_t)a->id, (uint32_t)a->c.seed ^ (uint32_t)(a->id >> 32), out);
+}
+
+void orc_glibc_seed(long seed) { srand48(seed); }
+
+/* ---- LinearRepresentation (linear.cpp) ---------------------------------- */
+
+/* linear.cpp:104-125 reset: params[ii] = rand->getUniform(init_min, init_max) */
+static void table_init(orc_agent *a, double *tbl, int stream)
+{
+  const orc_config *c = &a->c;
+  if (c->rng == ORC_RNG_GLIBC)
+  {
+    for (int32_t ii = 0; ii < c->memory; ++ii)
+    {
+      double r;
+      drand48_r(&a->randgen, &r);
+      tbl[ii] = c->init_min + r * (c->init_max - c->init_min);
+    }
+  }
+  else
+  {
+    for (int32_t ii = 0; ii < c->memory; ii += 2)
+    {
+      uint32_t w[4];
+      philox_for(a, stream, (uint64_t)(ii / 2), w);
+      tbl[ii] = c->init_min + u53(w[0], w[1]) * (c->init_max - c->init_min);
+      if (ii + 1 < c->memory)
+        tbl[ii + 1] = c->init_min + u53(w[2], w[3]) * (c->init_max - c->init_min);
+    }
+  }
+}
+
+/* linear.cpp:136-184 read (IndexProjection, weights empty): sequential sum from 0,
+ * divide by indices.size(), clamp to [omin, omax] */
+static double table_read(const double *tbl, const uint32_t *idx, int T, double omin, double omax)
+{
+  double result = 0;
+  for (int ii = 0; ii < T; ++ii)
+    result += tbl[idx[ii]];
+  result /= T;
+  return fmin(fmax(result, omin), omax);
+}
+
+/* linear.cpp:198-216 update (limit_ = 1): skips invalidated indices */
+static int table_update(double *tbl, const uint32_t *idx, int T, double delta, double omin, double omax)
+{
+  int n = 0;
+  for (int ii = 0; ii != T; ++ii)
+    if (idx[ii] != INVALID_INDEX)
+    {
+      tbl[idx[ii]] = fmin(fmax(tbl[idx[ii]] + delta, omin), omax);
+      ++n;
+    }
+  return n;
+}
+
+/* linear.cpp:186-196 write: value = read(p); delta = alpha*(target-value); update(p, delta) */
+static void table_write(double *tbl, const uint32_t *idx, int T, double target, double alpha,
+                        double omin, double omax)
+{
+  double value = table_read(tbl, idx, T, omin, omax);
+  double delta = alpha * (target - value);
+  table_update(tbl, idx, T, delta, omin, omax);
+}
+
+/* ---- EnumeratedTrace (trace.h:135-263) ---------------------------------- */
+
+static void trace_clear(orc_trace *t) { t->len = 0; t->total_decay = 1.; }
+
+static void trace_pop_front(orc_trace *t)
+{
+  memmove(&t->decay[0], &t->decay[1], (size_t)(t->len - 1) * sizeof(double));
+  memmove(&t->idx[0], &t->idx[1], (size_t)(t->len - 1) * sizeof(t->idx[0]));
+  t->len--;
+}
+
+/* projection.h:93-104 ssub (weights empty) */
+static void ssub(uint32_t *lhs, const uint32_t *rhs, int T)
+{
+  for (int ii = 0; ii < T; ++ii)
+    for (int jj = 0; jj < T; ++jj)
+      if (lhs[ii] == rhs[jj])
+        lhs[ii] = INVALID_INDEX;
+}
+
+/* trace.h:215-234 (replacing) / 244-261 (accumulating) */
+static void trace_add(orc_trace *t, int kind, const uint32_t *idx, int T, double decay)
+{
+  const double dc = kind == ORC_TRACE_REPLACING ? 0.01 : 0.0001;
+  if (decay < dc)
+    trace_clear(t);
+  if (kind == ORC_TRACE_REPLACING)
+    for (int ii = 0; ii < t->len; ++ii)
+      ssub(t->idx[ii], idx, T);
+  if (t->len == ORC_TRACE_STORE) abort();
+  memcpy(t->idx[t->len], idx, (size_t)T * sizeof(uint32_t));
+  t->decay[t->len] = decay;
+  t->len++;
+  t->total_decay *= decay;
+  while (t->total_decay < dc && t->len > 1)
+  {
+    t->total_decay /= t->decay[0];
+    trace_pop_front(t);
+  }
+}
+
+/* representation.h:79-83: newest -> oldest while weight > 0.001;
+ * update(projection, weight*delta*e); iterator weight_ *= decay of the entry just left
+ * (trace.h:168-176) */
+static void trace_sweep(const orc_trace *t, double *tbl, int T, double delta, double e,
+                        double omin, double omax, int *swept, int *entries)
+{
+  double weight = 1.;
+  int n = 0, m = 0;
+  for (int k = 0; k < t->len && weight > 0.001; ++k)
+  {
+    int pos = t->len - k - 1;
+    n += table_update(tbl, t->idx[pos], T, weight * delta * e, omin, omax);
+    weight *= t->decay[pos];
+    ++m;
+  }
+  if (swept) *swept = n;
+  if (entries) *entries = m;
+}
+
+/* ---- samplers (greedy.cpp) ---------------------------------------------- */
+
+typedef struct { double u; uint32_t r_explore, r_tie; int explored; } act_draws;
+
+/* greedy.cpp:47-61 */
+static void findmax(const double *values, int n, int *mai, int *man)
+{
+  *mai = 0; *man = 1;
+  for (int ii = 1; ii < n; ++ii)
+  {
+    if (values[ii] > values[*mai]) { *mai = ii; *man = 1; }
+    else if (values[ii] == values[*mai]) (*man)++;
+  }
+}
+
+/* tie walk, greedy.cpp:77-85 / 206-214 */
+static int tie_walk(const double *values, int mai, int r)
+{
+  int ii = mai;
+  for (int jj = r; jj >= 0; ++ii)
+    if (values[ii] == values[mai])
+      --jj;
+  return ii - 1;
+}
+
+/* raw 31-bit integer for getInteger(): lrand48() (utils.h:127-130) or a Philox word */
+static uint32_t draw_int(const orc_agent *a, uint32_t philox_word)
+{
+  if (a->c.rng == ORC_RNG_GLIBC) return (uint32_t)lrand48();
+  return philox_word >> 1;
+}
+
+/* EpsilonGreedySampler::sample (greedy.cpp:151-218, epsilon_.size()==1, decay_ = 1)
+ * when test == 0, GreedySampler::sample (greedy.cpp:63-86) when test != 0. */
+static int sample(orc_agent *a, const double *q, int test, act_draws *d)
+{
+  const int A = a->c.n_actions;
+  uint32_t w[4] = {0, 0, 0, 0};
+  int mai, man;
+  memset(d, 0, sizeof(*d));
+  findmax(q, A, &mai, &man);
+
+  if (a->c.rng == ORC_RNG_PHILOX)
+  {
+    if (test) philox_for(a, STREAM_TEST_ACT, a->test_act_counter++, w);
+    else      philox_for(a, STREAM_ACT, a->act_counter++, w);
+  }
+
+  if (!test)
+  {
+    double r;
+    if (a->c.rng == ORC_RNG_GLIBC) drand48_r(&a->sampler, &r);
+    else r = u53(w[0], w[1]);
+    d->u = r;
+    if (r < 1. * a->epsilon)
+    {
+      d->r_explore = draw_int(a, w[2]);
+      d->explored = 1;
+      return (int)(d->r_explore % (uint32_t)A);
+    }
+  }
+  if (man > 1)
+  {
+    d->r_tie = draw_int(a, w[3]);
+    return tie_walk(q, mai, (int)(d->r_tie % (uint32_t)man));
+  }
+  return mai;
+}
+
+/* ---- QPolicy (q.cpp:94-107,129-155) ------------------------------------- */
+
+static void q_values(const orc_agent *a, const double *obs, uint32_t *hash, uint32_t *idx, double *q)
+{
+  const orc_config *c = &a->c;
+  double in[ORC_MAX_DIMS];
+  for (int i = 0; i < c->obs_dims; ++i) in[i] = obs[i];
+  for (int aa = 0; aa < c->n_actions; ++aa)
+  {
+    in[c->obs_dims] = c->actions[aa];       /* extend(obs, variant) */
+    orc_project(c->resolution, c->wrapping, c->obs_dims + 1, c->tilings, c->memory, in,
+                hash ? hash + aa * c->tilings : NULL, idx + aa * c->tilings);
+    q[aa] = table_read(a->table, idx + aa * c->tilings, c->tilings, -DBL_MAX, DBL_MAX);
+  }
+}
+
+/* ---- task start (pendulum.cpp:97-103, cart_pole.cpp:152-160, cart_double_pole.cpp:250-262) */
+static double task_start(orc_agent *a, int test, double *state)
+{
+  const orc_config *c = &a->c;
+  double r;
+  if (c->rng == ORC_RNG_GLIBC) drand48_r(&a->randgen, &r);
+  else
+  {
+    uint32_t w[4];
+    philox_for(a, STREAM_START, a->episode_counter, w);
+    r = u53(w[0], w[1]);
+  }
+  a->episode_counter++;
+  for (int i = 0; i < a->S; ++i) state[i] = 0;
+  if (c->dynamics == ORC_DYN_PENDULUM)
+    state[0] = M_PI + c->randomization * (test == 0) * r * 2 * M_PI;
+  else if (c->dynamics == ORC_DYN_CART_POLE)
+    state[1] = M_PI + (int)c->randomization * ((r * 0.1) - 0.05);   /* int randomization_ (cart_pole.h:73) */
+  else
+    state[1] = (r * 0.01) - 0.005;
+  return r;
+}
+
+/* ---- SARSAPredictor::criticize (sarsa.cpp:98-124), tau = 1 --------------- */
+static void sarsa_update(orc_agent *a, double reward, const uint32_t *next_idx /* NULL if absorbing */,
+                         orc_record *rec)
+{
+  const orc_config *c = &a->c;
+  const int T = c->tilings;
+  double target = reward;
+  if (next_idx)
+    target += c->gamma * table_read(a->table, next_idx, T, -DBL_MAX, DBL_MAX);  /* pow(gamma,1) */
+  double qp = table_read(a->table, a->prev_idx, T, -DBL_MAX, DBL_MAX);
+  double delta = target - qp;
+  int swept = 0, entries = 0;
+
+  table_write(a->table, a->prev_idx, T, target, a->alpha, -DBL_MAX, DBL_MAX);
+  if (c->trace != ORC_TRACE_NONE)
+  {
+    double e = c->gamma * a->lambda;                                        /* pow(gamma*lambda,1) */
+    trace_sweep(&a->trace, a->table, T, a->alpha * delta, e, -DBL_MAX, DBL_MAX, &swept, &entries);
+    trace_add(&a->trace, c->trace, a->prev_idx, T, e);
+  }
+  a->swept_total += (uint64_t)swept;
+  if (rec)
+  {
+    rec->q_prev = qp; rec->target = target; rec->delta = delta;
+    rec->swept = swept; rec->swept_entries = entries;
+  }
+}
+
+static void dump_trace(const orc_agent *a, orc_record *rec)
+{
+  const int T = a->c.tilings;
+  int n = a->trace.len < ORC_MAX_TRACE ? a->trace.len : ORC_MAX_TRACE;
+  rec->trace_len = a->trace.len;
+  for (int k = 0; k < n; ++k)
+  {
+    int pos = a->trace.len - k - 1;
+    rec->trace_decay[k] = a->trace.decay[pos];
+    memcpy(&rec->trace_index[k * ORC_MAX_TILINGS], a->trace.idx[pos], (size_t)T * sizeof(uint32_t));
+  }
+}
+
+/* ---- construction -------------------------------------------------------- */
+
+orc_agent *orc_create(const orc_config *c, uint64_t agent_id)
+{
+  orc_agent *a = (orc_agent *)calloc(1, sizeof(orc_agent));
+  if (!a) return NULL;
+  a->c = *c;
+  a->id = agent_id;
+  a->S = orc_state_dims(c->dynamics);
+  a->alpha = c->alpha; a->lambda = c->lambda; a->epsilon = c->epsilon;
+  a->table = (double *)malloc((size_t)c->memory * sizeof(double));
+  if (c->algo == ORC_ALGO_AC)
+    a->actor = (double *)malloc((size_t)c->memory * sizeof(double));
+  trace_clear(&a->trace);
+
+  if (c->rng == ORC_RNG_GLIBC)
+  {
+    /* grld construction order for the shipped YAML (configurable.cpp:627-654 is
+     * depth-first in document order): representation::configure -> reset ->
+     * RandGen::instance() -> new Rand() -> srand48_r(lrand48()) (utils.h:90-93),
+     * then sampler/epsilon_greedy configure -> new Rand(), then the test agent's
+     * sampler/greedy -> new Rand(). */
+    srand48_r(lrand48(), &a->randgen);
+    table_init(a, a->table, STREAM_TABLE);
+    if (a->actor) table_init(a, a->actor, STREAM_ACTOR_TABLE);
+    srand48_r(lrand48(), &a->sampler);
+    srand48_r(lrand48(), &a->test_sampler);
+  }
+  else
+  {
+    table_init(a, a->table, STREAM_TABLE);
+    if (a->actor) table_init(a, a->actor, STREAM_ACTOR_TABLE);
+  }
+  return a;
+}
+
+void orc_destroy(orc_agent *a)
+{
+  if (!a) return;
+  free(a->table); free(a->actor); free(a);
+}
+
+void orc_set_hyper(orc_agent *a, double alpha, double lambda, double epsilon)
+{
+  a->alpha = alpha; a->lambda = lambda; a->epsilon = epsilon;
+}
+
+double *orc_table(orc_agent *a) { return a->table; }
+double *orc_actor_table(orc_agent *a) { return a->actor; }
+
+void orc_stats(const orc_agent *a, uint64_t *steps, uint64_t *episodes, uint64_t *swept,
+               double *last_return, double *last_test_return)
+{
+  if (steps) *steps = a->ss;
+  if (episodes) *episodes = a->episodes;
+  if (swept) *swept = a->swept_total;
+  if (last_return) *last_return = a->last_return;
+  if (last_test_return) *last_test_return = a->last_test_return;
+}
+
+void orc_get_state(const orc_agent *a, double *state, double *prev_obs, double *prev_action,
+                   int32_t *in_episode)
+{
+  if (state) memcpy(state, a->state, sizeof(double) * ORC_MAX_STATE);
+  if (prev_obs) memcpy(prev_obs, a->prev_obs, sizeof(double) * ORC_MAX_DIMS);
+  if (prev_action) *prev_action = a->prev_action;
+  if (in_episode) *in_episode = a->in_episode;
+}
+
+static int ac_step(orc_agent *a, orc_record *rec);
+
+/* ---- one agent-step (online_learning.cpp:154-222) ------------------------ */
+int orc_step(orc_agent *a, orc_record *rec)
+{
+  const orc_config *c = &a->c;
+  const int T = c->tilings, A = c->n_actions;
+  uint32_t hash[ORC_MAX_ACTIONS * ORC_MAX_TILINGS], idx[ORC_MAX_ACTIONS * ORC_MAX_TILINGS];
+  double q[ORC_MAX_ACTIONS], obs[ORC_MAX_DIMS], next[ORC_MAX_STATE], reward;
+  int32_t terminal;
+  act_draws d;
+
+  if (c->algo == ORC_ALGO_AC) return ac_step(a, rec);
+  if (rec) memset(rec, 0, sizeof(*rec));
+
+  if (!a->in_episode)
+  {
+    /* online_learning.cpp:160: test episode every (test_interval+1)-th trial */
+    a->test = (c->test_interval >= 0 &&
+               a->tt % (uint64_t)(c->test_interval + 1) == (uint64_t)c->test_interval);
+    double r = task_start(a, a->test, a->state);         /* modeled.cpp:132-158 */
+    orc_observe(c, a->state, obs, &terminal);
+    if (!a->test)
+      trace_clear(&a->trace);                             /* TDAgent::start -> predictor finalize */
+    q_values(a, obs, hash, idx, q);
+    int ai = sample(a, q, a->test, &d);
+    a->action = c->actions[ai];
+    memcpy(a->prev_obs, obs, sizeof(obs));
+    a->prev_action = a->action;
+    memcpy(a->prev_idx, idx + ai * T, (size_t)T * sizeof(uint32_t));
+    a->total_reward = 0;
+    a->in_episode = 1;
+    if (rec)
+    {
+      rec->started = 1; rec->start_draw = r;
+      memcpy(rec->start_state, a->state, sizeof(double) * (size_t)a->S);
+      rec->start_u = d.u; rec->start_r_explore = d.r_explore; rec->start_r_tie = d.r_tie;
+      rec->start_action_index = ai;
+      memcpy(rec->start_q, q, sizeof(double) * (size_t)A);
+    }
+  }
+
+  orc_env_step(c, a->state, a->action, next, obs, &reward, &terminal);
+  a->total_reward += reward;
+  if (rec)
+  {
+    memcpy(rec->state, a->state, sizeof(double) * (size_t)a->S);
+    rec->action = a->action;
+    memcpy(rec->next, next, sizeof(double) * (size_t)a->S);
+    memcpy(rec->obs, obs, sizeof(double) * (size_t)c->obs_dims);
+    rec->reward = reward; rec->terminal = terminal; rec->test = a->test;
+    rec->action_index = -1;
+  }
+
+  if (terminal == 2)
+  {
+    /* TDAgent::end (td.cpp:76-81): update without bootstrap; FixedAgent::end: nothing */
+    if (!a->test) sarsa_update(a, reward, NULL, rec);
+  }
+  else
+  {
+    /* TDAgent::step (td.cpp:63-74): act on the new observation, then update */
+    q_values(a, obs, hash, idx, q);
+    int ai = sample(a, q, a->test, &d);
+    double action = c->actions[ai];
+    if (rec)
+    {
+      rec->u = d.u; rec->r_explore = d.r_explore; rec->r_tie = d.r_tie; rec->explored = d.explored;
+      for (int aa = 0; aa < A; ++aa)
+      {
+        memcpy(&rec->hash[aa * ORC_MAX_TILINGS], hash + aa * T, (size_t)T * sizeof(uint32_t));
+        memcpy(&rec->index[aa * ORC_MAX_TILINGS], idx + aa * T, (size_t)T * sizeof(uint32_t));
+        rec->q[aa] = q[aa];
+      }
+      rec->action_index = ai;
+    }
+    if (!a->test) sarsa_update(a, reward, idx + ai * T, rec);
+    memcpy(a->prev_obs, obs, sizeof(obs));
+    a->prev_action = action;
+    memcpy(a->prev_idx, idx + ai * T, (size_t)T * sizeof(uint32_t));
+    a->action = action;
+  }
+  if (rec) dump_trace(a, rec);
+
+  memcpy(a->state, next, sizeof(double) * (size_t)a->S);
+  int counted = !a->test;
+  if (counted) a->ss++;
+  if (terminal)
+  {
+    a->in_episode = 0;
+    a->tt++;
+    a->episodes++;
+    if (a->test) a->last_test_return = a->total_reward;
+    else a->last_return = a->total_reward;
+    if (rec) { rec->episode_done = 1; rec->episode_return = a->total_reward; }
+  }
+  return counted;
+}
+
+uint64_t orc_run(orc_agent *a, uint64_t n_steps)
+{
+  uint64_t n = 0;
+  while (n < n_steps)
+    n += (uint64_t)orc_step(a, NULL);
+  return n;
+}
+
+/* actor-critic path (cfg 4) is added below */
+static int ac_step(orc_agent *a, orc_record *rec) { (void)a; (void)rec; abort(); return 0; }

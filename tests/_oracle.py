@@ -1,0 +1,153 @@
+"""ctypes binding of the CPU parity oracle (oracle/liborc.so).
+
+Test infrastructure only: imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  The product never imports it.
+"""
+import ctypes as C
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_DIR = os.path.join(os.path.dirname(HERE), "oracle")
+
+MAX_DIMS, MAX_ACTIONS, MAX_TILINGS, MAX_STATE, MAX_TRACE = 8, 8, 32, 7, 64
+INVALID = 0xFFFFFFFF
+
+DYN_PENDULUM, DYN_CART_POLE, DYN_CART_DOUBLE_POLE = 0, 1, 2
+TRACE_NONE, TRACE_REPLACING, TRACE_ACCUMULATING = 0, 1, 2
+ALGO_SARSA, ALGO_AC = 0, 1
+RNG_PHILOX, RNG_GLIBC = 0, 1
+
+
+class Config(C.Structure):
+    """Mirror of orc_config / grlcu_config (same field order in both headers)."""
+    _fields_ = [
+        ("dynamics", C.c_int32), ("integration_steps", C.c_int32),
+        ("control_step", C.c_double), ("timeout", C.c_double), ("randomization", C.c_double),
+        ("tilings", C.c_int32), ("memory", C.c_int32), ("obs_dims", C.c_int32), ("n_actions", C.c_int32),
+        ("resolution", C.c_double * MAX_DIMS), ("wrapping", C.c_double * MAX_DIMS),
+        ("actions", C.c_double * MAX_ACTIONS),
+        ("alpha", C.c_double), ("gamma", C.c_double), ("lambda_", C.c_double), ("epsilon", C.c_double),
+        ("trace", C.c_int32), ("test_interval", C.c_int32),
+        ("init_min", C.c_double), ("init_max", C.c_double),
+        ("seed", C.c_uint64), ("rng", C.c_int32), ("algo", C.c_int32),
+        ("sigma", C.c_double), ("actor_alpha", C.c_double),
+        ("action_min", C.c_double), ("action_max", C.c_double),
+        ("actor_resolution", C.c_double * MAX_DIMS), ("actor_wrapping", C.c_double * MAX_DIMS),
+    ]
+
+
+class Record(C.Structure):
+    _fields_ = [
+        ("started", C.c_int32), ("start_draw", C.c_double), ("start_state", C.c_double * MAX_STATE),
+        ("start_u", C.c_double), ("start_r_explore", C.c_uint32), ("start_r_tie", C.c_uint32),
+        ("start_action_index", C.c_int32), ("start_q", C.c_double * MAX_ACTIONS),
+        ("noise", C.c_double), ("start_noise", C.c_double),
+        ("state", C.c_double * MAX_STATE), ("action", C.c_double), ("next", C.c_double * MAX_STATE),
+        ("obs", C.c_double * MAX_DIMS), ("reward", C.c_double), ("terminal", C.c_int32), ("test", C.c_int32),
+        ("u", C.c_double), ("r_explore", C.c_uint32), ("r_tie", C.c_uint32), ("explored", C.c_int32),
+        ("hash", C.c_uint32 * (MAX_ACTIONS * MAX_TILINGS)), ("index", C.c_uint32 * (MAX_ACTIONS * MAX_TILINGS)),
+        ("q", C.c_double * MAX_ACTIONS), ("action_index", C.c_int32),
+        ("q_prev", C.c_double), ("target", C.c_double), ("delta", C.c_double),
+        ("swept", C.c_int32), ("swept_entries", C.c_int32),
+        ("trace_len", C.c_int32), ("trace_decay", C.c_double * MAX_TRACE),
+        ("trace_index", C.c_uint32 * (MAX_TRACE * MAX_TILINGS)),
+        ("episode_done", C.c_int32), ("episode_return", C.c_double),
+    ]
+
+
+def pendulum_config(memory=65536, **kw):
+    """cfg/pendulum/sarsa_tc.yaml (reference) with a per-agent table size."""
+    c = Config()
+    c.dynamics, c.integration_steps, c.control_step = DYN_PENDULUM, 5, 0.03
+    c.timeout, c.randomization = 2.99, 0.0
+    c.tilings, c.memory, c.obs_dims, c.n_actions = 16, memory, 2, 3
+    for i, v in enumerate([0.31415, 3.1415, 3]):
+        c.resolution[i] = v
+    for i, v in enumerate([6.283, 0, 0]):
+        c.wrapping[i] = v
+    for i, v in enumerate([-3.0, 0.0, 3.0]):
+        c.actions[i] = v
+    c.alpha, c.gamma, c.lambda_, c.epsilon = 0.2, 0.97, 0.65, 0.05
+    c.trace, c.test_interval = TRACE_REPLACING, 10
+    c.init_min, c.init_max, c.seed = 0.0, 1.0, 1
+    c.rng, c.algo = RNG_PHILOX, ALGO_SARSA
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+def cart_pole_config(memory=262144, **kw):
+    """cfg/cart_pole/sarsa.yaml (reference) with a per-agent table size."""
+    c = Config()
+    c.dynamics, c.integration_steps, c.control_step = DYN_CART_POLE, 5, 0.05
+    c.timeout, c.randomization = 9.99, 0.0
+    c.tilings, c.memory, c.obs_dims, c.n_actions = 16, memory, 4, 3
+    for i, v in enumerate([2.5, 0.157075, 2.5, 1.57075, 15]):
+        c.resolution[i] = v
+    for i, v in enumerate([0, 6.283, 0, 0, 0]):
+        c.wrapping[i] = v
+    for i, v in enumerate([-15.0, 0.0, 15.0]):
+        c.actions[i] = v
+    c.alpha, c.gamma, c.lambda_, c.epsilon = 0.2, 0.97, 0.65, 0.05
+    c.trace, c.test_interval = TRACE_REPLACING, 10
+    c.init_min, c.init_max, c.seed = 0.0, 1.0, 1
+    c.rng, c.algo = RNG_PHILOX, ALGO_SARSA
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+_lib = None
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR], check=True)
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = os.path.join(ORACLE_DIR, "liborc.so")
+    if not os.path.exists(path):
+        build()
+    L = C.CDLL(path)
+    dp, u32p, i32p = C.POINTER(C.c_double), C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
+    L.orc_hash.restype = C.c_uint32
+    L.orc_hash.argtypes = [i32p, C.c_uint32]
+    L.orc_murmur2_bytes.restype = C.c_uint32
+    L.orc_murmur2_bytes.argtypes = [C.c_void_p, C.c_int, C.c_uint32]
+    L.orc_project.restype = None
+    L.orc_project.argtypes = [dp, dp, C.c_int, C.c_int, C.c_int32, dp, u32p, u32p]
+    L.orc_eom.restype = None
+    L.orc_eom.argtypes = [C.c_int, dp, C.c_double, dp]
+    L.orc_rk4.restype = None
+    L.orc_rk4.argtypes = [C.c_int, C.c_double, C.c_int, dp, C.c_double, dp]
+    L.orc_state_dims.restype = C.c_int
+    L.orc_state_dims.argtypes = [C.c_int]
+    L.orc_env_step.restype = None
+    L.orc_env_step.argtypes = [C.POINTER(Config), dp, C.c_double, dp, dp, dp, i32p]
+    L.orc_philox.restype = None
+    L.orc_philox.argtypes = [C.c_uint32] * 6 + [u32p]
+    L.orc_create.restype = C.c_void_p
+    L.orc_create.argtypes = [C.POINTER(Config), C.c_uint64]
+    L.orc_destroy.restype = None
+    L.orc_destroy.argtypes = [C.c_void_p]
+    L.orc_set_hyper.restype = None
+    L.orc_set_hyper.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double]
+    L.orc_glibc_seed.restype = None
+    L.orc_glibc_seed.argtypes = [C.c_long]
+    L.orc_table.restype = dp
+    L.orc_table.argtypes = [C.c_void_p]
+    L.orc_actor_table.restype = dp
+    L.orc_actor_table.argtypes = [C.c_void_p]
+    L.orc_step.restype = C.c_int
+    L.orc_step.argtypes = [C.c_void_p, C.POINTER(Record)]
+    L.orc_run.restype = C.c_uint64
+    L.orc_run.argtypes = [C.c_void_p, C.c_uint64]
+    L.orc_stats.restype = None
+    L.orc_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                            C.POINTER(C.c_uint64), dp, dp]
+    _lib = L
+    return L
