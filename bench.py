@@ -1,0 +1,280 @@
+#!/usr/bin/env python
+"""bench.py -- agent-steps/sec of the batched GRL learning loop (step + tilecode + SARSA(lambda) update).
+
+One bench "step" = one pass of the hot path over one synthetic start-state batch: every agent runs
+STEPS_PER_PASS (=100, one pendulum episode) agent-steps.  Workload at N=1: BASELINE.json configs[1],
+pendulum swing-up SARSA(lambda) tile coding, 65,536 independent agents on one B200, per-agent table
+memory=65,536 entries (32 GiB of tables: far larger than L2, so nothing is cache-warm between passes).
+
+  value  : device-resident throughput (inputs already in HBM), CUDA events on the launching stream
+  e2e    : the same through grlcu_run_host with HOST buffers (H2D start states + D2H results inside)
+  roofline: algorithmic table bytes (640 + 16*V per agent-step, V measured on device) / run-kernel time
+  cpu_baseline: the CPU oracle (port of the reference; real grld needs Eigen, absent) on all host cores
+
+--impl reference times that CPU implementation alone, with the same JSON line layout.
+"""
+import argparse
+import ctypes as C
+import json
+import multiprocessing as mp
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+STEPS_PER_PASS = 100
+METRIC = "agent-steps/sec (step+tilecode+SARSA update)"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------- CPU oracle timing (reference arm)
+def _cpu_worker(args):
+    memory, agent_id, n_steps, dynamics = args
+    import _oracle as O
+    L = O.lib()
+    mk = O.pendulum_config if dynamics == 0 else O.cart_pole_config
+    cfg = mk(memory=memory, randomization=1.0, test_interval=-1)
+    a = L.orc_create(C.byref(cfg), agent_id)
+    L.orc_run(a, 2000)                         # warm the table/caches
+    t0 = time.perf_counter()
+    done = L.orc_run(a, n_steps)
+    dt = time.perf_counter() - t0
+    L.orc_destroy(a)
+    return done, dt
+
+
+def cpu_oracle_rate(memory, steps_per_proc, dynamics=0, procs=None):
+    """One oracle process per host core (the reference's grld is single-agent, single-thread);
+    aggregate agent-steps / wall time of the slowest process."""
+    import _oracle as O
+    O.build()
+    procs = procs or os.cpu_count() or 1
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(procs) as pool:
+        res = pool.map(_cpu_worker, [(memory, i, steps_per_proc, dynamics) for i in range(procs)])
+    wall = time.perf_counter() - t0
+    total = sum(r[0] for r in res)
+    slowest = max(r[1] for r in res)
+    return total / slowest, procs, wall
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    # size the sample so K+W steps finish within a few minutes: calibrate with a short run
+    rate0, procs, _ = cpu_oracle_rate(args.memory, 50000)
+    per_proc = max(int(rate0 / procs * 4.0), 10000)           # ~4 s of CPU work per step
+    for _ in range(args.warmup):
+        cpu_oracle_rate(args.memory, per_proc // 4)
+    rates, t0 = [], time.perf_counter()
+    for _ in range(args.steps):
+        r, procs, _ = cpu_oracle_rate(args.memory, per_proc)
+        rates.append(r)
+    wall = time.perf_counter() - t0
+    value = sum(rates) / len(rates)
+    sample = "%d oracle processes x %d agent-steps per bench step, memory=%d" % (procs, per_proc, args.memory)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * wall / max(args.steps, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": value, "unit": "agent-steps/s", "cores": procs, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference grld cannot be built (needs Eigen 3, absent): the timed CPU implementation is the "
+                "oracle port, pinned to the reference's golden curve (tests/test_oracle_golden.py)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, n_gpus):
+    return {"workload": "pendulum swing-up SARSA(lambda) tile coding (cfg/pendulum/sarsa_tc.yaml), "
+                        "%d independent agents per GPU" % args.agents,
+            "agents_per_gpu": args.agents, "agents_total": args.agents * n_gpus, "memory_per_agent": args.memory,
+            "agent_steps_per_pass": STEPS_PER_PASS, "tilings": 16, "actions": 3, "trace": "replacing",
+            "randomization": 1.0, "test_interval": -1, "cohort": args.cohort,
+            "l2": "tables (agents*memory*8 B = %.1f GiB per GPU) are far larger than L2; no flush needed"
+                  % (args.agents * args.memory * 8 / 2**30)}
+
+
+# ---------------------------------------------------------------- clocks sampler
+class Clocks(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                if out.returncode == 0 and out.stdout.strip():
+                    self.rows.append([x.strip() for x in out.stdout.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [nm for i, nm in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]),
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+# ---------------------------------------------------------------- our arm
+def ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import grl_b200
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the GRL B200 path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    cfg = grl_b200.pendulum_config(memory=args.memory, randomization=1.0, test_interval=-1)
+    stream = torch.cuda.current_stream().cuda_stream
+    batch = grl_b200.Batch(cfg, args.agents, first_agent_id=rank * args.agents, device=local, stream=stream)
+    n, S = args.agents, batch.S
+    bufs = batch.result_buffers()
+
+    # ---- device-resident throughput
+    for _ in range(args.warmup):
+        batch.run(STEPS_PER_PASS, args.cohort)
+    batch.sync()
+    batch.run_kernel_time()                    # drop warm-up events
+    r0 = batch.results()
+    launches0 = batch.launch_count()
+    clocks = Clocks(local)
+    clocks.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        batch.run(STEPS_PER_PASS, args.cohort)
+    e1.record()
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    kern_ms, kern_launches = batch.run_kernel_time()
+    launches = batch.launch_count() - launches0
+    r1 = batch.results()
+    steps_done = int((r1["steps"] - r0["steps"]).sum())
+    swept = int((r1["swept"] - r0["swept"]).sum())
+
+    # ---- end to end through the host-buffer call (pinned start states in, results out)
+    rng = np.random.default_rng(1234 + rank)
+    start = torch.zeros((n, S), dtype=torch.float64).pin_memory()
+    start_np = start.numpy()
+    start_np[:, 0] = np.pi + rng.uniform(0, 2 * np.pi, n)
+    for _ in range(max(1, min(args.warmup, 2))):
+        batch.run_host(start_np, STEPS_PER_PASS, args.cohort, bufs)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        start_np[:, 0] = np.pi + rng.uniform(0, 2 * np.pi, n)
+        batch.run_host(start_np, STEPS_PER_PASS, args.cohort, bufs)
+        _ = float(bufs["last_return"][0])
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clocks.stop_flag = True
+    clocks.join(timeout=2)
+    h2d = n * S * 8
+    d2h = n * (8 * 3 + 8 + 4 + 8)
+
+    # ---- max over ranks; the only collective: final statistics gather over NCCL
+    t = torch.tensor([dev_ms, e2e_s, kern_ms], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([steps_done, swept], dtype=torch.float64, device="cuda")
+    ret = torch.from_numpy(r1["last_return"]).cuda()
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        gathered = [torch.empty_like(ret) for _ in range(world)]
+        dist.all_gather(gathered, ret)
+        ret = torch.cat(gathered)
+    dev_ms, e2e_s, kern_ms = [float(x) for x in t.tolist()]
+    steps_all, swept_all = [float(x) for x in tot.tolist()]
+    mean_return = float(ret.mean())
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        V = swept_all / max(steps_all, 1)
+        B = 8 * 3 * 16 + 8 * 16 + 8 * 16 + 16 * V          # 640 + 16 V bytes per agent-step
+        per_gpu_steps = steps_all / world
+        achieved = per_gpu_steps * B / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
+        value = steps_all / (dev_ms * 1e-3)
+        e2e_val = args.agents * world * STEPS_PER_PASS * args.steps / e2e_s
+        line = {
+            "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, world),
+            "e2e": {"value": e2e_val, "unit": "agent-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches),
+            "clocks": clocks.summary(),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "bytes_per_agent_step": B, "V_mean": V, "kernel": "grlcu::k_run",
+                         "kernel_ms_per_launch": kern_ms / max(kern_launches, 1),
+                         "kernel_launches": int(kern_launches)},
+            "mean_last_return": mean_return,
+        }
+        if world == 1 and not args.no_cpu:
+            rate0, procs, _ = cpu_oracle_rate(args.memory, 50000)
+            per_proc = max(int(rate0 / procs * 12.0), 10000)
+            rate, procs, wall = cpu_oracle_rate(args.memory, per_proc)
+            line["cpu_baseline"] = {"value": rate, "unit": "agent-steps/s", "cores": procs, "kind": "port",
+                                    "sample": "%d oracle processes (one per core) x %d agent-steps, memory=%d, %.1f s"
+                                              % (procs, per_proc, args.memory, wall)}
+        print(json.dumps(line), flush=True)
+    batch.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--agents", type=int, default=65536, help="agents per GPU")
+    ap.add_argument("--memory", type=int, default=65536, help="table entries per agent")
+    ap.add_argument("--cohort", type=int, default=0, help="agents per L2-resident cohort (0 = all at once)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        ours(args)
+
+
+if __name__ == "__main__":
+    main()

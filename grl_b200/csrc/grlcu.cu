@@ -1,0 +1,578 @@
+// grlcu.cu -- C ABI (include/grlcu.h) over the sm_100a kernels.  No CPU fallback: every entry point
+// needs a usable CUDA device and reports GRLCU_ERR_CUDA otherwise.
+#include "../../include/grlcu.h"
+#include "grlcu_kernels.cuh"
+
+#include <cuda_runtime.h>
+#include <cmath>
+#include <cstdio>
+#include <cstdarg>
+#include <cstring>
+#include <new>
+#include <vector>
+
+using namespace grlcu;
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char *fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(GRLCU_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                  __FILE__, __LINE__);                                                    \
+  } while (0)
+
+struct grlcu_ctx
+{
+  grlcu_config cfg;
+  Params p;
+  int device;
+  cudaStream_t stream;
+  int S, OBS;
+  std::vector<void *> allocs;
+  double *d_alpha, *d_lambda, *d_epsilon, *d_start;
+  int64_t launches;
+  // run-kernel timing (events recorded around every k_run launch)
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending;
+  std::vector<cudaEvent_t> ev_pool;
+  int block;
+};
+
+extern "C" const char *grlcu_last_error(void) { return g_err; }
+extern "C" int grlcu_version(void) { return 1; }
+
+template <typename Tp>
+static int dalloc(grlcu_ctx *c, Tp **ptr, size_t count)
+{
+  void *q = nullptr;
+  cudaError_t e = cudaMalloc(&q, count * sizeof(Tp));
+  if (e != cudaSuccess)
+    return fail(GRLCU_ERR_NOMEM, "cudaMalloc of %zu bytes failed: %s", count * sizeof(Tp), cudaGetErrorString(e));
+  c->allocs.push_back(q);
+  *ptr = (Tp *)q;
+  return 0;
+}
+
+static int grid_for(int64_t work, int block, int cap = 148 * 16)
+{
+  int64_t g = (work + block - 1) / block;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+static int supported(const grlcu_config *cfg)
+{
+  if (cfg->algo != GRLCU_ALGO_SARSA)
+    return fail(GRLCU_ERR_UNSUPPORTED, "algo %d: only SARSA is built in this version", cfg->algo);
+  if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE)
+    return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for SARSA", cfg->dynamics);
+  if (cfg->tilings != 16) return fail(GRLCU_ERR_UNSUPPORTED, "tilings %d: kernels are instantiated for 16", cfg->tilings);
+  if (cfg->n_actions != 3) return fail(GRLCU_ERR_UNSUPPORTED, "n_actions %d: kernels are instantiated for 3", cfg->n_actions);
+  const int obs = cfg->dynamics == GRLCU_DYN_PENDULUM ? 2 : 4;
+  if (cfg->obs_dims != obs) return fail(GRLCU_ERR_ARG, "obs_dims %d does not match dynamics (%d)", cfg->obs_dims, obs);
+  if (cfg->memory < 1) return fail(GRLCU_ERR_ARG, "memory must be positive");
+  if (cfg->integration_steps < 1) return fail(GRLCU_ERR_ARG, "integration_steps must be >= 1");
+  return 0;
+}
+
+// smallest n with e^n < dc by repeated multiplication (the trace's own arithmetic) + 1 slack
+static int trace_capacity_for(double e, int kind)
+{
+  if (kind == GRLCU_TRACE_NONE) return 1;
+  const double dc = kind == GRLCU_TRACE_REPLACING ? 0.01 : 0.0001;
+  if (!(e < 1.0)) return -1;
+  double t = 1.;
+  int n = 0;
+  while (!(t < dc) && n < 4096) { t *= e; ++n; }
+  return n + 1;
+}
+
+static int launch_reset(grlcu_ctx *c, int what);
+
+extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t first_agent_id,
+                            int32_t device, void *stream, grlcu_ctx **out)
+{
+  if (!cfg || !out || n_agents < 1) return fail(GRLCU_ERR_ARG, "grlcu_create: bad arguments");
+  *out = nullptr;
+  if (int r = supported(cfg)) return r;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev < 1)
+    return fail(GRLCU_ERR_CUDA, "no CUDA device available (%s); libgrlcu has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail(GRLCU_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
+  CU(cudaSetDevice(device));
+
+  grlcu_ctx *c = new (std::nothrow) grlcu_ctx();
+  if (!c) return fail(GRLCU_ERR_NOMEM, "out of host memory");
+  c->cfg = *cfg;
+  c->device = device;
+  c->stream = (cudaStream_t)stream;
+  c->S = cfg->dynamics == GRLCU_DYN_PENDULUM ? 3 : cfg->dynamics == GRLCU_DYN_CART_POLE ? 5 : 7;
+  c->OBS = cfg->obs_dims;
+  c->d_alpha = c->d_lambda = c->d_epsilon = c->d_start = nullptr;
+  c->launches = 0;
+  c->block = 64;
+  if (const char *b = getenv("GRLCU_BLOCK")) { int v = atoi(b); if (v >= 32 && v <= 128 && v % 32 == 0) c->block = v; }
+
+  Params &p = c->p;
+  memset(&p, 0, sizeof(p));
+  p.n = n_agents; p.first_id = first_agent_id; p.seed = cfg->seed;
+  p.tau = cfg->control_step; p.isteps = cfg->integration_steps;
+  p.timeout = cfg->timeout; p.randomization = cfg->randomization;
+  // TileCodingProjector::configure (tile_coding.cpp:66-79)
+  const int dims = cfg->obs_dims + 1;
+  for (int i = 0; i < dims; ++i)
+  {
+    p.proj.scaling[i] = cfg->tilings / cfg->resolution[i];
+    double w = cfg->wrapping[i] * p.proj.scaling[i];
+    if (fabs(w - round(w)) > 0.001)
+    {
+      delete c;
+      return fail(GRLCU_ERR_ARG, "projector/tile_coding:wrapping: scaled wrapping for dimension %d (%.5f) is not an integer", i, w);
+    }
+    p.proj.wrap[i] = (int32_t)round(w);
+  }
+  p.proj.memory = cfg->memory;
+  for (int i = 0; i < cfg->n_actions; ++i) p.actions[i] = cfg->actions[i];
+  p.test_interval = cfg->test_interval;
+  p.alpha = cfg->alpha; p.gamma = cfg->gamma; p.lambda = cfg->lambda; p.epsilon = cfg->epsilon;
+  p.trace_kind = cfg->trace;
+  p.trace_cap = trace_capacity_for(cfg->gamma * cfg->lambda, cfg->trace);
+  if (p.trace_cap < 0 || p.trace_cap > 160)
+  {
+    delete c;
+    return fail(GRLCU_ERR_UNSUPPORTED, "gamma*lambda = %g needs an unbounded or too long trace", cfg->gamma * cfg->lambda);
+  }
+
+  const size_t n = (size_t)n_agents, T = (size_t)cfg->tilings;
+  int r = 0;
+  if (!r) r = dalloc(c, &p.table, n * (size_t)cfg->memory);
+  if (!r) r = dalloc(c, &p.state, n * c->S);
+  if (!r) r = dalloc(c, &p.action, n);
+  if (!r) r = dalloc(c, &p.prev_idx, n * T);
+  if (!r) r = dalloc(c, &p.trace_idx, n * T * (size_t)p.trace_cap);
+  if (!r) r = dalloc(c, &p.trace_len, n);
+  if (!r) r = dalloc(c, &p.trace_head, n);
+  if (!r) r = dalloc(c, &p.total_decay, n);
+  if (!r) r = dalloc(c, &p.flags, n);
+  if (!r) r = dalloc(c, &p.act_ctr, n);
+  if (!r) r = dalloc(c, &p.test_act_ctr, n);
+  if (!r) r = dalloc(c, &p.episode_ctr, n);
+  if (!r) r = dalloc(c, &p.tt, n);
+  if (!r) r = dalloc(c, &p.ss, n);
+  if (!r) r = dalloc(c, &p.swept, n);
+  if (!r) r = dalloc(c, &p.episodes, n);
+  if (!r) r = dalloc(c, &p.total_reward, n);
+  if (!r) r = dalloc(c, &p.last_return, n);
+  if (!r) r = dalloc(c, &p.last_test_return, n);
+  if (!r) r = dalloc(c, &p.return_sum, n);
+  if (!r) r = launch_reset(c, GRLCU_RESET_TABLES | GRLCU_RESET_AGENTS | GRLCU_RESET_STATS);
+  if (!r)
+  {
+    cudaError_t es = cudaStreamSynchronize(c->stream);
+    if (es != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "table initialisation failed: %s", cudaGetErrorString(es));
+  }
+  if (r) { grlcu_destroy(c); return r; }
+  *out = c;
+  return 0;
+}
+
+extern "C" int grlcu_destroy(grlcu_ctx *c)
+{
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (auto &pr : c->ev_pending) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  for (auto ev : c->ev_pool) cudaEventDestroy(ev);
+  for (void *q : c->allocs) cudaFree(q);
+  delete c;
+  return 0;
+}
+
+// ---- reset ---------------------------------------------------------------------------------
+__global__ void k_reset_agents(Params p)
+{
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= p.n) return;
+  p.flags[a] = 0; p.trace_len[a] = 0; p.trace_head[a] = 0; p.total_decay[a] = 1.;
+  p.total_reward[a] = 0; p.action[a] = 0;
+  p.act_ctr[a] = 0; p.test_act_ctr[a] = 0; p.episode_ctr[a] = 0; p.tt[a] = 0;
+}
+
+__global__ void k_reset_stats(Params p)
+{
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= p.n) return;
+  p.ss[a] = 0; p.swept[a] = 0; p.episodes[a] = 0;
+  p.last_return[a] = 0; p.last_test_return[a] = 0; p.return_sum[a] = 0;
+}
+
+__global__ void k_begin_override(Params p)
+{
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= p.n) return;
+  p.flags[a] = 4;     // not in episode, start-state override pending
+}
+
+static int launch_reset(grlcu_ctx *c, int what)
+{
+  Params &p = c->p;
+  const int blk = 256, grd = (p.n + blk - 1) / blk;
+  if (what & GRLCU_RESET_TABLES)
+  {
+    const int64_t work = ((int64_t)c->cfg.memory + 1) / 2 * p.n;
+    k_table_init<<<grid_for(work, 256, 148 * 32), 256, 0, c->stream>>>(
+        p.table, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_TABLE);
+    c->launches++;
+  }
+  if (what & GRLCU_RESET_AGENTS) { k_reset_agents<<<grd, blk, 0, c->stream>>>(p); c->launches++; }
+  if (what & GRLCU_RESET_STATS) { k_reset_stats<<<grd, blk, 0, c->stream>>>(p); c->launches++; }
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int grlcu_reset(grlcu_ctx *c, int32_t what)
+{
+  if (!c) return fail(GRLCU_ERR_ARG, "null context");
+  CU(cudaSetDevice(c->device));
+  return launch_reset(c, what);
+}
+
+static int upload_opt(grlcu_ctx *c, double **dst, const double *src)
+{
+  if (!src) return 0;
+  if (!*dst) if (int r = dalloc(c, dst, (size_t)c->p.n)) return r;
+  CU(cudaMemcpyAsync(*dst, src, sizeof(double) * c->p.n, cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+extern "C" int grlcu_set_hyper(grlcu_ctx *c, const double *alpha, const double *lambda, const double *epsilon)
+{
+  if (!c) return fail(GRLCU_ERR_ARG, "null context");
+  CU(cudaSetDevice(c->device));
+  if (lambda)
+  {
+    double mx = 0;
+    for (int i = 0; i < c->p.n; ++i) mx = lambda[i] > mx ? lambda[i] : mx;
+    int cap = trace_capacity_for(c->cfg.gamma * mx, c->cfg.trace);
+    if (cap < 0 || cap > c->p.trace_cap)
+      return fail(GRLCU_ERR_ARG, "per-agent lambda up to %g needs trace capacity %d > %d: create the context "
+                  "with config lambda = the largest lambda of the sweep", mx, cap, c->p.trace_cap);
+  }
+  if (int r = upload_opt(c, &c->d_alpha, alpha)) return r;
+  if (int r = upload_opt(c, &c->d_lambda, lambda)) return r;
+  if (int r = upload_opt(c, &c->d_epsilon, epsilon)) return r;
+  CU(cudaStreamSynchronize(c->stream));
+  c->p.alpha_a = c->d_alpha; c->p.lambda_a = c->d_lambda; c->p.epsilon_a = c->d_epsilon;
+  return 0;
+}
+
+// ---- scratch helpers for the host-buffer entry points ------------------------------------------
+struct Scratch
+{
+  std::vector<void *> ptrs;
+  ~Scratch() { for (void *q : ptrs) cudaFree(q); }
+  template <typename Tp> Tp *get(size_t count)
+  {
+    void *q = nullptr;
+    if (cudaMalloc(&q, count * sizeof(Tp) + 16) != cudaSuccess) return nullptr;
+    ptrs.push_back(q);
+    return (Tp *)q;
+  }
+};
+
+#define DISPATCH_DYN(c, CALL)                                   \
+  do {                                                          \
+    if ((c)->cfg.dynamics == GRLCU_DYN_PENDULUM) { CALL(0); }   \
+    else { CALL(1); }                                           \
+  } while (0)
+
+extern "C" int grlcu_project(grlcu_ctx *c, int64_t n, const double *in, uint32_t *hash, uint32_t *index)
+{
+  if (!c || n < 0 || !in || !index) return fail(GRLCU_ERR_ARG, "grlcu_project: bad arguments");
+  if (n == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  const int dims = c->cfg.obs_dims + 1, T = c->cfg.tilings;
+  Scratch s;
+  double *d_in = s.get<double>((size_t)n * dims);
+  uint32_t *d_h = s.get<uint32_t>((size_t)n * T), *d_i = s.get<uint32_t>((size_t)n * T);
+  if (!d_in || !d_h || !d_i) return fail(GRLCU_ERR_NOMEM, "grlcu_project: out of device memory");
+  CU(cudaMemcpyAsync(d_in, in, sizeof(double) * n * dims, cudaMemcpyHostToDevice, c->stream));
+  const int grd = grid_for(n, 128);
+#define CALL(D) k_project<Dyn<D>::OBS + 1, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i)
+  DISPATCH_DYN(c, CALL);
+#undef CALL
+  c->launches++;
+  CU(cudaGetLastError());
+  if (hash) CU(cudaMemcpyAsync(hash, d_h, sizeof(uint32_t) * n * T, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(index, d_i, sizeof(uint32_t) * n * T, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int grlcu_model_step(grlcu_ctx *c, int64_t n, const double *state, const double *action,
+                                double *next, double *obs, double *reward, int32_t *terminal)
+{
+  if (!c || n < 0 || !state || !action || !next || !obs || !reward || !terminal)
+    return fail(GRLCU_ERR_ARG, "grlcu_model_step: bad arguments");
+  if (n == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  const int S = c->S, OBS = c->OBS;
+  Scratch s;
+  double *d_s = s.get<double>((size_t)n * S), *d_a = s.get<double>(n), *d_n = s.get<double>((size_t)n * S),
+         *d_o = s.get<double>((size_t)n * OBS), *d_r = s.get<double>(n);
+  int32_t *d_t = s.get<int32_t>(n);
+  if (!d_s || !d_a || !d_n || !d_o || !d_r || !d_t) return fail(GRLCU_ERR_NOMEM, "grlcu_model_step: out of device memory");
+  CU(cudaMemcpyAsync(d_s, state, sizeof(double) * n * S, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_a, action, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+  const int grd = grid_for(n, 128);
+#define CALL(D) k_model_step<D><<<grd, 128, 0, c->stream>>>(n, c->p.tau, c->p.isteps, c->p.timeout, d_s, d_a, d_n, d_o, d_r, d_t)
+  DISPATCH_DYN(c, CALL);
+#undef CALL
+  c->launches++;
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(next, d_n, sizeof(double) * n * S, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(obs, d_o, sizeof(double) * n * OBS, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(reward, d_r, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(terminal, d_t, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// ---- fused run -------------------------------------------------------------------------------
+static cudaEvent_t get_event(grlcu_ctx *c)
+{
+  if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  return e;
+}
+
+extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
+{
+  if (!c || n_steps < 0) return fail(GRLCU_ERR_ARG, "grlcu_run: bad arguments");
+  if (n_steps == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  const int n = c->p.n;
+  if (cohort <= 0 || cohort > n) cohort = n;
+  for (int begin = 0; begin < n; begin += cohort)
+  {
+    const int end = begin + cohort < n ? begin + cohort : n;
+    const int grd = (end - begin + c->block - 1) / c->block;
+    cudaEvent_t e0 = get_event(c), e1 = get_event(c);
+    CU(cudaEventRecord(e0, c->stream));
+#define CALL(D) k_run<D, 16, 3><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps)
+    DISPATCH_DYN(c, CALL);
+#undef CALL
+    CU(cudaEventRecord(e1, c->stream));
+    c->ev_pending.push_back({e0, e1});
+    c->launches++;
+  }
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int grlcu_sync(grlcu_ctx *c)
+{
+  if (!c) return fail(GRLCU_ERR_ARG, "null context");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int grlcu_run_kernel_time(grlcu_ctx *c, double *ms, int64_t *launches)
+{
+  if (!c) return fail(GRLCU_ERR_ARG, "null context");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  double total = 0;
+  for (auto &pr : c->ev_pending)
+  {
+    float t = 0;
+    CU(cudaEventElapsedTime(&t, pr.first, pr.second));
+    total += t;
+    c->ev_pool.push_back(pr.first); c->ev_pool.push_back(pr.second);
+  }
+  if (ms) *ms = total;
+  if (launches) *launches = (int64_t)c->ev_pending.size();
+  c->ev_pending.clear();
+  return 0;
+}
+
+extern "C" int64_t grlcu_launch_count(grlcu_ctx *c) { return c ? c->launches : -1; }
+extern "C" int grlcu_trace_capacity(grlcu_ctx *c) { return c ? c->p.trace_cap : -1; }
+
+// ---- results / tables --------------------------------------------------------------------------
+template <typename Tp>
+static int d2h(grlcu_ctx *c, Tp *dst, const Tp *src, size_t count)
+{
+  if (!dst) return 0;
+  CU(cudaMemcpyAsync(dst, src, sizeof(Tp) * count, cudaMemcpyDeviceToHost, c->stream));
+  return 0;
+}
+
+static int results_async(grlcu_ctx *c, grlcu_results *r)
+{
+  if (!r) return 0;
+  const Params &p = c->p;
+  const size_t n = (size_t)p.n;
+  if (int e = d2h(c, r->last_return, p.last_return, n)) return e;
+  if (int e = d2h(c, r->last_test_return, p.last_test_return, n)) return e;
+  if (int e = d2h(c, r->return_sum, p.return_sum, n)) return e;
+  if (int e = d2h(c, r->steps, p.ss, n)) return e;
+  if (int e = d2h(c, r->episodes, p.episodes, n)) return e;
+  if (int e = d2h(c, r->swept, p.swept, n)) return e;
+  return 0;
+}
+
+extern "C" int grlcu_get_results(grlcu_ctx *c, grlcu_results *r)
+{
+  if (!c || !r) return fail(GRLCU_ERR_ARG, "grlcu_get_results: bad arguments");
+  CU(cudaSetDevice(c->device));
+  if (int e = results_async(c, r)) return e;
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+__global__ void k_transpose_start(const double *rows, double *soa, int n, int S)
+{
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n) return;
+  for (int i = 0; i < S; ++i) soa[(size_t)i * n + a] = rows[(size_t)a * S + i];
+}
+
+extern "C" int grlcu_run_host(grlcu_ctx *c, const double *start_states, int64_t n_steps, int32_t cohort,
+                              grlcu_results *results)
+{
+  if (!c || n_steps < 0) return fail(GRLCU_ERR_ARG, "grlcu_run_host: bad arguments");
+  CU(cudaSetDevice(c->device));
+  const int n = c->p.n, S = c->S;
+  if (start_states)
+  {
+    if (!c->d_start) if (int r = dalloc(c, &c->d_start, (size_t)n * S * 2)) return r;
+    double *rows = c->d_start + (size_t)n * S;
+    CU(cudaMemcpyAsync(rows, start_states, sizeof(double) * n * S, cudaMemcpyHostToDevice, c->stream));
+    const int blk = 256, grd = (n + blk - 1) / blk;
+    k_transpose_start<<<grd, blk, 0, c->stream>>>(rows, c->d_start, n, S);
+    k_begin_override<<<grd, blk, 0, c->stream>>>(c->p);
+    c->launches += 2;
+    c->p.start_override = c->d_start;
+  }
+  if (int r = grlcu_run(c, n_steps, cohort)) return r;
+  if (int r = results_async(c, results)) return r;
+  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int grlcu_get_table(grlcu_ctx *c, int32_t agent, double *out)
+{
+  if (!c || !out || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_get_table: bad arguments");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(out, c->p.table + (size_t)agent * c->cfg.memory, sizeof(double) * c->cfg.memory,
+                     cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int grlcu_set_table(grlcu_ctx *c, int32_t agent, const double *in)
+{
+  if (!c || !in || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_set_table: bad arguments");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->p.table + (size_t)agent * c->cfg.memory, in, sizeof(double) * c->cfg.memory,
+                     cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int grlcu_get_state(grlcu_ctx *c, int32_t agent, double *state, double *action, int32_t *in_episode)
+{
+  if (!c || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_get_state: bad arguments");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  if (state)
+    for (int i = 0; i < c->S; ++i)
+      CU(cudaMemcpy(state + i, c->p.state + (size_t)i * c->p.n + agent, sizeof(double), cudaMemcpyDeviceToHost));
+  if (action) CU(cudaMemcpy(action, c->p.action + agent, sizeof(double), cudaMemcpyDeviceToHost));
+  if (in_episode)
+  {
+    int32_t f = 0;
+    CU(cudaMemcpy(&f, c->p.flags + agent, sizeof(int32_t), cudaMemcpyDeviceToHost));
+    *in_episode = f & 1;
+  }
+  return 0;
+}
+
+// ---- replay ------------------------------------------------------------------------------------
+extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_replay_out *out)
+{
+  if (!c || !in || !out) return fail(GRLCU_ERR_ARG, "grlcu_replay_step: bad arguments");
+  if (!in->started || !in->state || !in->action || !in->test || !in->obs || !in->reward || !in->terminal ||
+      !in->u || !in->r_explore || !in->r_tie || !in->start_state || !in->start_u || !in->start_r_explore ||
+      !in->start_r_tie)
+    return fail(GRLCU_ERR_ARG, "grlcu_replay_step: missing input array");
+  CU(cudaSetDevice(c->device));
+  const size_t n = (size_t)c->p.n, S = (size_t)c->S, OBS = (size_t)c->OBS, T = (size_t)c->cfg.tilings,
+               A = (size_t)c->cfg.n_actions, cap = (size_t)c->p.trace_cap;
+  Scratch s;
+  ReplayIO io;
+  memset(&io, 0, sizeof(io));
+  bool oom = false;
+#define UP(field, type, count)                                                                  \
+  do {                                                                                          \
+    type *d = s.get<type>(count);                                                               \
+    if (!d) { oom = true; break; }                                                              \
+    if (cudaMemcpyAsync(d, in->field, sizeof(type) * (count), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) oom = true; \
+    io.field = d;                                                                               \
+  } while (0)
+  UP(started, int32_t, n); UP(start_state, double, S * n); UP(start_u, double, n);
+  UP(start_r_explore, uint32_t, n); UP(start_r_tie, uint32_t, n);
+  UP(state, double, S * n); UP(action, double, n); UP(test, int32_t, n);
+  UP(obs, double, OBS * n); UP(reward, double, n); UP(terminal, int32_t, n);
+  UP(u, double, n); UP(r_explore, uint32_t, n); UP(r_tie, uint32_t, n);
+  if (in->force_action) UP(force_action, int32_t, n);
+#undef UP
+#define OUTB(ofield, field, type, count) \
+  do { if (out->field) { io.ofield = s.get<type>(count); if (!io.ofield) oom = true; } } while (0)
+  OUTB(o_next, next, double, S * n); OUTB(o_obs, obs, double, OBS * n); OUTB(o_reward, reward, double, n);
+  OUTB(o_terminal, terminal, int32_t, n); OUTB(o_hash, hash, uint32_t, A * T * n);
+  OUTB(o_index, index, uint32_t, A * T * n); OUTB(o_q, q, double, A * n);
+  OUTB(o_action_index, action_index, int32_t, n); OUTB(o_start_q, start_q, double, A * n);
+  OUTB(o_start_action_index, start_action_index, int32_t, n);
+  OUTB(o_q_prev, q_prev, double, n); OUTB(o_target, target, double, n); OUTB(o_delta, delta, double, n);
+  OUTB(o_swept, swept, int32_t, n); OUTB(o_trace_len, trace_len, int32_t, n);
+  OUTB(o_trace_index, trace_index, uint32_t, cap * T * n);
+#undef OUTB
+  if (oom) return fail(GRLCU_ERR_NOMEM, "grlcu_replay_step: device scratch allocation/copy failed");
+  const int blk = 64, grd = ((int)n + blk - 1) / blk;
+#define CALL(D) k_replay<D, 16, 3><<<grd, blk, 0, c->stream>>>(c->p, io)
+  DISPATCH_DYN(c, CALL);
+#undef CALL
+  c->launches++;
+  CU(cudaGetLastError());
+#define DOWN(ofield, field, type, count) \
+  do { if (out->field) CU(cudaMemcpyAsync(out->field, io.ofield, sizeof(type) * (count), cudaMemcpyDeviceToHost, c->stream)); } while (0)
+  DOWN(o_next, next, double, S * n); DOWN(o_obs, obs, double, OBS * n); DOWN(o_reward, reward, double, n);
+  DOWN(o_terminal, terminal, int32_t, n); DOWN(o_hash, hash, uint32_t, A * T * n);
+  DOWN(o_index, index, uint32_t, A * T * n); DOWN(o_q, q, double, A * n);
+  DOWN(o_action_index, action_index, int32_t, n); DOWN(o_start_q, start_q, double, A * n);
+  DOWN(o_start_action_index, start_action_index, int32_t, n);
+  DOWN(o_q_prev, q_prev, double, n); DOWN(o_target, target, double, n); DOWN(o_delta, delta, double, n);
+  DOWN(o_swept, swept, int32_t, n); DOWN(o_trace_len, trace_len, int32_t, n);
+  DOWN(o_trace_index, trace_index, uint32_t, cap * T * n);
+#undef DOWN
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}

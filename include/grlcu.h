@@ -1,0 +1,192 @@
+/* grlcu.h -- C ABI of the B200-native batched GRL learning loop (libgrlcu.so).
+ *
+ * This is the drop-in boundary for ONE hot path of wcaarls/grl: the on-line learning
+ * loop (RK4 environment step -> tile-coding hash -> linear Q read -> epsilon-greedy ->
+ * SARSA(lambda) update with enumerated trace), batched over many independent agents.
+ * GRL itself has no C FFI: the path sits behind its C++ Configurable plugin API
+ * (base/include/grl/configurable.h:704-826).  The callers of this ABI are the thin C++
+ * Configurable shims in grl_b200/host/ (environment/model/cuda_batched,
+ * projector/tile_coding/cuda, representation/linear/cuda, predictor/sarsa/cuda; see
+ * INTEGRATION.md) and the Python ctypes harness used by tests/ and bench.py.
+ *
+ * Conventions: plain pointers and sizes, caller-owned HOST buffers unless a name says
+ * "_dev", int return codes (0 = ok, non-zero = error, text in grlcu_last_error()),
+ * opaque context handle, one context per host thread / GPU.  There is no CPU fallback:
+ * every entry point fails with GRLCU_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to
+ * /root/reference/base).
+ */
+#ifndef GRLCU_H_
+#define GRLCU_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GRLCU_MAX_DIMS 8
+#define GRLCU_MAX_ACTIONS 8
+#define GRLCU_MAX_STATE 7
+
+enum { GRLCU_DYN_PENDULUM = 0, GRLCU_DYN_CART_POLE = 1, GRLCU_DYN_CART_DOUBLE_POLE = 2 };
+enum { GRLCU_TRACE_NONE = 0, GRLCU_TRACE_REPLACING = 1, GRLCU_TRACE_ACCUMULATING = 2 };
+enum { GRLCU_ALGO_SARSA = 0, GRLCU_ALGO_AC = 1 };
+enum { GRLCU_OK = 0, GRLCU_ERR_ARG = 1, GRLCU_ERR_CUDA = 2, GRLCU_ERR_UNSUPPORTED = 3,
+       GRLCU_ERR_NOMEM = 4 };
+enum { GRLCU_RESET_TABLES = 1, GRLCU_RESET_AGENTS = 2, GRLCU_RESET_STATS = 4 };
+
+/* Parameters of the four GRL objects on the path, named after their YAML keys. */
+typedef struct grlcu_config
+{
+  int32_t dynamics;           /* dynamics/pendulum | cart_pole | cart_double_pole */
+  int32_t integration_steps;  /* model/dynamical integration_steps (modeled.cpp:234-240) */
+  double  control_step;       /* model/dynamical control_step */
+  double  timeout;            /* task timeout */
+  double  randomization;      /* task randomization */
+  int32_t tilings;            /* projector/tile_coding tilings (tile_coding.cpp:35-43) */
+  int32_t memory;             /* projector/tile_coding memory = table entries PER AGENT */
+  int32_t obs_dims;           /* task observation_dims */
+  int32_t n_actions;          /* discretizer/uniform: number of discrete actions */
+  double  resolution[GRLCU_MAX_DIMS];   /* projector resolution (obs dims then action) */
+  double  wrapping[GRLCU_MAX_DIMS];     /* projector wrapping */
+  double  actions[GRLCU_MAX_ACTIONS];   /* discretizer values (uniform.cpp:60-94) */
+  double  alpha, gamma, lambda, epsilon; /* predictor/critic/sarsa, sampler/epsilon_greedy */
+  int32_t trace;              /* trace/enumerated/replacing | accumulating | none */
+  int32_t test_interval;      /* experiment/online_learning test_interval (-1 = none) */
+  double  init_min, init_max; /* representation/parameterized/linear init_min/init_max */
+  uint64_t seed;              /* Philox key; stream = global agent id */
+  int32_t rng;                /* ignored (oracle field) */
+  int32_t algo;               /* GRLCU_ALGO_* */
+  double  sigma;              /* policy/action sigma (AC) */
+  double  actor_alpha;        /* predictor/ac/action alpha (AC) */
+  double  action_min, action_max;
+  double  actor_resolution[GRLCU_MAX_DIMS];
+  double  actor_wrapping[GRLCU_MAX_DIMS];
+} grlcu_config;
+
+typedef struct grlcu_ctx grlcu_ctx;
+
+/* Replay-mode inputs for one agent-step of every agent (host, SoA: [field][agent]).
+ * Replaces nothing in the reference: it is the north-star's correctness harness
+ * ("feeds identical states, actions and random draws to both implementations"). */
+typedef struct grlcu_replay_in
+{
+  const int32_t  *started;       /* [n] 1: perform an episode start first */
+  const double   *start_state;   /* [S][n] state after Task::start */
+  const double   *start_u;       /* [n] draws of the start act() */
+  const uint32_t *start_r_explore, *start_r_tie;
+  const double   *state;         /* [S][n] state before the step (re-fed every step) */
+  const double   *action;        /* [n] action to apply */
+  const int32_t  *test;          /* [n] test episode flag */
+  const double   *obs;           /* [obs_dims][n] observation fed to the agent half */
+  const double   *reward;        /* [n] reward fed to the agent half */
+  const int32_t  *terminal;      /* [n] terminal fed to the agent half */
+  const double   *u;             /* [n] draws of this step's act() */
+  const uint32_t *r_explore, *r_tie;
+  const int32_t  *force_action;  /* [n] action index to commit (or NULL: use own choice) */
+} grlcu_replay_in;
+
+/* Replay-mode outputs (host, SoA).  Any pointer may be NULL. */
+typedef struct grlcu_replay_out
+{
+  double   *next;          /* [S][n] RK4 result from in.state, in.action */
+  double   *obs;           /* [obs_dims][n] observe(next) */
+  double   *reward;        /* [n] evaluate(state, action, next) */
+  int32_t  *terminal;      /* [n] */
+  uint32_t *hash;          /* [A][T][n] tile hashes of (in.obs, a) */
+  uint32_t *index;         /* [A][T][n] hash % memory */
+  double   *q;             /* [A][n] */
+  int32_t  *action_index;  /* [n] own choice (-1 when terminal == 2) */
+  double   *start_q;       /* [A][n] (only meaningful where started) */
+  int32_t  *start_action_index; /* [n] */
+  double   *q_prev, *target, *delta;   /* [n] */
+  int32_t  *swept;         /* [n] valid trace indices swept (V) */
+  int32_t  *trace_len;     /* [n] after add() */
+  uint32_t *trace_index;   /* [trace_cap][T][n] newest first, 0xFFFFFFFF = invalidated */
+} grlcu_replay_out;
+
+/* Per-agent results (host arrays of n_agents). Any pointer may be NULL. */
+typedef struct grlcu_results
+{
+  double   *last_return;       /* return of the last finished learning episode */
+  double   *last_test_return;  /* return of the last finished test episode */
+  double   *return_sum;        /* sum of learning-episode returns */
+  uint64_t *steps;             /* learning steps (ss, online_learning.cpp:219) */
+  uint32_t *episodes;          /* finished episodes (learning + test) */
+  uint64_t *swept;             /* sum of V over learning steps */
+} grlcu_results;
+
+const char *grlcu_last_error(void);
+int grlcu_version(void);
+
+/* Creates the device-resident state of n_agents agents with global ids
+ * [first_agent_id, first_agent_id + n_agents) on CUDA device `device`, launching on
+ * `stream` (a cudaStream_t, NULL = default stream).  Tables are initialised like
+ * LinearRepresentation::reset (linear.cpp:104-125) from Philox(seed, agent id).
+ * Replaces: object construction + configure() of ModeledEnvironment/DynamicalModel
+ * (modeled.cpp:59-121,234-252), TileCodingProjector (tile_coding.cpp:45-80),
+ * LinearRepresentation (linear.cpp:66-102), SARSAPredictor (sarsa.cpp:48-59). */
+int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t first_agent_id,
+                 int32_t device, void *stream, grlcu_ctx **out);
+int grlcu_destroy(grlcu_ctx *ctx);
+
+/* reconfigure(action=reset) of the objects (linear.cpp:104-125, sarsa.cpp:61-67,
+ * modeled.cpp:117-121).  what = OR of GRLCU_RESET_*. */
+int grlcu_reset(grlcu_ctx *ctx, int32_t what);
+
+/* Per-agent alpha / lambda / epsilon (cfg 5 hyper-parameter sweep).  NULL keeps the
+ * config value.  Replaces per-instance YAML parameters of MultiExperiment / grlo. */
+int grlcu_set_hyper(grlcu_ctx *ctx, const double *alpha, const double *lambda, const double *epsilon);
+
+/* K2: TileCodingProjector::_project (tile_coding.cpp:103-149, tile_coding.h:78-151).
+ * in: [n][dims] row-major, dims = obs_dims + 1.  hash/index: [n][tilings]. */
+int grlcu_project(grlcu_ctx *ctx, int64_t n, const double *in, uint32_t *hash, uint32_t *index);
+
+/* K1: ModeledEnvironment::step body (modeled.cpp:160-213) = Task::actuate +
+ * DynamicalModel::step (modeled.cpp:254-276) + Task::observe + Task::evaluate.
+ * state/next: [n][S] row-major; action/reward: [n]; obs: [n][obs_dims]. */
+int grlcu_model_step(grlcu_ctx *ctx, int64_t n, const double *state, const double *action,
+                     double *next, double *obs, double *reward, int32_t *terminal);
+
+/* Fused K1-K4: n_steps iterations of online_learning.cpp:186-221 for every agent
+ * (episode start/end handled on device).  Asynchronous on the context's stream.
+ * cohort > 0 runs the agents in groups of `cohort` (each group does all n_steps before
+ * the next starts) so a group's tables stay L2-resident; 0 = all agents at once. */
+int grlcu_run(grlcu_ctx *ctx, int64_t n_steps, int32_t cohort);
+int grlcu_sync(grlcu_ctx *ctx);
+
+/* Plugin-facing end-to-end call with HOST buffers: uploads a batch of start states
+ * ([n_agents][S] row-major; every agent begins a new learning episode from its row,
+ * replacing Task::start), runs n_steps agent-steps per agent, downloads the results,
+ * and synchronises.  start_states may be NULL (Philox starts). */
+int grlcu_run_host(grlcu_ctx *ctx, const double *start_states, int64_t n_steps, int32_t cohort,
+                   grlcu_results *results);
+
+/* One replayed agent-step for all agents (see grlcu_replay_in/out). */
+int grlcu_replay_step(grlcu_ctx *ctx, const grlcu_replay_in *in, grlcu_replay_out *out);
+
+int grlcu_get_results(grlcu_ctx *ctx, grlcu_results *results);
+
+/* ParameterizedRepresentation::params()/setParams (representation.h:275-281) and the
+ * raw-double checkpoint format of representation.h:201-263: `memory` doubles. */
+int grlcu_get_table(grlcu_ctx *ctx, int32_t agent, double *out);
+int grlcu_set_table(grlcu_ctx *ctx, int32_t agent, const double *in);
+
+/* Environment state ([S]) and pending action of one agent. */
+int grlcu_get_state(grlcu_ctx *ctx, int32_t agent, double *state, double *action, int32_t *in_episode);
+
+/* Trace capacity (entries) the context allocated per agent. */
+int grlcu_trace_capacity(grlcu_ctx *ctx);
+/* Counters for the roofline: launches of our kernels so far, and kernel name list. */
+int64_t grlcu_launch_count(grlcu_ctx *ctx);
+/* Device time (ms) spent in the fused run kernel since the last call (CUDA events on
+ * the context's stream), and the number of run-kernel launches it covers. */
+int grlcu_run_kernel_time(grlcu_ctx *ctx, double *ms, int64_t *launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -151,3 +151,67 @@ def lib():
                             C.POINTER(C.c_uint64), dp, dp]
     _lib = L
     return L
+
+
+class OracleBatch:
+    """N independent oracle agents (global ids first_id..), stepped in lock-step, with the records
+    of a step gathered into SoA numpy arrays shaped like grlcu_replay_in/out."""
+
+    def __init__(self, cfg, n, first_id=0):
+        import numpy as np
+        self.np = np
+        self.L, self.cfg, self.n = lib(), cfg, n
+        self.S = self.L.orc_state_dims(cfg.dynamics)
+        self.agents = [self.L.orc_create(C.byref(cfg), first_id + i) for i in range(n)]
+        self.recs = [Record() for _ in range(n)]
+
+    def close(self):
+        for a in self.agents:
+            self.L.orc_destroy(a)
+        self.agents = []
+
+    def table(self, i):
+        return self.np.ctypeslib.as_array(self.L.orc_table(self.agents[i]), shape=(self.cfg.memory,))
+
+    def set_hyper(self, alpha, lambda_, epsilon):
+        for i, a in enumerate(self.agents):
+            self.L.orc_set_hyper(a, float(alpha[i]), float(lambda_[i]), float(epsilon[i]))
+
+    def step(self):
+        np, n, S, OBS, T, A = self.np, self.n, self.S, self.cfg.obs_dims, self.cfg.tilings, self.cfg.n_actions
+        for a, r in zip(self.agents, self.recs):
+            self.L.orc_step(a, C.byref(r))
+        R = self.recs
+        f64 = lambda name: np.array([getattr(r, name) for r in R], dtype=np.float64)
+        i32 = lambda name: np.array([getattr(r, name) for r in R], dtype=np.int32)
+        u32 = lambda name: np.array([getattr(r, name) for r in R], dtype=np.uint32)
+        vec = lambda name, k: np.array([list(getattr(r, name))[:k] for r in R], dtype=np.float64).T.copy()
+        d = dict(started=i32("started"), start_state=vec("start_state", S), start_u=f64("start_u"),
+                 start_r_explore=u32("start_r_explore"), start_r_tie=u32("start_r_tie"),
+                 state=vec("state", S), action=f64("action"), test=i32("test"),
+                 obs=vec("obs", OBS), reward=f64("reward"), terminal=i32("terminal"),
+                 u=f64("u"), r_explore=u32("r_explore"), r_tie=u32("r_tie"),
+                 next=vec("next", S), q=vec("q", A), action_index=i32("action_index"),
+                 start_q=vec("start_q", A), start_action_index=i32("start_action_index"),
+                 q_prev=f64("q_prev"), target=f64("target"), delta=f64("delta"),
+                 swept=i32("swept"), trace_len=i32("trace_len"),
+                 episode_done=i32("episode_done"), episode_return=f64("episode_return"))
+        hs = np.zeros((A, T, n), np.uint32)
+        ix = np.zeros((A, T, n), np.uint32)
+        for i, r in enumerate(R):
+            h = np.ctypeslib.as_array(r.hash).reshape(MAX_ACTIONS, MAX_TILINGS)
+            x = np.ctypeslib.as_array(r.index).reshape(MAX_ACTIONS, MAX_TILINGS)
+            hs[:, :, i] = h[:A, :T]
+            ix[:, :, i] = x[:A, :T]
+        d["hash"], d["index"] = hs, ix
+        return d
+
+    def trace(self, cap):
+        """[cap][T][n] newest first, INVALID beyond trace_len (matches grlcu's dump)."""
+        np, T = self.np, self.cfg.tilings
+        out = np.full((cap, T, self.n), INVALID, np.uint32)
+        for i, r in enumerate(self.recs):
+            t = np.ctypeslib.as_array(r.trace_index).reshape(MAX_TRACE, MAX_TILINGS)
+            k = min(r.trace_len, cap)
+            out[:k, :, i] = t[:k, :T]
+        return out

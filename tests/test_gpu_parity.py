@@ -1,0 +1,200 @@
+"""GPU parity tests proper: libgrlcu (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): tile hashes / indices, action choices and trace index sets bit-exact;
+dynamics and Q-values within 1e-9 relative per step (the agent half is in fact bit-exact in FP64 too,
+because it is fed identical inputs and keeps the reference's summation order)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import _oracle as O
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def G():
+    import grl_b200
+    grl_b200.load()
+    return grl_b200
+
+
+def _cfgs(G):
+    return [("pendulum", G.pendulum_config, O.pendulum_config, 65536),
+            ("cart_pole", G.cart_pole_config, O.cart_pole_config, 262144)]
+
+
+def _rel(a, b):
+    return np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)) if a.size else 0.0
+
+
+@pytest.mark.parametrize("which", [0, 1])
+def test_tile_hash_bit_exact(G, orc, which):
+    name, gcfg, ocfg, mem = _cfgs(G)[which]
+    rng = np.random.default_rng(7 + which)
+    cfg = gcfg(memory=mem)
+    dims = cfg.obs_dims + 1
+    n = 20000
+    x = rng.uniform(-30, 30, size=(n, dims))
+    x[: n // 4] *= 1e-3                       # near the origin (negative/positive boundary)
+    x[n // 4: n // 2] = np.round(x[n // 4: n // 2])   # exactly on tile boundaries
+    b = G.Batch(cfg, 1)
+    try:
+        h, idx = b.project(x)
+    finally:
+        b.close()
+    oc = ocfg(memory=mem)
+    dp, u32p = C.POINTER(C.c_double), C.POINTER(C.c_uint32)
+    oh, oi = np.empty(16, np.uint32), np.empty(16, np.uint32)
+    for k in range(n):
+        row = np.ascontiguousarray(x[k])
+        orc.orc_project(oc.resolution, oc.wrapping, dims, 16, mem, row.ctypes.data_as(dp),
+                        oh.ctypes.data_as(u32p), oi.ctypes.data_as(u32p))
+        assert np.array_equal(h[k], oh), (name, k)
+        assert np.array_equal(idx[k], oi), (name, k)
+
+
+@pytest.mark.parametrize("which", [0, 1])
+def test_model_step_within_tolerance(G, orc, which):
+    name, gcfg, ocfg, mem = _cfgs(G)[which]
+    rng = np.random.default_rng(11 + which)
+    cfg, oc = gcfg(memory=1024), ocfg(memory=1024)
+    S = 3 if which == 0 else 5
+    n = 4000
+    st = rng.uniform(-3, 3, size=(n, S))
+    if which == 0:
+        st[:, 0] = rng.uniform(-20, 20, n); st[:, 1] = rng.uniform(-40, 40, n); st[:, 2] = rng.uniform(0, 3.1, n)
+    else:
+        st[:, 0] = rng.uniform(-2.6, 2.6, n); st[:, 1] = rng.uniform(-10, 10, n)
+        st[:, 2] = rng.uniform(-5, 5, n); st[:, 3] = rng.uniform(-15, 15, n); st[:, 4] = rng.uniform(0, 10.2, n)
+    act = rng.choice(np.array(list(cfg.actions)[:3]), n)
+    b = G.Batch(cfg, 1)
+    try:
+        nxt, obs, rew, term = b.model_step(st, act)
+    finally:
+        b.close()
+    dp = C.POINTER(C.c_double)
+    on, oo, orr, ot = np.empty(7), np.empty(8), C.c_double(), C.c_int32()
+    for k in range(n):
+        row = np.ascontiguousarray(st[k])
+        orc.orc_env_step(C.byref(oc), row.ctypes.data_as(dp), float(act[k]), on.ctypes.data_as(dp),
+                         oo.ctypes.data_as(dp), C.byref(orr), C.byref(ot))
+        assert term[k] == ot.value
+        assert _rel(nxt[k], on[:S]) <= RTOL, (name, k, nxt[k], on[:S])
+        assert _rel(obs[k], oo[:cfg.obs_dims]) <= RTOL
+        assert abs(rew[k] - orr.value) <= RTOL * max(abs(orr.value), 1e-300)
+
+
+def test_table_init_bit_exact(G, orc):
+    cfg, oc = G.pendulum_config(memory=4099, seed=5), O.pendulum_config(memory=4099, seed=5)
+    b = G.Batch(cfg, 3, first_agent_id=1000)
+    ob = O.OracleBatch(oc, 3, first_id=1000)
+    try:
+        for i in range(3):
+            assert np.array_equal(b.get_table(i), ob.table(i))
+    finally:
+        b.close(); ob.close()
+
+
+def _replay(G, gcfg, ocfg, n, steps, mem, check_tables=True, **kw):
+    cfg, oc = gcfg(memory=mem, **kw), ocfg(memory=mem, **kw)
+    b = G.Batch(cfg, n)
+    ob = O.OracleBatch(oc, n)
+    mism_actions = 0
+    try:
+        for t in range(steps):
+            d = ob.step()
+            inp = dict(d)
+            inp["force_action"] = np.where(d["action_index"] < 0, 0, d["action_index"]).astype(np.int32)
+            out = b.replay_step(inp)
+            live = d["terminal"] != 2
+            # environment half: 1e-9 relative
+            assert _rel(out["next"], d["next"]) <= RTOL, t
+            assert _rel(out["obs"], d["obs"]) <= RTOL, t
+            assert _rel(out["reward"], d["reward"]) <= RTOL, t
+            assert np.array_equal(out["terminal"], d["terminal"]), t
+            # agent half: integers bit-exact
+            assert np.array_equal(out["hash"][:, :, live], d["hash"][:, :, live]), t
+            assert np.array_equal(out["index"][:, :, live], d["index"][:, :, live]), t
+            assert np.array_equal(out["action_index"], d["action_index"]), t
+            st = d["started"] != 0
+            assert np.array_equal(out["start_action_index"][st], d["start_action_index"][st]), t
+            assert np.array_equal(out["start_q"][:, st], d["start_q"][:, st]), t
+            assert np.array_equal(out["trace_len"], d["trace_len"]), t
+            assert np.array_equal(out["trace_index"], ob.trace(b.trace_cap)), t
+            learn = d["test"] == 0
+            assert np.array_equal(out["swept"][learn], d["swept"][learn]), t
+            # FP of the agent half: identical inputs and order -> identical bits; bar is 1e-9
+            assert _rel(out["q"][:, live], d["q"][:, live]) <= RTOL, t
+            assert np.array_equal(out["q"][:, live], d["q"][:, live]), t
+            for k in ("q_prev", "target", "delta"):
+                assert np.array_equal(out[k][learn], d[k][learn]), (t, k)
+        if check_tables:
+            for i in range(n):
+                assert np.array_equal(b.get_table(i), ob.table(i)), i
+        res = b.results()
+        for i, a in enumerate(ob.agents):
+            s, e, w = C.c_uint64(), C.c_uint64(), C.c_uint64()
+            orc_l = O.lib()
+            orc_l.orc_stats(a, C.byref(s), C.byref(e), C.byref(w), None, None)
+            assert (res["steps"][i], res["episodes"][i], res["swept"][i]) == (s.value, e.value, w.value)
+    finally:
+        b.close(); ob.close()
+    return mism_actions
+
+
+def test_replay_pendulum(G, orc):
+    # 3 learning episodes + part of a 4th incl. a test episode (test_interval=2)
+    _replay(G, G.pendulum_config, O.pendulum_config, n=48, steps=450, mem=65536,
+            randomization=1.0, test_interval=2)
+
+
+def test_replay_pendulum_small_table_collisions(G, orc):
+    # memory 257: many intra-projection and cross-tiling collisions (duplicate indices)
+    _replay(G, G.pendulum_config, O.pendulum_config, n=32, steps=330, mem=257,
+            randomization=1.0, test_interval=-1)
+
+
+def test_replay_cart_pole(G, orc):
+    _replay(G, G.cart_pole_config, O.cart_pole_config, n=32, steps=500, mem=262144,
+            randomization=1.0, test_interval=3, epsilon=0.3)
+
+
+def test_replay_accumulating_and_no_trace(G, orc):
+    _replay(G, G.pendulum_config, O.pendulum_config, n=16, steps=150, mem=8192,
+            randomization=1.0, test_interval=-1, trace=2)
+    _replay(G, G.pendulum_config, O.pendulum_config, n=16, steps=150, mem=8192,
+            randomization=1.0, test_interval=-1, trace=0)
+
+
+def test_free_running_matches_oracle_statistically(G, orc):
+    """Seeded Philox streams on both sides: identical draws; trajectories agree until a last-bit
+    sin/cos difference flips a tile, so compare per-agent learning curves statistically."""
+    n, episodes = 256, 60
+    cfg = G.pendulum_config(memory=65536, randomization=1.0, test_interval=-1)
+    oc = O.pendulum_config(memory=65536, randomization=1.0, test_interval=-1)
+    b = G.Batch(cfg, n)
+    try:
+        b.run(100 * episodes)
+        res = b.results()
+    finally:
+        b.close()
+    assert np.all(res["steps"] == 100 * episodes) and np.all(res["episodes"] == episodes)
+    L = O.lib()
+    orc_ret, orc_last = [], []
+    for i in range(32):
+        a = L.orc_create(C.byref(oc), i)
+        L.orc_run(a, 100 * episodes)
+        lr = C.c_double()
+        L.orc_stats(a, None, None, None, C.byref(lr), None)
+        orc_last.append(lr.value)
+        L.orc_destroy(a)
+    g_mean, o_mean = float(np.mean(res["last_return"])), float(np.mean(orc_last))
+    g_sd = float(np.std(res["last_return"]))
+    # same distribution: means within 4 standard errors of the smaller sample
+    assert abs(g_mean - o_mean) < 4 * g_sd / np.sqrt(32) + 1e-9, (g_mean, o_mean, g_sd)
+    # learning happened: mean return of the summed curve improves on the first episode's level
+    assert g_mean > -4000

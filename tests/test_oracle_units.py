@@ -1,0 +1,90 @@
+"""CPU tests of the oracle's primitives against independent formulations."""
+import ctypes as C
+
+import numpy as np
+
+import _oracle as O
+
+
+def test_hash_matches_independent_murmur2(orc):
+    # GRL's createHashSum == Appleby's MurmurHash2 over the little-endian int bytes with
+    # seed' = 449 ^ n ^ 4n (tile_coding.h:94 xors the COUNT of ints, the original the byte length).
+    rng = np.random.default_rng(3)
+    for n in (1, 3, 4, 6, 7, 9):
+        for _ in range(200):
+            ints = rng.integers(-2**31, 2**31 - 1, size=n, dtype=np.int64).astype(np.int32)
+            h = orc.orc_hash(ints.ctypes.data_as(C.POINTER(C.c_int32)), n)
+            m = orc.orc_murmur2_bytes(ints.ctypes.data_as(C.c_void_p), 4 * n, (449 ^ n ^ (4 * n)) & 0xFFFFFFFF)
+            assert h == m
+
+
+def test_murmur2_python_restatement(orc):
+    def murmur(ints):
+        m, h = 0x5bd1e995, 449 ^ len(ints)
+        for v in ints:
+            k = (int(v) & 0xFFFFFFFF) * m & 0xFFFFFFFF
+            k ^= k >> 24
+            k = k * m & 0xFFFFFFFF
+            h = (h * m & 0xFFFFFFFF) ^ k
+        h ^= h >> 13
+        h = h * m & 0xFFFFFFFF
+        return h ^ (h >> 15)
+    for ints in ([0, 0, 0, 0], [1, -1, 5, 15], [-320, 7, -3, 0], [2**31 - 1, -2**31, 0, 3, 2, 1]):
+        a = np.array(ints, dtype=np.int32)
+        assert orc.orc_hash(a.ctypes.data_as(C.POINTER(C.c_int32)), len(ints)) == murmur(ints)
+
+
+def test_philox_known_answer(orc):
+    # Random123 kat_vectors: philox4x32-10, counter/key all zero and all ones
+    out = (C.c_uint32 * 4)()
+    orc.orc_philox(0, 0, 0, 0, 0, 0, out)
+    assert list(out) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    orc.orc_philox(0xffffffff, 0xffffffff, 0xffffffff, 0xffffffff, 0xffffffff, 0xffffffff, out)
+    assert list(out) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+
+
+def test_projection_wrapping_and_tiling_structure(orc):
+    c = O.pendulum_config(memory=1 << 20)
+    dp, u32p = C.POINTER(C.c_double), C.POINTER(C.c_uint32)
+
+    def proj(x):
+        x = np.array(x, dtype=np.float64)
+        h, i = np.empty(16, np.uint32), np.empty(16, np.uint32)
+        orc.orc_project(c.resolution, c.wrapping, 3, 16, c.memory, x.ctypes.data_as(dp),
+                        h.ctypes.data_as(u32p), i.ctypes.data_as(u32p))
+        return h, i
+    h0, i0 = proj([0.1, 0.5, 0.0])
+    # angle wraps at 6.283: same tiles one period later (wrapping 6.283 * 16/0.31415 = 320 exactly)
+    h1, _ = proj([0.1 + 6.283, 0.5, 0.0])
+    assert np.array_equal(h0, h1)
+    assert np.array_equal(i0, h0 % np.uint32(c.memory))
+    # a tiny move keeps most tilings' tiles, a big one none
+    h2, _ = proj([0.1 + 0.31415 / 16 * 1.01, 0.5, 0.0])
+    assert 1 <= int(np.sum(h0 != h2)) <= 2
+    h3, _ = proj([2.0, -3.0, 3.0])
+    assert int(np.sum(h0 == h3)) == 0
+
+
+def test_rk4_pendulum_energy_and_time(orc):
+    dp = C.POINTER(C.c_double)
+    x = np.array([np.pi, 0.0, 0.0])
+    nxt = np.empty(3)
+    orc.orc_rk4(0, 0.03, 5, x.ctypes.data_as(dp), 0.0, nxt.ctypes.data_as(dp))
+    assert abs(nxt[2] - 0.03) < 1e-15 and nxt[2] != 1.0
+    assert abs(nxt[0] - np.pi) < 1e-9 and abs(nxt[1]) < 1e-6     # hanging equilibrium stays put
+    x = np.array([0.3, 0.0, 0.0])
+    orc.orc_rk4(0, 0.03, 5, x.ctypes.data_as(dp), 3.0, nxt.ctypes.data_as(dp))
+    assert nxt[1] > 0            # positive torque + gravity away from upright accelerate positively
+
+
+def test_trace_length_bound_and_V(orc):
+    """Replacing trace with gamma*lambda = 0.6305 holds <= 9 entries; V <= 16*9."""
+    c = O.pendulum_config(memory=65536, randomization=1.0, test_interval=-1)
+    a = orc.orc_create(C.byref(c), 7)
+    rec = O.Record()
+    mx_len = mx_v = 0
+    for _ in range(600):
+        orc.orc_step(a, C.byref(rec))
+        mx_len, mx_v = max(mx_len, rec.trace_len), max(mx_v, rec.swept)
+    orc.orc_destroy(a)
+    assert mx_len == 9 and 0 < mx_v <= 144
