@@ -149,6 +149,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   p.test_interval = cfg->test_interval;
   p.alpha = cfg->alpha; p.gamma = cfg->gamma; p.lambda = cfg->lambda; p.epsilon = cfg->epsilon;
   p.trace_kind = cfg->trace;
+  p.force_slow = getenv("GRLCU_FORCE_SLOW") ? atoi(getenv("GRLCU_FORCE_SLOW")) : 0;
   p.trace_cap = trace_capacity_for(cfg->gamma * cfg->lambda, cfg->trace);
   if (p.trace_cap < 0 || p.trace_cap > 160)
   {
@@ -167,6 +168,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   if (!r) r = dalloc(c, &p.trace_head, n);
   if (!r) r = dalloc(c, &p.total_decay, n);
   if (!r) r = dalloc(c, &p.flags, n);
+  if (!r) r = dalloc(c, &p.dupmask, n);
   if (!r) r = dalloc(c, &p.act_ctr, n);
   if (!r) r = dalloc(c, &p.test_act_ctr, n);
   if (!r) r = dalloc(c, &p.episode_ctr, n);
@@ -206,7 +208,7 @@ __global__ void k_reset_agents(Params p)
 {
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= p.n) return;
-  p.flags[a] = 0; p.trace_len[a] = 0; p.trace_head[a] = 0; p.total_decay[a] = 1.;
+  p.flags[a] = 0; p.dupmask[a] = 0; p.trace_len[a] = 0; p.trace_head[a] = 0; p.total_decay[a] = 1.;
   p.total_reward[a] = 0; p.action[a] = 0;
   p.act_ctr[a] = 0; p.test_act_ctr[a] = 0; p.episode_ctr[a] = 0; p.tt[a] = 0;
 }

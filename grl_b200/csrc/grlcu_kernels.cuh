@@ -87,19 +87,13 @@ __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag
   uint32_t idx[A][T];
   int term;
   observe<DYN>(ag.x, p.timeout, obs, term);
-  if (!test) { ag.len = 0; ag.total_decay = 1.; }          // predictor finalize -> trace clear
+  if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }   // predictor finalize -> trace clear
   q_values<DYN, T, A>(p, tbl, obs, idx, q, nullptr, p.n, a);
   int ai = sample_action<A>(q, d, ag.epsilon, test);
   ag.action = p.actions[ai];
-#pragma unroll
-  for (int aa = 0; aa < A; ++aa)
-    if (aa == ai)
-    {
-#pragma unroll
-      for (int j = 0; j < T; ++j) ag.pidx[j] = idx[aa][j];
-    }
   ag.total_reward = 0;
   ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
+  set_prev_projection<DYN, T, A>(ag, idx, ai);
   if (o_q)
   {
 #pragma unroll
@@ -183,13 +177,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
 #pragma unroll
       for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
       if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, qp, target, delta, swept);
-#pragma unroll
-      for (int aa = 0; aa < A; ++aa)
-        if (aa == ai)
-        {
-#pragma unroll
-          for (int j = 0; j < T; ++j) ag.pidx[j] = idx[aa][j];
-        }
+      set_prev_projection<DYN, T, A>(ag, idx, ai);
       ag.action = p.actions[ai];
     }
 #pragma unroll
@@ -275,13 +263,7 @@ k_replay(Params p, ReplayIO io)
 #pragma unroll
     for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
     if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, qp, target, delta, swept);
-#pragma unroll
-    for (int aa = 0; aa < A; ++aa)
-      if (aa == ai)
-      {
-#pragma unroll
-        for (int j = 0; j < T; ++j) ag.pidx[j] = idx[aa][j];
-      }
+    set_prev_projection<DYN, T, A>(ag, idx, ai);
     ag.action = p.actions[ai];
     if (test) ag.test_act_ctr++; else ag.act_ctr++;
   }
