@@ -113,6 +113,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
                 e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
   if (device < 0 || device >= ndev) return fail(GRLCU_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
   CU(cudaSetDevice(device));
+  // hashed 8-byte gathers use one 32-byte sector per access: ask L2 not to fetch the neighbour sector
+  cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, getenv("GRLCU_L2_FETCH") ? (size_t)atoi(getenv("GRLCU_L2_FETCH")) : 32);
 
   grlcu_ctx *c = new (std::nothrow) grlcu_ctx();
   if (!c) return fail(GRLCU_ERR_NOMEM, "out of host memory");
@@ -124,7 +126,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   c->d_alpha = c->d_lambda = c->d_epsilon = c->d_start = nullptr;
   c->launches = 0;
   c->block = 64;
-  if (const char *b = getenv("GRLCU_BLOCK")) { int v = atoi(b); if (v >= 32 && v <= 128 && v % 32 == 0) c->block = v; }
+  if (const char *b = getenv("GRLCU_BLOCK")) { int v = atoi(b); if (v >= 32 && v <= kMaxBlock && v % 32 == 0) c->block = v; }
 
   Params &p = c->p;
   memset(&p, 0, sizeof(p));
@@ -145,6 +147,30 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     p.proj.wrap[i] = (int32_t)round(w);
   }
   p.proj.memory = cfg->memory;
+  // Words of the tile hash that do not depend on the state, pre-mixed exactly as createHashSum does
+  // (tile_coding.h:96-106): the action coordinate of tiling j (tile_coding.cpp:122-140) and j itself.
+  {
+    const uint32_t m = 0x5bd1e995u;
+    auto mix = [m](uint32_t k) { k *= m; k ^= k >> 24; k *= m; return k; };
+    const int ia = cfg->obs_dims;                 // the action is the last projector input
+    for (int aa = 0; aa < cfg->n_actions; ++aa)
+    {
+      const int32_t qa = (int32_t)floor(cfg->actions[aa] * p.proj.scaling[ia]);
+      for (int j = 0; j < cfg->tilings; ++j)
+      {
+        const int32_t base = j * (1 + 2 * ia);
+        int32_t r = (qa - base) % cfg->tilings; if (r < 0) r += cfg->tilings;
+        int32_t cc = qa - r;
+        if (p.proj.wrap[ia] != 0) { cc %= p.proj.wrap[ia]; if (cc < 0) cc += p.proj.wrap[ia]; }
+        p.kact[aa][j] = mix((uint32_t)cc);
+      }
+    }
+    for (int j = 0; j < cfg->tilings; ++j) p.kj[j] = mix((uint32_t)j);
+    const uint32_t mem = (uint32_t)cfg->memory;
+    p.mem_mask = (mem & (mem - 1)) == 0 ? mem - 1 : 0;
+    if (mem == 1) p.mem_mask = 0;
+    p.mem_magic = mem > 1 ? 0xFFFFFFFFFFFFFFFFull / mem + 1 : 0;
+  }
   for (int i = 0; i < cfg->n_actions; ++i) p.actions[i] = cfg->actions[i];
   p.test_interval = cfg->test_interval;
   p.alpha = cfg->alpha; p.gamma = cfg->gamma; p.lambda = cfg->lambda; p.epsilon = cfg->epsilon;

@@ -22,6 +22,10 @@ struct Params
   uint64_t seed;
   double   tau; int32_t isteps; double timeout, randomization;
   Projector proj;
+  uint32_t kact[8][16];      // pre-mixed MurmurHash2 word of the action coordinate, per (action, tiling)
+  uint32_t kj[16];           // pre-mixed word of the tiling number
+  uint32_t mem_mask;         // memory-1 if memory is a power of two, else 0
+  uint64_t mem_magic;        // 2^64/memory + 1 (exact 32-bit remainder by multiplication)
   double   actions[8];
   int32_t  test_interval;
   double   alpha, gamma, lambda, epsilon;
@@ -82,7 +86,27 @@ __device__ __forceinline__ int sample_action(const double (&q)[A], const Draws &
   return mai;
 }
 
-// Per-thread view of one agent's persistent state.
+constexpr int kMaxBlock = 64;     // threads per block of the fused kernels (shared index stash is sized for it)
+
+// h % memory (tile_coding.h:118) without a division: mask for powers of two, else the exact
+// multiply-high remainder of Lemire, Kaser & Kurz (2019): r = hi64((M*h mod 2^64) * d), M = 2^64/d + 1.
+__device__ __forceinline__ uint32_t reduce_index(const Params &p, uint32_t h)
+{
+  if (p.mem_mask) return h & p.mem_mask;
+  const uint64_t low = p.mem_magic * (uint64_t)h;
+  return (uint32_t)__umul64hi(low, (uint64_t)(uint32_t)p.proj.memory);
+}
+
+__device__ __forceinline__ uint32_t murmur_mix(uint32_t k)
+{
+  const uint32_t m = 0x5bd1e995u;
+  k *= m; k ^= k >> 24; k *= m;
+  return k;
+}
+
+// Per-thread view of one agent's persistent state.  Only what every step touches lives in
+// registers; episode-level counters and returns are read/updated in global memory when an
+// episode starts or ends (once per ~100 steps).
 template <int DYN, int T>
 struct Agent
 {
@@ -93,10 +117,9 @@ struct Agent
   int32_t  len, head, flags;
   uint32_t dupmask;
   double   total_decay, total_reward;
-  uint64_t act_ctr, test_act_ctr, episode_ctr, tt, ss, swept;
-  uint32_t episodes;
-  double   last_return, last_test_return, return_sum;
-  double   alpha, lambda, epsilon;
+  uint64_t act_ctr;
+  double   alpha, e, epsilon;       // e = gamma*lambda = pow(gamma*lambda, tau) for tau = 1
+  uint32_t dsteps, dswept;          // learning steps / swept indices since load()
 
   __device__ __forceinline__ void load(const Params &p, int a)
   {
@@ -107,12 +130,11 @@ struct Agent
     for (int j = 0; j < T; ++j) pidx[j] = p.prev_idx[(size_t)j * p.n + a];
     len = p.trace_len[a]; head = p.trace_head[a]; flags = p.flags[a]; dupmask = p.dupmask[a];
     total_decay = p.total_decay[a]; total_reward = p.total_reward[a];
-    act_ctr = p.act_ctr[a]; test_act_ctr = p.test_act_ctr[a]; episode_ctr = p.episode_ctr[a];
-    tt = p.tt[a]; ss = p.ss[a]; swept = p.swept[a]; episodes = p.episodes[a];
-    last_return = p.last_return[a]; last_test_return = p.last_test_return[a]; return_sum = p.return_sum[a];
+    act_ctr = p.act_ctr[a];
     alpha = p.alpha_a ? p.alpha_a[a] : p.alpha;
-    lambda = p.lambda_a ? p.lambda_a[a] : p.lambda;
+    e = p.gamma * (p.lambda_a ? p.lambda_a[a] : p.lambda);
     epsilon = p.epsilon_a ? p.epsilon_a[a] : p.epsilon;
+    dsteps = 0; dswept = 0;
   }
   __device__ __forceinline__ void store(const Params &p, int a) const
   {
@@ -123,47 +145,97 @@ struct Agent
     for (int j = 0; j < T; ++j) p.prev_idx[(size_t)j * p.n + a] = pidx[j];
     p.trace_len[a] = len; p.trace_head[a] = head; p.flags[a] = flags; p.dupmask[a] = dupmask;
     p.total_decay[a] = total_decay; p.total_reward[a] = total_reward;
-    p.act_ctr[a] = act_ctr; p.test_act_ctr[a] = test_act_ctr; p.episode_ctr[a] = episode_ctr;
-    p.tt[a] = tt; p.ss[a] = ss; p.swept[a] = swept; p.episodes[a] = episodes;
-    p.last_return[a] = last_return; p.last_test_return[a] = last_test_return; p.return_sum[a] = return_sum;
+    p.act_ctr[a] = act_ctr;
+    p.ss[a] += dsteps; p.swept[a] += dswept;
+  }
+  // online_learning.cpp:223-262 bookkeeping at the end of an episode
+  __device__ __forceinline__ void episode_end(const Params &p, int a, bool test)
+  {
+    flags = 0;
+    p.tt[a] += 1;
+    p.episodes[a] += 1;
+    if (test) p.last_test_return[a] = total_reward;
+    else { p.last_return[a] = total_reward; p.return_sum[a] += total_reward; }
   }
 };
 
-// QPolicy::values (q.cpp:94-107): projections of (obs, a) for every action, then
-// LinearRepresentation::read (linear.cpp:136-184): sequential sum in tiling order, / T.
-// All A*T gathers are issued before the first sum so they are in flight together.
-template <int DYN, int T, int A>
-__device__ __forceinline__ void q_values(const Params &p, const double *tbl,
-                                         const double (&obs)[Dyn<DYN>::OBS],
-                                         uint32_t (&idx)[A][T], double (&q)[A], uint32_t *hash_out, int n, int a)
+// QPolicy::values (q.cpp:94-107): TileCodingProjector::_project of (obs, a) for every action
+// (tile_coding.cpp:103-149) + LinearRepresentation::read (linear.cpp:136-184: sequential sum in tiling
+// order, then / T).  The MurmurHash2 state after the observation coordinates is shared by the A actions
+// (the action coordinate and the tiling number are the last two words and are pre-mixed on the host).
+// Indices go to the shared-memory stash `sid` (element (aa*T+j) at sid[(aa*T+j)*kMaxBlock]).
+// The gathers are issued in two groups (actions 0..A-2, then action A-1 together with the T entries of
+// the previous projection p) to bound the registers holding loads in flight.
+template <int DYN, int T, int A, bool WITH_P>
+__device__ __forceinline__ void q_values(const Params &p, const double *tbl, const double (&obs)[Dyn<DYN>::OBS],
+                                         uint32_t *sid, double (&q)[A], const uint32_t (&pidx)[T],
+                                         double (&vp)[T], uint32_t *hash_out, int n, int a)
 {
-  constexpr int OBS = Dyn<DYN>::OBS, DIMS = OBS + 1;
-  double w[A][T];
+  constexpr int OBS = Dyn<DYN>::OBS;
+  const uint32_t m = 0x5bd1e995u;
+  int32_t qz[OBS];
 #pragma unroll
-  for (int aa = 0; aa < A; ++aa)
+  for (int i = 0; i < OBS; ++i) qz[i] = (int32_t)floor(obs[i] * p.proj.scaling[i]);
+  uint32_t pre[T];
+#pragma unroll
+  for (int j = 0; j < T; ++j)
   {
-    double in[DIMS];
-    int32_t qz[DIMS];
+    uint32_t h = 449u ^ (uint32_t)(OBS + 2);
 #pragma unroll
-    for (int i = 0; i < OBS; ++i) in[i] = obs[i];
-    in[OBS] = p.actions[aa];
-    quantize<DIMS, T>(p.proj, in, qz);
+    for (int i = 0; i < OBS; ++i)
+    {
+      int32_t c = qz[i] - safe_mod(qz[i] - j * (1 + 2 * i), T);
+      if (p.proj.wrap[i] != 0) c = safe_mod(c, p.proj.wrap[i]);
+      h = (h * m) ^ murmur_mix((uint32_t)c);
+    }
+    pre[j] = h;
+  }
+  auto index_of = [&](int aa, int j) -> uint32_t {
+    uint32_t h = (pre[j] * m) ^ p.kact[aa][j];
+    h = (h * m) ^ p.kj[j];
+    h ^= h >> 13; h *= m; h ^= h >> 15;
+    if (hash_out) hash_out[((size_t)aa * T + j) * n + a] = h;
+    return reduce_index(p, h);
+  };
+  {
+    double w[A - 1][T];
+#pragma unroll
+    for (int aa = 0; aa < A - 1; ++aa)
+#pragma unroll
+      for (int j = 0; j < T; ++j)
+      {
+        const uint32_t ix = index_of(aa, j);
+        sid[(aa * T + j) * kMaxBlock] = ix;
+        w[aa][j] = tbl[ix];
+      }
+#pragma unroll
+    for (int aa = 0; aa < A - 1; ++aa)
+    {
+      double r = 0;
+#pragma unroll
+      for (int j = 0; j < T; ++j) r += w[aa][j];
+      q[aa] = r / T;    // clamp to +-DBL_MAX is the identity for finite values (linear.cpp:179-180)
+    }
+  }
+  asm volatile("" ::: "memory");
+  {
+    double w[T];
 #pragma unroll
     for (int j = 0; j < T; ++j)
     {
-      uint32_t h = tile_hash_of<DIMS, T>(p.proj, qz, j);
-      idx[aa][j] = h % (uint32_t)p.proj.memory;
-      if (hash_out) hash_out[((size_t)aa * T + j) * n + a] = h;
-      w[aa][j] = tbl[idx[aa][j]];
+      const uint32_t ix = index_of(A - 1, j);
+      sid[((A - 1) * T + j) * kMaxBlock] = ix;
+      w[j] = tbl[ix];
     }
-  }
+    if (WITH_P)
+    {
 #pragma unroll
-  for (int aa = 0; aa < A; ++aa)
-  {
+      for (int j = 0; j < T; ++j) vp[j] = tbl[pidx[j]];
+    }
     double r = 0;
 #pragma unroll
-    for (int j = 0; j < T; ++j) r += w[aa][j];
-    q[aa] = r / T;      // clamp to +-DBL_MAX is the identity for finite values (linear.cpp:179-180)
+    for (int j = 0; j < T; ++j) r += w[j];
+    q[A - 1] = r / T;
   }
 }
 
@@ -185,17 +257,13 @@ __device__ __forceinline__ bool has_duplicates(const uint32_t (&ix)[T])
   return dup;
 }
 
-// Install the projection chosen by the policy as the agent's (prev_obs, prev_action) projection.
-template <int DYN, int T, int A>
-__device__ __forceinline__ void set_prev_projection(Agent<DYN, T> &ag, const uint32_t (&idx)[A][T], int ai)
+// Install the projection chosen by the policy (read back from the index stash) as the agent's
+// (prev_obs, prev_action) projection.
+template <int DYN, int T>
+__device__ __forceinline__ void set_prev_projection(Agent<DYN, T> &ag, const uint32_t *sid, int ai)
 {
 #pragma unroll
-  for (int aa = 0; aa < A; ++aa)
-    if (aa == ai)
-    {
-#pragma unroll
-      for (int j = 0; j < T; ++j) ag.pidx[j] = idx[aa][j];
-    }
+  for (int j = 0; j < T; ++j) ag.pidx[j] = sid[(ai * T + j) * kMaxBlock];
   ag.flags = (ag.flags & ~8) | (has_duplicates<T>(ag.pidx) ? 8 : 0);
 }
 
@@ -204,10 +272,12 @@ __device__ __forceinline__ void set_prev_projection(Agent<DYN, T> &ag, const uin
 template <int DYN, int T>
 __device__ __forceinline__ void trace_push(const Params &p, Agent<DYN, T> &ag, uint32_t *tr, double e, double dc)
 {
-  const int n = p.n, cap = p.trace_cap;
+  const int cap = p.trace_cap;
+  const size_t n = (size_t)p.n;
   ag.head = ag.head + 1 == cap ? 0 : ag.head + 1;
+  uint32_t *dst = tr + (size_t)ag.head * T * n;
 #pragma unroll
-  for (int j = 0; j < T; ++j) tr[((size_t)ag.head * T + j) * n] = ag.pidx[j];
+  for (int j = 0; j < T; ++j) dst[j * n] = ag.pidx[j];
   ag.len++;
   ag.dupmask = (ag.dupmask << 1) | ((ag.flags & 8) ? 1u : 0u);
   ag.total_decay *= e;
@@ -217,6 +287,7 @@ __device__ __forceinline__ void trace_push(const Params &p, Agent<DYN, T> &ag, u
 // SARSAPredictor::criticize (sarsa.cpp:98-124) with tau = 1:
 //   target = r [+ gamma*Q(s',a')]; delta = target - Q(p); write(p, target, alpha);
 //   update(trace, alpha*delta, gamma*lambda); trace.add(p, gamma*lambda)
+// vp[] holds the table values at p's indices, gathered by the caller before any store of this step.
 //
 // The reference applies every table increment as a sequential read-modify-write (p's T entries, then
 // the trace entries newest to oldest).  Two code paths give bit-identical tables:
@@ -225,20 +296,18 @@ __device__ __forceinline__ void trace_push(const Params &p, Agent<DYN, T> &ag, u
 //  * fast path (replacing trace, no duplicate indices in p or in any live entry): all valid trace
 //    indices are then pairwise distinct (ssub removed every index an older entry shared with a newer
 //    one, projection.h:93-104), so after p's T stores every remaining address gets exactly one
-//    increment and the gathers/scatters are independent: they are issued G entries (G*T loads) at a
-//    time instead of one dependent RMW after another.
+//    increment; the T gathers of an entry are independent and issued together, and ssub is done in the
+//    same pass (same-tiling compare, then a 64-bit Bloom signature of p, then the exact T compares).
 template <int DYN, int T>
-__device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag, double *tbl,
-                                             int a, double reward, bool bootstrap, double q_next,
+__device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag, double *tbl, int a,
+                                             double reward, bool bootstrap, double q_next, const double (&vp)[T],
                                              double &o_qp, double &o_target, double &o_delta, int &o_swept)
 {
-  const int n = p.n, cap = p.trace_cap;
+  const int cap = p.trace_cap;
+  const size_t n = (size_t)p.n;
   uint32_t *tr = p.trace_idx + a;               // element (pos, j) at tr[((size_t)pos*T + j)*n]
   double target = reward;
   if (bootstrap) target += p.gamma * q_next;    // pow(gamma, 1)
-  double vp[T];
-#pragma unroll
-  for (int j = 0; j < T; ++j) vp[j] = tbl[ag.pidx[j]];
   double qp = 0;
 #pragma unroll
   for (int j = 0; j < T; ++j) qp += vp[j];
@@ -246,7 +315,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
   const double delta = target - qp;
   // LinearRepresentation::write (linear.cpp:186-196): delta_w = alpha*(target - read(p))
   const double dw = ag.alpha * (target - qp);
-  const double e = p.gamma * ag.lambda;         // pow(gamma*lambda, 1)
+  const double e = ag.e;
   const double ad = ag.alpha * delta;
   const double dc = p.trace_kind == 1 ? 0.01 : 0.0001;
   const uint32_t live = ag.len >= 32 ? 0xFFFFFFFFu : ((1u << ag.len) - 1u);
@@ -260,47 +329,37 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
     for (int j = 0; j < T; ++j) tbl[ag.pidx[j]] = vp[j] + dw;
     if (p.trace_kind == 1)
     {
-      constexpr int G = 2;
+      uint64_t bloom = 0;
+#pragma unroll
+      for (int j = 0; j < T; ++j) bloom |= 1ull << (ag.pidx[j] & 63u);
       double weight = 1.;
-      for (int k0 = 0; k0 < ag.len; k0 += G)
+      for (int k = 0; k < ag.len; ++k)
       {
-        uint32_t ix[G][T];
-        double v[G][T], inc[G];
-        bool sw[G];
+        uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * n;
+        const bool sw = weight > 0.001;           // representation.h:81
+        const double inc = weight * ad * e;
+        weight *= e;
+        uint32_t ix[T];
+        double v[T];
 #pragma unroll
-        for (int g = 0; g < G; ++g)
+        for (int j = 0; j < T; ++j) ix[j] = ent[j * n];
+#pragma unroll
+        for (int j = 0; j < T; ++j)
+          if (sw && ix[j] != kInvalidIndex) v[j] = tbl[ix[j]];
+#pragma unroll
+        for (int j = 0; j < T; ++j)
         {
-          const int k = k0 + g;
-          const bool in = k < ag.len;
-          const int pos = ring_pos(ag.head, in ? k : 0, cap);
-          sw[g] = in && weight > 0.001;
-          inc[g] = weight * ad * e;
-          weight *= e;
-#pragma unroll
-          for (int j = 0; j < T; ++j) ix[g][j] = in ? tr[((size_t)pos * T + j) * n] : kInvalidIndex;
-        }
-#pragma unroll
-        for (int g = 0; g < G; ++g)
-#pragma unroll
-          for (int j = 0; j < T; ++j)
-            if (sw[g] && ix[g][j] != kInvalidIndex) v[g][j] = tbl[ix[g][j]];
-#pragma unroll
-        for (int g = 0; g < G; ++g)
-        {
-          const int k = k0 + g;
-          const int pos = ring_pos(ag.head, k < ag.len ? k : 0, cap);
-#pragma unroll
-          for (int j = 0; j < T; ++j)
+          const uint32_t x = ix[j];
+          if (x != kInvalidIndex)
           {
-            const uint32_t x = ix[g][j];
-            if (x != kInvalidIndex)
+            if (sw) { tbl[x] = v[j] + inc; ++swept; }
+            bool hit = (x == ag.pidx[j]);                       // same tiling, same tile: the common case
+            if (!hit && ((bloom >> (x & 63u)) & 1ull))
             {
-              if (sw[g]) { tbl[x] = v[g][j] + inc[g]; ++swept; }
-              bool hit = false;                                   // ssub against p (projection.h:93-104)
 #pragma unroll
               for (int jj = 0; jj < T; ++jj) hit |= (x == ag.pidx[jj]);
-              if (hit) tr[((size_t)pos * T + j) * n] = kInvalidIndex;
             }
+            if (hit) ent[j * n] = kInvalidIndex;                // ssub (projection.h:93-104)
           }
         }
       }
@@ -317,11 +376,11 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
       double weight = 1.;
       for (int k = 0; k < ag.len && weight > 0.001; ++k)
       {
-        const int pos = ring_pos(ag.head, k, cap);
+        const uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * n;
         const double inc = weight * ad * e;
         for (int j = 0; j < T; ++j)
         {
-          uint32_t ix = tr[((size_t)pos * T + j) * n];
+          uint32_t ix = ent[j * n];
           if (ix != kInvalidIndex) { tbl[ix] += inc; ++swept; }
         }
         weight *= e;
@@ -331,20 +390,20 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
       if (p.trace_kind == 1)
         for (int k = 0; k < ag.len; ++k)
         {
-          const int pos = ring_pos(ag.head, k, cap);
+          uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * n;
           for (int j = 0; j < T; ++j)
           {
-            uint32_t ix = tr[((size_t)pos * T + j) * n];
+            uint32_t ix = ent[j * n];
             bool hit = false;
 #pragma unroll
             for (int jj = 0; jj < T; ++jj) hit |= (ix == ag.pidx[jj]);
-            if (hit) tr[((size_t)pos * T + j) * n] = kInvalidIndex;
+            if (hit) ent[j * n] = kInvalidIndex;
           }
         }
       trace_push<DYN, T>(p, ag, tr, e, dc);
     }
   }
-  ag.swept += (uint64_t)swept;
+  ag.dswept += (uint32_t)swept;
   o_qp = qp; o_target = target; o_delta = delta; o_swept = swept;
 }
 

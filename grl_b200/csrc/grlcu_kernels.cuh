@@ -76,32 +76,6 @@ __global__ void k_model_step(int64_t n, double tau, int isteps, double timeout, 
   }
 }
 
-// Episode start (online_learning.cpp:160-178): Task::start, observe, TDAgent::start /
-// FixedAgent::start (first act), trace clear.
-template <int DYN, int T, int A>
-__device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag, double *tbl, int a,
-                                              const Draws &d, bool test, double *o_q, int *o_ai)
-{
-  constexpr int OBS = Dyn<DYN>::OBS;
-  double obs[OBS], q[A];
-  uint32_t idx[A][T];
-  int term;
-  observe<DYN>(ag.x, p.timeout, obs, term);
-  if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }   // predictor finalize -> trace clear
-  q_values<DYN, T, A>(p, tbl, obs, idx, q, nullptr, p.n, a);
-  int ai = sample_action<A>(q, d, ag.epsilon, test);
-  ag.action = p.actions[ai];
-  ag.total_reward = 0;
-  ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
-  set_prev_projection<DYN, T, A>(ag, idx, ai);
-  if (o_q)
-  {
-#pragma unroll
-    for (int aa = 0; aa < A; ++aa) o_q[(size_t)aa * p.n + a] = q[aa];
-  }
-  if (o_ai) *o_ai = ai;
-}
-
 __device__ __forceinline__ Draws draws_from(const Philox4 &w)
 {
   Draws d;
@@ -111,15 +85,99 @@ __device__ __forceinline__ Draws draws_from(const Philox4 &w)
   return d;
 }
 
-// Fused K1-K4: each thread owns one agent and runs n_steps iterations of the hot loop with
-// the agent's state in registers; only the hashed table and the trace ring are in memory.
+// Draws of one act(): learning episodes use the agent's STREAM_ACT counter (registers), test
+// episodes the STREAM_TEST_ACT counter kept in global memory (rare).
+template <int DYN, int T>
+__device__ __forceinline__ Draws next_draws(const Params &p, Agent<DYN, T> &ag, int a, uint64_t gid, bool test)
+{
+  if (test)
+  {
+    const uint64_t c = p.test_act_ctr[a];
+    p.test_act_ctr[a] = c + 1;
+    return draws_from(philox_for(p.seed, gid, STREAM_TEST_ACT, c));
+  }
+  return draws_from(philox_for(p.seed, gid, STREAM_ACT, ag.act_ctr++));
+}
+
+// Episode start (online_learning.cpp:160-178): observe the start state, TDAgent::start /
+// FixedAgent::start (trace clear + first act).
 template <int DYN, int T, int A>
-__global__ void __launch_bounds__(128)
+__device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag, double *tbl, uint32_t *sid, int a,
+                                              const Draws &d, bool test, double *o_q, int *o_ai)
+{
+  constexpr int OBS = Dyn<DYN>::OBS;
+  double obs[OBS], q[A], vp[T];
+  int term;
+  observe<DYN>(ag.x, p.timeout, obs, term);
+  if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }   // predictor finalize -> trace clear
+  q_values<DYN, T, A, false>(p, tbl, obs, sid, q, ag.pidx, vp, nullptr, p.n, a);
+  const int ai = sample_action<A>(q, d, ag.epsilon, test);
+  ag.action = p.actions[ai];
+  ag.total_reward = 0;
+  ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
+  set_prev_projection<DYN, T>(ag, sid, ai);
+  if (o_q)
+  {
+#pragma unroll
+    for (int aa = 0; aa < A; ++aa) o_q[(size_t)aa * p.n + a] = q[aa];
+  }
+  if (o_ai) *o_ai = ai;
+}
+
+// The agent half of one step (TDAgent::step / end, td.cpp:63-81; FixedAgent for test episodes).
+// Returns the policy's own action choice (-1 when the observation is absorbing); commits `force`
+// instead when force >= 0 (replay mode).
+template <int DYN, int T, int A>
+__device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, double *tbl, uint32_t *sid, int a,
+                                          const double (&obs)[Dyn<DYN>::OBS], double reward, int terminal, bool test,
+                                          const Draws &d, int force, uint32_t *hash_out, double *o_q,
+                                          double &qp, double &target, double &delta, int &swept)
+{
+  qp = target = delta = 0; swept = 0;
+  double vp[T];
+  if (terminal == 2)
+  {
+    // TDAgent::end (td.cpp:76-81): update without bootstrap
+    if (!test)
+    {
+#pragma unroll
+      for (int j = 0; j < T; ++j) vp[j] = tbl[ag.pidx[j]];
+      sarsa_update<DYN, T>(p, ag, tbl, a, reward, false, 0., vp, qp, target, delta, swept);
+    }
+    return -1;
+  }
+  // TDAgent::step (td.cpp:63-74): act on the new observation, then update with (s,a,r,s',a')
+  double q[A];
+  q_values<DYN, T, A, true>(p, tbl, obs, sid, q, ag.pidx, vp, hash_out, p.n, a);
+  const int own = sample_action<A>(q, d, ag.epsilon, test);
+  const int ai = force >= 0 ? force : own;
+  if (o_q)
+  {
+#pragma unroll
+    for (int aa = 0; aa < A; ++aa) o_q[(size_t)aa * p.n + a] = q[aa];
+  }
+  double qn = q[0];
+#pragma unroll
+  for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
+  if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, vp, qp, target, delta, swept);
+  set_prev_projection<DYN, T>(ag, sid, ai);
+  ag.action = p.actions[ai];
+  return own;
+}
+
+// Fused K1-K4: each thread owns one agent and runs n_steps iterations of the hot loop with the
+// agent's state in registers; only the hashed table and the trace ring are in memory.
+// 64 threads x 7 blocks per SM keeps all 65,536 agents of BASELINE configs[1] resident at once on
+// 148 SMs (448 threads/SM), which bounds the kernel at 144 registers per thread.
+template <int DYN, int T, int A>
+__global__ void __launch_bounds__(kMaxBlock, 7)
 k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
+  __shared__ uint32_t s_idx[A * T][kMaxBlock];
   const int a = agent_begin + blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= agent_end) return;
+  uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
   double *tbl = p.table + (size_t)a * p.proj.memory;
@@ -130,7 +188,9 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
     if (!(ag.flags & 1))
     {
       const bool test = p.test_interval >= 0 &&
-                        ag.tt % (uint64_t)(p.test_interval + 1) == (uint64_t)p.test_interval;
+                        p.tt[a] % (uint64_t)(p.test_interval + 1) == (uint64_t)p.test_interval;
+      const uint64_t ep = p.episode_ctr[a];
+      p.episode_ctr[a] = ep + 1;
       if (p.start_override && (ag.flags & 4))
       {
 #pragma unroll
@@ -138,13 +198,11 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
       }
       else
       {
-        Philox4 w = philox_for(p.seed, gid, STREAM_START, ag.episode_ctr);
+        Philox4 w = philox_for(p.seed, gid, STREAM_START, ep);
         task_start<DYN>(u53(w.w[0], w.w[1]), p.randomization, test ? 1 : 0, ag.x);
       }
-      ag.episode_ctr++;
-      Philox4 w = test ? philox_for(p.seed, gid, STREAM_TEST_ACT, ag.test_act_ctr++)
-                       : philox_for(p.seed, gid, STREAM_ACT, ag.act_ctr++);
-      episode_start<DYN, T, A>(p, ag, tbl, a, draws_from(w), test, nullptr, nullptr);
+      const Draws d = next_draws<DYN, T>(p, ag, a, gid, test);
+      episode_start<DYN, T, A>(p, ag, tbl, sid, a, d, test, nullptr, nullptr);
     }
     const bool test = (ag.flags & 2) != 0;
 
@@ -157,40 +215,16 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
     observe<DYN>(next, p.timeout, obs, terminal);
     const double reward = evaluate<DYN>(ag.x, ag.action, next);
     ag.total_reward += reward;
-
-    double qp, target, delta; int swept;
-    if (terminal == 2)
-    {
-      // TDAgent::end (td.cpp:76-81)
-      if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, false, 0., qp, target, delta, swept);
-    }
-    else
-    {
-      // TDAgent::step (td.cpp:63-74): act, then update
-      double q[A];
-      uint32_t idx[A][T];
-      q_values<DYN, T, A>(p, tbl, obs, idx, q, nullptr, p.n, a);
-      Philox4 w = test ? philox_for(p.seed, gid, STREAM_TEST_ACT, ag.test_act_ctr++)
-                       : philox_for(p.seed, gid, STREAM_ACT, ag.act_ctr++);
-      const int ai = sample_action<A>(q, draws_from(w), ag.epsilon, test);
-      double qn = q[0];
-#pragma unroll
-      for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
-      if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, qp, target, delta, swept);
-      set_prev_projection<DYN, T, A>(ag, idx, ai);
-      ag.action = p.actions[ai];
-    }
 #pragma unroll
     for (int i = 0; i < S; ++i) ag.x[i] = next[i];
-    if (!test) ag.ss++;
-    if (terminal)
-    {
-      ag.flags = 0;
-      ag.tt++;
-      ag.episodes++;
-      if (test) ag.last_test_return = ag.total_reward;
-      else { ag.last_return = ag.total_reward; ag.return_sum += ag.total_reward; }
-    }
+
+    double qp, target, delta; int swept;
+    Draws d; d.u = 1.; d.r_explore = 0; d.r_tie = 0;
+    if (terminal != 2) d = next_draws<DYN, T>(p, ag, a, gid, test);
+    agent_half<DYN, T, A>(p, ag, tbl, sid, a, obs, reward, terminal, test, d, -1, nullptr, nullptr,
+                          qp, target, delta, swept);
+    if (!test) ag.dsteps++;
+    if (terminal) ag.episode_end(p, a, test);
   }
   ag.store(p, a);
 }
@@ -198,13 +232,15 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
 // Replay: one agent-step per agent with states, observations, rewards, draws (and optionally the
 // committed action) fed from outside; emits everything observable for comparison.
 template <int DYN, int T, int A>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(kMaxBlock)
 k_replay(Params p, ReplayIO io)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
+  __shared__ uint32_t s_idx[A * T][kMaxBlock];
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = p.n;
   if (a >= n) return;
+  uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
   double *tbl = p.table + (size_t)a * p.proj.memory;
@@ -216,9 +252,9 @@ k_replay(Params p, ReplayIO io)
     for (int i = 0; i < S; ++i) ag.x[i] = io.start_state[(size_t)i * n + a];
     Draws d; d.u = io.start_u[a]; d.r_explore = io.start_r_explore[a]; d.r_tie = io.start_r_tie[a];
     int ai;
-    episode_start<DYN, T, A>(p, ag, tbl, a, d, test, io.o_start_q, &ai);
+    episode_start<DYN, T, A>(p, ag, tbl, sid, a, d, test, io.o_start_q, &ai);
     if (io.o_start_action_index) io.o_start_action_index[a] = ai;
-    ag.episode_ctr++;
+    p.episode_ctr[a] += 1;
   }
 
   // environment half from the re-fed state and action
@@ -234,6 +270,8 @@ k_replay(Params p, ReplayIO io)
   if (io.o_obs) for (int i = 0; i < OBS; ++i) io.o_obs[(size_t)i * n + a] = obs[i];
   if (io.o_reward) io.o_reward[a] = r_own;
   if (io.o_terminal) io.o_terminal[a] = terminal;
+#pragma unroll
+  for (int i = 0; i < S; ++i) ag.x[i] = next[i];
 
   // agent half on the fed observation / reward / terminal
 #pragma unroll
@@ -241,31 +279,16 @@ k_replay(Params p, ReplayIO io)
   const double reward = io.reward[a];
   terminal = io.terminal[a];
   ag.total_reward += reward;
-  double qp = 0, target = 0, delta = 0; int swept = 0, own = -1;
-  if (terminal == 2)
+  double qp, target, delta; int swept;
+  Draws d; d.u = io.u[a]; d.r_explore = io.r_explore[a]; d.r_tie = io.r_tie[a];
+  const int force = (io.force_action && terminal != 2) ? io.force_action[a] : -1;
+  const int own = agent_half<DYN, T, A>(p, ag, tbl, sid, a, obs, reward, terminal, test, d, force,
+                                        io.o_hash, io.o_q, qp, target, delta, swept);
+  if (terminal != 2)
   {
-    if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, false, 0., qp, target, delta, swept);
-  }
-  else
-  {
-    double q[A];
-    uint32_t idx[A][T];
-    q_values<DYN, T, A>(p, tbl, obs, idx, q, io.o_hash, n, a);
-    Draws d; d.u = io.u[a]; d.r_explore = io.r_explore[a]; d.r_tie = io.r_tie[a];
-    own = sample_action<A>(q, d, ag.epsilon, test);
-    const int ai = io.force_action ? io.force_action[a] : own;
-    for (int aa = 0; aa < A; ++aa)
-    {
-      if (io.o_q) io.o_q[(size_t)aa * n + a] = q[aa];
-      if (io.o_index) for (int j = 0; j < T; ++j) io.o_index[((size_t)aa * T + j) * n + a] = idx[aa][j];
-    }
-    double qn = q[0];
-#pragma unroll
-    for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
-    if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, qp, target, delta, swept);
-    set_prev_projection<DYN, T, A>(ag, idx, ai);
-    ag.action = p.actions[ai];
-    if (test) ag.test_act_ctr++; else ag.act_ctr++;
+    if (io.o_index)
+      for (int k = 0; k < A * T; ++k) io.o_index[(size_t)k * n + a] = sid[k * kMaxBlock];
+    if (test) p.test_act_ctr[a] += 1; else ag.act_ctr++;
   }
   if (io.o_action_index) io.o_action_index[a] = own;
   if (io.o_q_prev) io.o_q_prev[a] = qp;
@@ -281,15 +304,8 @@ k_replay(Params p, ReplayIO io)
         io.o_trace_index[((size_t)k * T + j) * n + a] =
             k < ag.len ? p.trace_idx[((size_t)pos * T + j) * n + a] : kInvalidIndex;
     }
-#pragma unroll
-  for (int i = 0; i < S; ++i) ag.x[i] = next[i];
-  if (!test) ag.ss++;
-  if (terminal)
-  {
-    ag.flags = 0; ag.tt++; ag.episodes++;
-    if (test) ag.last_test_return = ag.total_reward;
-    else { ag.last_return = ag.total_reward; ag.return_sum += ag.total_reward; }
-  }
+  if (!test) ag.dsteps++;
+  if (terminal) ag.episode_end(p, a, test);
   ag.store(p, a);
 }
 
