@@ -318,15 +318,30 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
   const double e = ag.e;
   const double ad = ag.alpha * delta;
   const double dc = p.trace_kind == 1 ? 0.01 : 0.0001;
-  const uint32_t live = ag.len >= 32 ? 0xFFFFFFFFu : ((1u << ag.len) - 1u);
-  const bool fast = !p.force_slow && p.trace_kind != 2 && cap <= 32 && !(ag.flags & 8) &&
-                    (ag.dupmask & live) == 0;
+  const bool fast = !p.force_slow && p.trace_kind != 2 && cap <= 32;
   int swept = 0;
 
   if (fast)
   {
+    if (!(ag.flags & 8))
+    {
 #pragma unroll
-    for (int j = 0; j < T; ++j) tbl[ag.pidx[j]] = vp[j] + dw;
+      for (int j = 0; j < T; ++j) tbl[ag.pidx[j]] = vp[j] + dw;
+    }
+    else
+    {
+      // p holds duplicate indices (hash collision between tilings): the reference adds dw once per
+      // occurrence, one after the other.  The last occurrence's store carries the full sum and lands last.
+#pragma unroll
+      for (int j = 0; j < T; ++j)
+      {
+        double v = vp[j] + dw;
+#pragma unroll
+        for (int jj = 0; jj < j; ++jj)
+          if (ag.pidx[jj] == ag.pidx[j]) v += dw;
+        tbl[ag.pidx[j]] = v;
+      }
+    }
     if (p.trace_kind == 1)
     {
       uint64_t bloom = 0;
@@ -347,12 +362,23 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
         for (int j = 0; j < T; ++j)
           if (sw && ix[j] != kInvalidIndex) v[j] = tbl[ix[j]];
 #pragma unroll
+        for (int j = 0; j < T; ++j) v[j] += inc;
+        if ((ag.dupmask >> k) & 1u)
+        {
+          // duplicate indices inside this entry: one more sequential += inc per earlier occurrence
+#pragma unroll
+          for (int j = T - 1; j > 0; --j)
+#pragma unroll
+            for (int jj = 0; jj < j; ++jj)
+              if (ix[jj] == ix[j] && ix[j] != kInvalidIndex) v[j] += inc;
+        }
+#pragma unroll
         for (int j = 0; j < T; ++j)
         {
           const uint32_t x = ix[j];
           if (x != kInvalidIndex)
           {
-            if (sw) { tbl[x] = v[j] + inc; ++swept; }
+            if (sw) { tbl[x] = v[j]; ++swept; }
             bool hit = (x == ag.pidx[j]);                       // same tiling, same tile: the common case
             if (!hit && ((bloom >> (x & 63u)) & 1ull))
             {
