@@ -176,6 +176,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   p.alpha = cfg->alpha; p.gamma = cfg->gamma; p.lambda = cfg->lambda; p.epsilon = cfg->epsilon;
   p.trace_kind = cfg->trace;
   p.force_slow = getenv("GRLCU_FORCE_SLOW") ? atoi(getenv("GRLCU_FORCE_SLOW")) : 0;
+  p.mode = getenv("GRLCU_MODE") ? atoi(getenv("GRLCU_MODE")) : 0;
   p.trace_cap = trace_capacity_for(cfg->gamma * cfg->lambda, cfg->trace);
   if (p.trace_cap < 0 || p.trace_cap > 160)
   {
@@ -195,6 +196,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   if (!r) r = dalloc(c, &p.total_decay, n);
   if (!r) r = dalloc(c, &p.flags, n);
   if (!r) r = dalloc(c, &p.dupmask, n);
+  if (!r) r = dalloc(c, &p.cache_val, n * T * (size_t)p.trace_cap);
+  if (!r) r = dalloc(c, &p.cache_mask, n * (size_t)p.trace_cap);
   if (!r) r = dalloc(c, &p.act_ctr, n);
   if (!r) r = dalloc(c, &p.test_act_ctr, n);
   if (!r) r = dalloc(c, &p.episode_ctr, n);
@@ -401,7 +404,13 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
     const int grd = (end - begin + c->block - 1) / c->block;
     cudaEvent_t e0 = get_event(c), e1 = get_event(c);
     CU(cudaEventRecord(e0, c->stream));
-#define CALL(D) k_run<D, 16, 3><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps)
+    // the trace value cache applies to the replacing trace (unique owner slot per index)
+    const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 32;
+#define CALL(D)                                                                                    \
+    do {                                                                                           \
+      if (cached) k_run<D, 16, 3, true><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps); \
+      else k_run<D, 16, 3, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps);      \
+    } while (0)
     DISPATCH_DYN(c, CALL);
 #undef CALL
     CU(cudaEventRecord(e1, c->stream));

@@ -39,6 +39,9 @@ struct Params
   int32_t  *flags;            // bit0 in_episode, bit1 test, bit2 start override pending, bit3 prev projection has duplicate indices
   uint32_t *dupmask;          // bit k: trace entry of age k holds duplicate indices
   int32_t  force_slow;        // 1: always take the sequential update path (A/B testing)
+  int32_t  mode;              // 0: trace value cache where eligible, 1: uncached
+  double   *cache_val;        // [cap*T][n] cached trace weights (grlcu_cached.cuh)
+  uint32_t *cache_mask;       // [cap][n] valid bits per trace entry
   uint64_t *act_ctr, *test_act_ctr, *episode_ctr, *tt, *ss, *swept;
   uint32_t *episodes;
   double   *total_reward, *last_return, *last_test_return, *return_sum;
@@ -166,10 +169,10 @@ struct Agent
 // Indices go to the shared-memory stash `sid` (element (aa*T+j) at sid[(aa*T+j)*kMaxBlock]).
 // The gathers are issued in two groups (actions 0..A-2, then action A-1 together with the T entries of
 // the previous projection p) to bound the registers holding loads in flight.
-template <int DYN, int T, int A, bool WITH_P>
+template <int DYN, int T, int A, bool WITH_P, typename Resolve>
 __device__ __forceinline__ void q_values(const Params &p, const double *tbl, const double (&obs)[Dyn<DYN>::OBS],
                                          uint32_t *sid, double (&q)[A], const uint32_t (&pidx)[T],
-                                         double (&vp)[T], uint32_t *hash_out, int n, int a)
+                                         double (&vp)[T], uint32_t *hash_out, int n, int a, Resolve resolve)
 {
   constexpr int OBS = Dyn<DYN>::OBS;
   const uint32_t m = 0x5bd1e995u;
@@ -213,7 +216,7 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
     {
       double r = 0;
 #pragma unroll
-      for (int j = 0; j < T; ++j) r += w[aa][j];
+      for (int j = 0; j < T; ++j) r += resolve(w[aa][j]);
       q[aa] = r / T;    // clamp to +-DBL_MAX is the identity for finite values (linear.cpp:179-180)
     }
   }
@@ -234,7 +237,7 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
     }
     double r = 0;
 #pragma unroll
-    for (int j = 0; j < T; ++j) r += w[j];
+    for (int j = 0; j < T; ++j) r += resolve(w[j]);
     q[A - 1] = r / T;
   }
 }

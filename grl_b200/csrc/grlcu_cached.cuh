@@ -1,0 +1,278 @@
+// grlcu_cached.cuh -- SARSA(lambda) update with the eligibility trace's weights held in a dense
+// per-agent value cache instead of being read-modify-written in the hashed table every step.
+//
+// Why: the reference's trace sweep (representation.h:79-83) does ~100 random 8-byte RMWs per step into a
+// 512 KiB table.  On B200 a random 8-byte RMW over tens of GiB runs at ~15 G/s and a random read at
+// ~36 G/s (tools/randbench.cu, profiles/r01_randbench_*.txt), so the uncached path sits exactly on that
+// ceiling (~1.05e8 agent-steps/s).  A weight that is in the replacing trace is touched every step for up
+// to L steps, so it is kept in cv[slot][agent] (coalesced, streamed) while it is in the trace:
+//
+//   * directory in the table itself: while index x is cached in trace slot s, table[x] holds a NaN-boxed
+//     sentinel {hi = kSentinelHi, lo = s}.  Every table read checks for it and, if present, takes the value
+//     from cv[s].  That resolves Q(s',.), Q(p) and -- because the sentinel names the slot -- also does the
+//     replacing trace's ssub (projection.h:93-104) with no index comparisons at all: the old slot that
+//     holds one of p's indices is exactly the slot its sentinel names.
+//   * replacing trace => a valid index lives in exactly one slot (ssub removed it from all older entries),
+//     so cv[s] is the single copy of table[x]; duplicate indices inside one projection are folded onto
+//     their first occurrence (alias slots), which preserves the reference's sequential += order.
+//   * values return to the table when their entry is popped (trace.h:229-233), when the trace is cleared
+//     (sarsa.cpp:126-132) and when the kernel exits, so between launches the table and the trace ring are
+//     in the plain (uncached) representation the replay kernel and grlcu_get_table use.
+//
+// Every floating-point operation is the one the reference performs on that weight, in the same order:
+// results are bit-identical to the uncached path (tests/test_gpu_cached.py) and hence to the oracle.
+#pragma once
+#include "grlcu_agent.cuh"
+
+namespace grlcu {
+
+constexpr int kSentinelHi = 0x7FF4C0DE;       // signalling-NaN pattern no arithmetic produces
+constexpr uint32_t kAliasBit = 0x80000000u;   // ring value: duplicate of slot (value & 15) of the same entry
+
+__device__ __forceinline__ bool is_sentinel(double v) { return __double2hiint(v) == kSentinelHi; }
+__device__ __forceinline__ int sentinel_slot(double v) { return __double2loint(v); }
+__device__ __forceinline__ double make_sentinel(int slot) { return __hiloint2double(kSentinelHi, slot); }
+
+// Cache geometry: slot = pos*T + j (pos = ring position); cv[slot*n + a]; vmask[pos*n + a] bit j = valid.
+template <int T>
+struct Cache
+{
+  double   *cv;      // + a
+  uint32_t *vmask;   // + a
+  uint32_t *ring;    // trace_idx + a
+  size_t    n;
+  __device__ __forceinline__ double &val(int slot) const { return cv[(size_t)slot * n]; }
+  __device__ __forceinline__ uint32_t &mask(int pos) const { return vmask[(size_t)pos * n]; }
+  __device__ __forceinline__ uint32_t &idx(int pos, int j) const { return ring[((size_t)pos * T + j) * n]; }
+};
+
+// table read through the directory
+template <int T>
+__device__ __forceinline__ double resolve(const Cache<T> &c, double raw)
+{
+  return is_sentinel(raw) ? c.val(sentinel_slot(raw)) : raw;
+}
+
+// Write the cached values of one entry back into the table (plain representation).
+template <int T>
+__device__ __forceinline__ void flush_entry(const Cache<T> &c, double *tbl, int pos)
+{
+  const uint32_t m = c.mask(pos);
+#pragma unroll
+  for (int j = 0; j < T; ++j)
+    if ((m >> j) & 1u) tbl[c.idx(pos, j)] = c.val(pos * T + j);
+}
+
+// Kernel entry: the ring is in the plain representation (kInvalidIndex = invalidated).  Build the valid
+// masks, fold duplicate indices inside an entry onto their first occurrence, pull the cached weights out
+// of the table and leave sentinels behind.
+template <int DYN, int T>
+__device__ __forceinline__ void cache_open(const Params &p, const Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+{
+  for (int k = 0; k < ag.len; ++k)
+  {
+    const int pos = ring_pos(ag.head, k, p.trace_cap);
+    uint32_t ix[T];
+    uint32_t m = 0;
+#pragma unroll
+    for (int j = 0; j < T; ++j) { ix[j] = c.idx(pos, j); if (ix[j] != kInvalidIndex) m |= 1u << j; }
+    if ((ag.dupmask >> k) & 1u)
+    {
+#pragma unroll
+      for (int j = 1; j < T; ++j)
+#pragma unroll
+        for (int jj = j - 1; jj >= 0; --jj)
+          if (((m >> j) & 1u) && ((m >> jj) & 1u) && ix[j] == ix[jj]) { m &= ~(1u << j); c.idx(pos, j) = kAliasBit | (uint32_t)jj; }
+    }
+    c.mask(pos) = m;
+#pragma unroll
+    for (int j = 0; j < T; ++j)
+      if ((m >> j) & 1u)
+      {
+        c.val(pos * T + j) = tbl[ix[j]];
+        tbl[ix[j]] = make_sentinel(pos * T + j);
+      }
+  }
+}
+
+// Kernel exit: back to the plain representation (values in the table, kInvalidIndex in the ring for
+// invalidated slots, alias slots showing the index they duplicate).
+template <int DYN, int T>
+__device__ __forceinline__ void cache_close(const Params &p, const Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+{
+  for (int k = 0; k < ag.len; ++k)
+  {
+    const int pos = ring_pos(ag.head, k, p.trace_cap);
+    const uint32_t m = c.mask(pos);
+#pragma unroll
+    for (int j = 0; j < T; ++j)
+    {
+      const uint32_t x = c.idx(pos, j);
+      if ((m >> j) & 1u) tbl[x] = c.val(pos * T + j);
+      else if (x & kAliasBit)
+      {
+        const int jj = (int)(x & 15u);
+        c.idx(pos, j) = ((m >> jj) & 1u) ? c.idx(pos, jj) : kInvalidIndex;
+      }
+      else c.idx(pos, j) = kInvalidIndex;
+    }
+  }
+}
+
+// trace.clear() (sarsa.cpp:126-132 via TDAgent::start): cached weights go back to the table.
+template <int DYN, int T>
+__device__ __forceinline__ void cache_clear(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+{
+  for (int k = 0; k < ag.len; ++k) flush_entry<T>(c, tbl, ring_pos(ag.head, k, p.trace_cap));
+  ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0;
+}
+
+// SARSAPredictor::criticize (sarsa.cpp:98-124), replacing trace, through the value cache.
+//   rawp[j]: table[pidx[j]] as read before any store of this step (value or sentinel).
+template <int DYN, int T>
+__device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
+                                                    double reward, bool bootstrap, double q_next,
+                                                    const double (&rawp)[T],
+                                                    double &o_qp, double &o_target, double &o_delta, int &o_swept)
+{
+  const int cap = p.trace_cap;
+  double target = reward;
+  if (bootstrap) target += p.gamma * q_next;    // pow(gamma, 1)
+  // read(p): resolve through the directory; remember which old slot holds each index
+  double np[T];
+  int sp[T];
+#pragma unroll
+  for (int j = 0; j < T; ++j)
+  {
+    sp[j] = is_sentinel(rawp[j]) ? sentinel_slot(rawp[j]) : -1;
+    np[j] = sp[j] >= 0 ? c.val(sp[j]) : rawp[j];
+  }
+  double qp = 0;
+#pragma unroll
+  for (int j = 0; j < T; ++j) qp += np[j];
+  qp /= T;
+  const double delta = target - qp;
+  const double dw = ag.alpha * (target - qp);   // linear.cpp:194
+  const double e = ag.e;
+  const double ad = ag.alpha * delta;
+  const double dc = 0.01;
+  const bool pdup = (ag.flags & 8) != 0;
+
+  // write(p): += dw per occurrence, in tiling order.  Duplicates are folded onto the first occurrence.
+  uint32_t owner = 0xFFFFu;                     // bit j: slot j owns its index (first occurrence)
+  if (pdup)
+  {
+#pragma unroll
+    for (int j = 1; j < T; ++j)
+#pragma unroll
+      for (int jj = 0; jj < j; ++jj)
+        if (((owner >> jj) & 1u) && ((owner >> j) & 1u) && ag.pidx[jj] == ag.pidx[j]) owner &= ~(1u << j);
+  }
+#pragma unroll
+  for (int j = 0; j < T; ++j) np[j] += dw;
+  if (pdup)
+  {
+#pragma unroll
+    for (int j = 1; j < T; ++j)
+      if (!((owner >> j) & 1u))
+      {
+#pragma unroll
+        for (int jj = 0; jj < j; ++jj)
+          if (((owner >> jj) & 1u) && ag.pidx[jj] == ag.pidx[j]) np[jj] += dw;
+      }
+  }
+  // indices that an older entry holds: that slot receives p's write now and the sweep's increment below
+#pragma unroll
+  for (int j = 0; j < T; ++j)
+    if (((owner >> j) & 1u) && sp[j] >= 0) c.val(sp[j]) = np[j];
+
+  // update(trace, alpha*delta, gamma*lambda) (representation.h:79-83): newest -> oldest, on the cache
+  int swept = 0;
+  {
+    double weight = 1.;
+    for (int k = 0; k < ag.len && weight > 0.001; ++k)
+    {
+      const int pos = ring_pos(ag.head, k, cap);
+      const double inc = weight * ad * e;
+      weight *= e;
+      const uint32_t m = c.mask(pos);
+      double v[T];
+#pragma unroll
+      for (int j = 0; j < T; ++j)
+        if ((m >> j) & 1u) v[j] = c.val(pos * T + j);
+#pragma unroll
+      for (int j = 0; j < T; ++j) v[j] += inc;
+      swept += __popc(m);
+      if ((ag.dupmask >> k) & 1u)
+      {
+        // alias slots: one more sequential += inc on the slot they duplicate (if it is still valid)
+#pragma unroll
+        for (int j = 1; j < T; ++j)
+        {
+          const uint32_t x = c.idx(pos, j);
+          if (!((m >> j) & 1u) && x != kInvalidIndex && (x & kAliasBit))
+          {
+            const int jj = (int)(x & 15u);
+            if ((m >> jj) & 1u)
+            {
+#pragma unroll
+              for (int t = 0; t < T; ++t) if (t == jj) v[t] += inc;
+              ++swept;
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < T; ++j)
+        if ((m >> j) & 1u) c.val(pos * T + j) = v[j];
+    }
+  }
+
+  // trace.add(p, e) (trace.h:215-234).  ssub: every old slot named by one of p's sentinels is invalidated
+  // and its weight moves into p's new slot.
+#pragma unroll
+  for (int j = 0; j < T; ++j)
+    if (((owner >> j) & 1u) && sp[j] >= 0)
+    {
+      np[j] = c.val(sp[j]);
+      const int pos = sp[j] / T, jj = sp[j] - pos * T;
+      c.mask(pos) &= ~(1u << jj);
+    }
+  if (e < dc) cache_clear<DYN, T>(p, ag, c, tbl);                      // trace.h:220-221
+  // push; then pop while total_decay < 0.01 (flushing what leaves)
+  ag.head = ag.head + 1 == cap ? 0 : ag.head + 1;
+  {
+    const int pos = ag.head;
+#pragma unroll
+    for (int j = 0; j < T; ++j)
+    {
+      uint32_t x = ag.pidx[j];
+      if ((owner >> j) & 1u)
+      {
+        c.val(pos * T + j) = np[j];
+        tbl[x] = make_sentinel(pos * T + j);
+      }
+      else
+      {
+#pragma unroll
+        for (int jj = 0; jj < j; ++jj)
+          if (((owner >> jj) & 1u) && ag.pidx[jj] == ag.pidx[j]) x = kAliasBit | (uint32_t)jj;
+      }
+      c.idx(pos, j) = x;
+    }
+    c.mask(pos) = owner;
+  }
+  ag.len++;
+  ag.dupmask = (ag.dupmask << 1) | (pdup ? 1u : 0u);
+  ag.total_decay *= e;
+  while (ag.total_decay < dc && ag.len > 1)
+  {
+    ag.total_decay /= e;
+    flush_entry<T>(c, tbl, ring_pos(ag.head, ag.len - 1, cap));
+    ag.len--;
+  }
+  ag.dswept += (uint32_t)swept;
+  o_qp = qp; o_target = target; o_delta = delta; o_swept = swept;
+}
+
+}  // namespace grlcu

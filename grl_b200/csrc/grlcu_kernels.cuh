@@ -1,6 +1,7 @@
 // grlcu_kernels.cuh -- __global__ kernels of the batched GRL learning loop (sm_100a).
 #pragma once
 #include "grlcu_agent.cuh"
+#include "grlcu_cached.cuh"
 
 namespace grlcu {
 
@@ -99,18 +100,31 @@ __device__ __forceinline__ Draws next_draws(const Params &p, Agent<DYN, T> &ag, 
   return draws_from(philox_for(p.seed, gid, STREAM_ACT, ag.act_ctr++));
 }
 
+struct NoResolve { __device__ __forceinline__ double operator()(double v) const { return v; } };
+template <int T> struct CacheResolve
+{
+  Cache<T> c;
+  __device__ __forceinline__ double operator()(double v) const { return resolve<T>(c, v); }
+};
+
 // Episode start (online_learning.cpp:160-178): observe the start state, TDAgent::start /
 // FixedAgent::start (trace clear + first act).
-template <int DYN, int T, int A>
-__device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag, double *tbl, uint32_t *sid, int a,
-                                              const Draws &d, bool test, double *o_q, int *o_ai)
+template <int DYN, int T, int A, bool CACHED>
+__device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
+                                              uint32_t *sid, int a, const Draws &d, bool test, double *o_q, int *o_ai)
 {
   constexpr int OBS = Dyn<DYN>::OBS;
   double obs[OBS], q[A], vp[T];
   int term;
   observe<DYN>(ag.x, p.timeout, obs, term);
-  if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }   // predictor finalize -> trace clear
-  q_values<DYN, T, A, false>(p, tbl, obs, sid, q, ag.pidx, vp, nullptr, p.n, a);
+  if (!test)
+  {
+    // predictor finalize -> trace clear
+    if (CACHED) cache_clear<DYN, T>(p, ag, c, tbl);
+    else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
+  }
+  if (CACHED) q_values<DYN, T, A, false>(p, tbl, obs, sid, q, ag.pidx, vp, nullptr, p.n, a, CacheResolve<T>{c});
+  else q_values<DYN, T, A, false>(p, tbl, obs, sid, q, ag.pidx, vp, nullptr, p.n, a, NoResolve());
   const int ai = sample_action<A>(q, d, ag.epsilon, test);
   ag.action = p.actions[ai];
   ag.total_reward = 0;
@@ -127,8 +141,9 @@ __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag
 // The agent half of one step (TDAgent::step / end, td.cpp:63-81; FixedAgent for test episodes).
 // Returns the policy's own action choice (-1 when the observation is absorbing); commits `force`
 // instead when force >= 0 (replay mode).
-template <int DYN, int T, int A>
-__device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, double *tbl, uint32_t *sid, int a,
+template <int DYN, int T, int A, bool CACHED>
+__device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
+                                          uint32_t *sid, int a,
                                           const double (&obs)[Dyn<DYN>::OBS], double reward, int terminal, bool test,
                                           const Draws &d, int force, uint32_t *hash_out, double *o_q,
                                           double &qp, double &target, double &delta, int &swept)
@@ -142,13 +157,15 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, do
     {
 #pragma unroll
       for (int j = 0; j < T; ++j) vp[j] = tbl[ag.pidx[j]];
-      sarsa_update<DYN, T>(p, ag, tbl, a, reward, false, 0., vp, qp, target, delta, swept);
+      if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, tbl, reward, false, 0., vp, qp, target, delta, swept);
+      else sarsa_update<DYN, T>(p, ag, tbl, a, reward, false, 0., vp, qp, target, delta, swept);
     }
     return -1;
   }
   // TDAgent::step (td.cpp:63-74): act on the new observation, then update with (s,a,r,s',a')
   double q[A];
-  q_values<DYN, T, A, true>(p, tbl, obs, sid, q, ag.pidx, vp, hash_out, p.n, a);
+  if (CACHED) q_values<DYN, T, A, true>(p, tbl, obs, sid, q, ag.pidx, vp, hash_out, p.n, a, CacheResolve<T>{c});
+  else q_values<DYN, T, A, true>(p, tbl, obs, sid, q, ag.pidx, vp, hash_out, p.n, a, NoResolve());
   const int own = sample_action<A>(q, d, ag.epsilon, test);
   const int ai = force >= 0 ? force : own;
   if (o_q)
@@ -159,7 +176,11 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, do
   double qn = q[0];
 #pragma unroll
   for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
-  if (!test) sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, vp, qp, target, delta, swept);
+  if (!test)
+  {
+    if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, tbl, reward, true, qn, vp, qp, target, delta, swept);
+    else sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, vp, qp, target, delta, swept);
+  }
   set_prev_projection<DYN, T>(ag, sid, ai);
   ag.action = p.actions[ai];
   return own;
@@ -169,7 +190,7 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, do
 // agent's state in registers; only the hashed table and the trace ring are in memory.
 // 64 threads x 7 blocks per SM keeps all 65,536 agents of BASELINE configs[1] resident at once on
 // 148 SMs (448 threads/SM), which bounds the kernel at 144 registers per thread.
-template <int DYN, int T, int A>
+template <int DYN, int T, int A, bool CACHED>
 __global__ void __launch_bounds__(kMaxBlock, 7)
 k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
 {
@@ -182,6 +203,9 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
   ag.load(p, a);
   double *tbl = p.table + (size_t)a * p.proj.memory;
   const uint64_t gid = (uint64_t)(p.first_id + a);
+  Cache<T> c;
+  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (size_t)p.n;
+  if (CACHED) cache_open<DYN, T>(p, ag, c, tbl);
 
   for (int64_t step = 0; step < n_steps; ++step)
   {
@@ -202,7 +226,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
         task_start<DYN>(u53(w.w[0], w.w[1]), p.randomization, test ? 1 : 0, ag.x);
       }
       const Draws d = next_draws<DYN, T>(p, ag, a, gid, test);
-      episode_start<DYN, T, A>(p, ag, tbl, sid, a, d, test, nullptr, nullptr);
+      episode_start<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, d, test, nullptr, nullptr);
     }
     const bool test = (ag.flags & 2) != 0;
 
@@ -221,11 +245,12 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
     double qp, target, delta; int swept;
     Draws d; d.u = 1.; d.r_explore = 0; d.r_tie = 0;
     if (terminal != 2) d = next_draws<DYN, T>(p, ag, a, gid, test);
-    agent_half<DYN, T, A>(p, ag, tbl, sid, a, obs, reward, terminal, test, d, -1, nullptr, nullptr,
-                          qp, target, delta, swept);
+    agent_half<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, reward, terminal, test, d, -1, nullptr, nullptr,
+                                  qp, target, delta, swept);
     if (!test) ag.dsteps++;
     if (terminal) ag.episode_end(p, a, test);
   }
+  if (CACHED) cache_close<DYN, T>(p, ag, c, tbl);
   ag.store(p, a);
 }
 
@@ -252,7 +277,7 @@ k_replay(Params p, ReplayIO io)
     for (int i = 0; i < S; ++i) ag.x[i] = io.start_state[(size_t)i * n + a];
     Draws d; d.u = io.start_u[a]; d.r_explore = io.start_r_explore[a]; d.r_tie = io.start_r_tie[a];
     int ai;
-    episode_start<DYN, T, A>(p, ag, tbl, sid, a, d, test, io.o_start_q, &ai);
+    episode_start<DYN, T, A, false>(p, ag, Cache<T>(), tbl, sid, a, d, test, io.o_start_q, &ai);
     if (io.o_start_action_index) io.o_start_action_index[a] = ai;
     p.episode_ctr[a] += 1;
   }
@@ -282,7 +307,7 @@ k_replay(Params p, ReplayIO io)
   double qp, target, delta; int swept;
   Draws d; d.u = io.u[a]; d.r_explore = io.r_explore[a]; d.r_tie = io.r_tie[a];
   const int force = (io.force_action && terminal != 2) ? io.force_action[a] : -1;
-  const int own = agent_half<DYN, T, A>(p, ag, tbl, sid, a, obs, reward, terminal, test, d, force,
+  const int own = agent_half<DYN, T, A, false>(p, ag, Cache<T>(), tbl, sid, a, obs, reward, terminal, test, d, force,
                                         io.o_hash, io.o_q, qp, target, delta, swept);
   if (terminal != 2)
   {

@@ -1,0 +1,52 @@
+"""The trace value cache (grlcu_cached.cuh) is an internal optimisation of the fused kernel: it must
+leave tables, traces, counters and returns bit-identical to the uncached path, which the replay tests
+pin to the oracle step by step.  Both paths run the same device dynamics and Philox streams, so every
+bit has to agree, across launch boundaries, test episodes, absorbing ends and index collisions."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(G, mk, mode, n, launches, **kw):
+    os.environ["GRLCU_MODE"] = str(mode)
+    try:
+        b = G.Batch(mk(**kw), n)
+    finally:
+        os.environ.pop("GRLCU_MODE", None)
+    try:
+        for k in launches:
+            b.run(k)
+        res = b.results()
+        tables = np.stack([b.get_table(i) for i in range(n)])
+        states = [b.get_state(i) for i in range(n)]
+    finally:
+        b.close()
+    return res, tables, states
+
+
+@pytest.mark.parametrize("case", [
+    dict(which="pendulum", n=96, memory=65536, launches=[37, 100, 63, 1, 250], test_interval=3),
+    dict(which="pendulum", n=64, memory=257, launches=[150, 75], test_interval=-1),      # heavy collisions
+    dict(which="pendulum", n=64, memory=4099, launches=[220], test_interval=2),          # non power of two
+    dict(which="cart_pole", n=64, memory=262144, launches=[180, 333], test_interval=4, epsilon=0.2),
+    dict(which="cart_pole", n=32, memory=1031, launches=[400], test_interval=-1, epsilon=0.5),
+    dict(which="pendulum", n=32, memory=8192, launches=[130], test_interval=-1, lambda_=0.0),  # decay < 0.01
+    dict(which="pendulum", n=32, memory=8192, launches=[260], test_interval=-1, lambda_=0.9),  # long trace
+])
+def test_cached_equals_uncached(case):
+    import grl_b200 as G
+    case = dict(case)
+    mk = G.pendulum_config if case.pop("which") == "pendulum" else G.cart_pole_config
+    n, launches = case.pop("n"), case.pop("launches")
+    r1, t1, s1 = _run(G, mk, 1, n, launches, randomization=1.0, **case)
+    r0, t0, s0 = _run(G, mk, 0, n, launches, randomization=1.0, **case)
+    assert not np.isnan(t0).any()                      # no directory sentinel left in a table
+    assert np.array_equal(t0, t1)
+    for k in r0:
+        assert np.array_equal(r0[k], r1[k]), k
+    for a, b in zip(s0, s1):
+        assert np.array_equal(a[0], b[0]) and a[1:] == b[1:]
+    assert int(r0["steps"].sum()) > 0 and int(r0["swept"].sum()) >= 0
