@@ -162,7 +162,9 @@ def ours(args):
 
     cfg = grl_b200.pendulum_config(memory=args.memory, randomization=1.0, test_interval=-1)
     stream = torch.cuda.current_stream().cuda_stream
-    batch = grl_b200.Batch(cfg, args.agents, first_agent_id=rank * args.agents, device=local, stream=stream)
+    from grl_b200.dist import shard
+    first_id, _ = shard(rank, world, args.agents)
+    batch = grl_b200.Batch(cfg, args.agents, first_agent_id=first_id, device=local, stream=stream)
     n, S = args.agents, batch.S
     bufs = batch.result_buffers()
 
@@ -210,17 +212,9 @@ def ours(args):
     d2h = n * (8 * 3 + 8 + 4 + 8)
 
     # ---- max over ranks; the only collective: final statistics gather over NCCL
-    t = torch.tensor([dev_ms, e2e_s, kern_ms], dtype=torch.float64, device="cuda")
-    tot = torch.tensor([steps_done, swept], dtype=torch.float64, device="cuda")
-    ret = torch.from_numpy(r1["last_return"]).cuda()
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-        gathered = [torch.empty_like(ret) for _ in range(world)]
-        dist.all_gather(gathered, ret)
-        ret = torch.cat(gathered)
-    dev_ms, e2e_s, kern_ms = [float(x) for x in t.tolist()]
-    steps_all, swept_all = [float(x) for x in tot.tolist()]
+    from grl_b200.dist import finalize
+    (dev_ms, e2e_s, kern_ms), (steps_all, swept_all), ret = finalize(
+        [dev_ms, e2e_s, kern_ms], [steps_done, swept], r1["last_return"], "cuda")
     mean_return = float(ret.mean())
 
     if rank == 0:
