@@ -100,7 +100,7 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_set_hyper", "grlcu_project", "grlcu_model_step", "grlcu_run", "grlcu_sync",
            "grlcu_run_host", "grlcu_replay_step", "grlcu_get_results", "grlcu_get_table",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
-           "grlcu_run_kernel_time"]
+           "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update"]
 
 _lib = None
 
@@ -134,6 +134,9 @@ def load(build=True):
     L.grlcu_launch_count.argtypes = [vp]
     L.grlcu_launch_count.restype = C.c_int64
     L.grlcu_run_kernel_time.argtypes = [vp, _dp, _P(C.c_int64)]
+    L.grlcu_task_start.argtypes = [vp, C.c_int64, C.c_int32, _dp, _dp, _dp, _i32p]
+    L.grlcu_read.argtypes = [vp, C.c_int32, C.c_int32, _u64p, _dp]
+    L.grlcu_update.argtypes = [vp, C.c_int32, C.c_int32, _u64p, C.c_double]
     _lib = L
     return L
 
@@ -192,6 +195,27 @@ class Batch:
         self._chk(self.lib.grlcu_model_step(self.h, n, _ptr(s, _dp), _ptr(a, _dp), _ptr(nxt, _dp), _ptr(obs, _dp),
                                             _ptr(rew, _dp), _ptr(term, _i32p)))
         return nxt, obs, rew, term
+
+    def task_start(self, u, test=0):
+        """Task::start + observe for len(u) episodes: (state [n][S], obs [n][obs_dims], terminal [n])."""
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        n = u.shape[0]
+        st, obs, term = np.empty((n, self.S)), np.empty((n, self.cfg.obs_dims)), np.empty(n, np.int32)
+        self._chk(self.lib.grlcu_task_start(self.h, n, int(test), _ptr(u, _dp), _ptr(st, _dp), _ptr(obs, _dp),
+                                            _ptr(term, _i32p)))
+        return st, obs, term
+
+    def read(self, agent, indices):
+        """LinearRepresentation::read of one projection on one agent's table."""
+        idx = np.ascontiguousarray(indices, dtype=np.uint64)
+        v = C.c_double()
+        self._chk(self.lib.grlcu_read(self.h, int(agent), idx.shape[0], _ptr(idx, _u64p), C.byref(v)))
+        return v.value
+
+    def update(self, agent, indices, delta):
+        """LinearRepresentation::update(projection, delta) on one agent's table."""
+        idx = np.ascontiguousarray(indices, dtype=np.uint64)
+        self._chk(self.lib.grlcu_update(self.h, int(agent), idx.shape[0], _ptr(idx, _u64p), C.c_double(delta)))
 
     def run(self, n_steps, cohort=0):
         self._chk(self.lib.grlcu_run(self.h, n_steps, cohort))

@@ -382,6 +382,108 @@ extern "C" int grlcu_model_step(grlcu_ctx *c, int64_t n, const double *state, co
   return 0;
 }
 
+// ---- one-agent views (L2-signature shims) --------------------------------------------------------
+template <int DYN>
+__global__ void k_task_start(int64_t n, int test, double randomization, double timeout, const double *u,
+                             double *state, double *obs, int32_t *terminal)
+{
+  constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x)
+  {
+    double x[S], o[OBS];
+    int term;
+    task_start<DYN>(u[t], randomization, test, x);
+    observe<DYN>(x, timeout, o, term);
+#pragma unroll
+    for (int i = 0; i < S; ++i) state[t * S + i] = x[i];
+#pragma unroll
+    for (int i = 0; i < OBS; ++i) obs[t * OBS + i] = o[i];
+    if (terminal) terminal[t] = term;
+  }
+}
+
+extern "C" int grlcu_task_start(grlcu_ctx *c, int64_t n, int32_t test, const double *u, double *state, double *obs,
+                                int32_t *terminal)
+{
+  if (!c || n < 0 || !u || !state || !obs) return fail(GRLCU_ERR_ARG, "grlcu_task_start: bad arguments");
+  if (n == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  const int S = c->S, OBS = c->OBS;
+  Scratch s;
+  double *d_u = s.get<double>(n), *d_s = s.get<double>((size_t)n * S), *d_o = s.get<double>((size_t)n * OBS);
+  int32_t *d_t = s.get<int32_t>(n);
+  if (!d_u || !d_s || !d_o || !d_t) return fail(GRLCU_ERR_NOMEM, "grlcu_task_start: out of device memory");
+  CU(cudaMemcpyAsync(d_u, u, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+  const int grd = grid_for(n, 128);
+#define CALL(D) k_task_start<D><<<grd, 128, 0, c->stream>>>(n, test, c->p.randomization, c->p.timeout, d_u, d_s, d_o, d_t)
+  DISPATCH_DYN(c, CALL);
+#undef CALL
+  c->launches++;
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(state, d_s, sizeof(double) * n * S, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(obs, d_o, sizeof(double) * n * OBS, cudaMemcpyDeviceToHost, c->stream));
+  if (terminal) CU(cudaMemcpyAsync(terminal, d_t, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// one thread: the reference's sequential order is the contract (linear.cpp:147-151, 207-215)
+__global__ void k_table_read(const double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double *value, int *bad)
+{
+  double r = 0;
+  for (int i = 0; i < n_idx; ++i)
+  {
+    if (idx[i] >= memory) { *bad = 1; return; }
+    r += tbl[idx[i]];
+  }
+  *value = r / n_idx;
+}
+
+__global__ void k_table_update(double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double delta, int *bad)
+{
+  for (int i = 0; i < n_idx; ++i)
+  {
+    if (idx[i] == ~0ull) continue;                    // IndexProjection::invalid_index()
+    if (idx[i] >= memory) { *bad = 1; return; }
+    tbl[idx[i]] += delta;
+  }
+}
+
+static int table_view(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value, double delta)
+{
+  if (!c || agent < 0 || agent >= c->p.n || n_idx < 1 || !idx) return fail(GRLCU_ERR_ARG, "grlcu_read/update: bad arguments");
+  CU(cudaSetDevice(c->device));
+  Scratch s;
+  uint64_t *d_i = s.get<uint64_t>(n_idx);
+  double *d_v = s.get<double>(1);
+  int *d_bad = s.get<int>(1);
+  if (!d_i || !d_v || !d_bad) return fail(GRLCU_ERR_NOMEM, "grlcu_read/update: out of device memory");
+  CU(cudaMemcpyAsync(d_i, idx, sizeof(uint64_t) * n_idx, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
+  double *tbl = c->p.table + (size_t)agent * c->cfg.memory;
+  if (value) k_table_read<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, d_v, d_bad);
+  else k_table_update<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, delta, d_bad);
+  c->launches++;
+  CU(cudaGetLastError());
+  int bad = 0;
+  CU(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  if (value) CU(cudaMemcpyAsync(value, d_v, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (bad) return fail(GRLCU_ERR_ARG, "grlcu_read/update: index beyond memory (%d entries)", c->cfg.memory);
+  return 0;
+}
+
+extern "C" int grlcu_read(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value)
+{
+  if (!value) return fail(GRLCU_ERR_ARG, "grlcu_read: null output");
+  return table_view(c, agent, n_idx, idx, value, 0.);
+}
+
+extern "C" int grlcu_update(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double delta)
+{
+  return table_view(c, agent, n_idx, idx, nullptr, delta);
+}
+
 // ---- fused run -------------------------------------------------------------------------------
 static cudaEvent_t get_event(grlcu_ctx *c)
 {

@@ -1,0 +1,186 @@
+// grl_experiment.cpp -- experiment/online_learning with an `agents` count: the reference's episode loop
+// (online_learning.cpp:154-279) executed for `agents` independent agents per launch of the fused kernel.
+#include "grl_objects.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <fstream>
+#include <iomanip>
+#include <numeric>
+
+namespace grl {
+
+REGISTER_CONFIGURABLE(OnlineLearningExperiment)
+
+void OnlineLearningExperiment::request(ConfigurationRequest *config)
+{
+  config->push_back(CRP("runs", "Number of separate learning runs to perform", runs_, CRP::Configuration, 1));
+  config->push_back(CRP("run_offset", "Run offset to start at", run_offset_));
+  config->push_back(CRP("trials", "Number of episodes per learning run", trials_));
+  config->push_back(CRP("steps", "Number of steps per learning run", steps_));
+  config->push_back(CRP("rate", "Control step frequency in Hz", rate_, CRP::Online));
+  config->push_back(CRP("test_interval", "Number of episodes in between test trials", test_interval_, CRP::Configuration, -1));
+  config->push_back(CRP("test_trials", "Number of test trials per interval", test_trials_, CRP::Configuration, 1));
+  config->push_back(CRP("output", "Output base filename", output_));
+  config->push_back(CRP("environment", "environment", "Environment in which the agent acts", environment_));
+  config->push_back(CRP("agent", "agent", "Agent", agent_));
+  config->push_back(CRP("test_agent", "agent", "Agent to use in test trials", agent_, true));
+  config->push_back(CRP("load_file", "Load policy filename", load_file_));
+  config->push_back(CRP("save_every", "Save policy to 'output' at the end of event", save_every_));
+  // new on the batched path
+  config->push_back(CRP("agents", "Independent agents learning side by side on the GPU (per run)", agents_, CRP::Configuration, 1));
+  config->push_back(CRP("steps_per_launch", "Agent-steps per agent between two reports", steps_per_launch_, CRP::Configuration, 1));
+  config->push_back(CRP("device", "CUDA device ordinal", device_, CRP::Configuration, 0));
+}
+
+void OnlineLearningExperiment::configure(Configuration &config)
+{
+  agent_ = dynamic_cast<Agent *>(config["agent"].ptr());
+  test_agent_ = dynamic_cast<Agent *>(config["test_agent"].ptr());
+  environment_ = dynamic_cast<Environment *>(config["environment"].ptr());
+  runs_ = config["runs"]; run_offset_ = config["run_offset"]; trials_ = config["trials"]; steps_ = config["steps"];
+  rate_ = config["rate"]; test_interval_ = config["test_interval"]; test_trials_ = config["test_trials"];
+  output_ = config["output"].str(); load_file_ = config["load_file"].str(); save_every_ = config["save_every"].str();
+  agents_ = config["agents"]; steps_per_launch_ = config["steps_per_launch"]; device_ = config["device"];
+  if (runs_ < 1) throw bad_param("experiment/online_learning:runs");
+  if (agents_ < 1) throw bad_param("experiment/online_learning:agents");
+  if (steps_per_launch_ < 1) throw bad_param("experiment/online_learning:steps_per_launch");
+  if (test_trials_ != 1) throw bad_param("experiment/online_learning:test_trials");
+  if (save_every_ != "never" && save_every_ != "run") throw bad_param("experiment/online_learning:save_every");
+  if (test_interval_ >= 0 && !test_agent_) throw bad_param("experiment/online_learning:test_agent");
+}
+
+void OnlineLearningExperiment::reconfigure(const Configuration &config)
+{
+  config.get("rate", rate_);
+  if (config.has("identity")) identity = config["identity"].str();
+}
+
+// Collect the parameters of the four CUDA objects into one grlcu_config (no device needed).
+void OnlineLearningExperiment::assemble()
+{
+  if (assembled_) return;
+  CudaBatchedEnvironment *env = dynamic_cast<CudaBatchedEnvironment *>(environment_);
+  TDAgent *td = dynamic_cast<TDAgent *>(agent_);
+  if (!env) throw Exception(path() + ": environment must be an environment/model/cuda_batched");
+  if (!td || !td->policy) throw Exception(path() + ": agent must be an agent/td with a mapping/policy/discrete/value/q policy");
+  CudaSARSAPredictor *pred = dynamic_cast<CudaSARSAPredictor *>(td->predictor);
+  if (!pred) throw Exception(path() + ": agent predictor must be a predictor/sarsa/cuda");
+  QPolicy *pol = td->policy;
+  CudaTileCodingProjector *proj = dynamic_cast<CudaTileCodingProjector *>(pol->projector);
+  CudaLinearRepresentation *rep = dynamic_cast<CudaLinearRepresentation *>(pol->representation);
+  if (!proj) throw Exception(path() + ": policy projector must be a projector/tile_coding/cuda");
+  if (!rep) throw Exception(path() + ": policy representation must be a representation/linear/cuda");
+  if (pred->projector() != pol->projector || pred->representation() != pol->representation)
+    throw Exception(path() + ": predictor and policy must share one projector and one representation");
+  if (!pol->discretizer || !pol->sampler) throw Exception(path() + ": policy needs a discretizer and a sampler");
+  if (test_agent_ && test_agent_->policy)
+  {
+    QPolicy *tp = test_agent_->policy;
+    if (tp->projector != pol->projector || tp->representation != pol->representation || tp->discretizer != pol->discretizer)
+      throw Exception(path() + ": test_agent must evaluate the learning agent's discretizer, projector and representation");
+    if (!dynamic_cast<GreedySampler *>(tp->sampler)) throw Exception(path() + ": test_agent sampler must be sampler/greedy");
+  }
+  env->contribute(&path_);
+  proj->contribute(&path_);
+  rep->contribute(&path_);
+  pred->contribute(&path_);
+  grlcu_config &c = path_.cfg;
+  c.n_actions = (int)pol->discretizer->values.size();
+  for (int i = 0; i < c.n_actions; ++i) c.actions[i] = pol->discretizer->values[i];
+  c.epsilon = pol->sampler->epsilon;
+  c.test_interval = test_interval_;
+  c.seed = seed;
+  path_.agents = agents_;
+  path_.device = device_;
+  env->attach(&path_); proj->attach(&path_); rep->attach(&path_);
+  assembled_ = true;
+}
+
+std::vector<double> OnlineLearningExperiment::run()
+{
+  assemble();
+  if (!trials_ && !steps_)
+    throw Exception(path() + ": set `trials` or `steps` (the batched experiment does not run until interrupted)");
+  std::vector<double> curve;
+  const size_t n = (size_t)agents_;
+  std::vector<double> last_return(n), last_test(n);
+  std::vector<uint64_t> ss(n);
+  std::vector<uint32_t> episodes(n);
+  grlcu_results res;
+  memset(&res, 0, sizeof(res));
+  res.last_return = last_return.data(); res.last_test_return = last_test.data();
+  res.steps = ss.data(); res.episodes = episodes.data();
+
+  for (int rr = run_offset_; rr < runs_ + run_offset_; ++rr)
+  {
+    // every run is a fresh set of agents with its own Philox streams (global agent ids rr*agents ...)
+    path_.release();
+    path_.first_agent_id = (long long)rr * agents_;
+    grlcu_ctx *ctx = path_.context();
+    std::ofstream ofs;
+    if (!output_.empty())
+    {
+      std::ostringstream oss;
+      oss << output_ << "-" << rr << identity << ".txt";
+      ofs.open(oss.str().c_str());
+    }
+    if (!load_file_.empty())
+    {
+      Configuration loadconfig;
+      loadconfig.set("action", "load");
+      loadconfig.set("file", load_file_ + "-");
+      loadconfig.set("agents", agents_);
+      if (agent_->policy && agent_->policy->representation) agent_->policy->representation->reconfigure(loadconfig);
+    }
+    auto start = std::chrono::steady_clock::now();
+    {
+      std::ostringstream h;
+      h << std::setw(15) << "Trial" << std::setw(15) << "Steps" << std::setw(15) << "Episode reward" << std::setw(15)
+        << "Reward min" << std::setw(15) << "Reward max" << std::setw(15) << "Wall time";
+      INFO(h.str());
+    }
+    for (;;)
+    {
+      CudaPath::check(grlcu_run(ctx, steps_per_launch_, 0));
+      CudaPath::check(grlcu_get_results(ctx, &res));
+      const uint64_t min_ss = *std::min_element(ss.begin(), ss.end());
+      const uint32_t min_tt = *std::min_element(episodes.begin(), episodes.end());
+      const std::vector<double> &r = test_interval_ >= 0 ? last_test : last_return;
+      const double mean = std::accumulate(r.begin(), r.end(), 0.) / n;
+      const double mean_tt = std::accumulate(episodes.begin(), episodes.end(), 0.) / n;
+      const double mean_ss = std::accumulate(ss.begin(), ss.end(), 0.) / n;
+      const double wall = std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::steady_clock::now() - start).count() / 1e6;
+      std::ostringstream oss;
+      oss << std::setw(15) << std::fixed << std::setprecision(1) << mean_tt << std::setw(15) << std::setprecision(0) << mean_ss
+          << std::setw(15) << std::setprecision(3) << mean << std::setw(15) << *std::min_element(r.begin(), r.end())
+          << std::setw(15) << *std::max_element(r.begin(), r.end()) << std::setw(15) << wall;
+      INFO(oss.str());
+      if (ofs.is_open()) ofs << oss.str() << std::endl;
+      curve.push_back(mean);
+      if ((steps_ && min_ss >= (uint64_t)steps_) || (trials_ && min_tt >= (uint32_t)trials_)) break;
+    }
+    if (save_every_ == "run" && !output_.empty())
+    {
+      std::ostringstream oss;
+      oss << output_ << "-run" << rr << "-";
+      Configuration saveconfig;
+      saveconfig.set("action", "save");
+      saveconfig.set("file", oss.str());
+      saveconfig.set("agents", agents_);
+      agent_->policy->representation->reconfigure(saveconfig);
+    }
+    if (ofs.is_open())
+    {
+      // per-agent summary: the batched analogue of one learning curve per `grld` process
+      ofs << "# agent steps episodes last_return last_test_return" << std::endl;
+      for (size_t a = 0; a < n; ++a)
+        ofs << "# " << a << " " << ss[a] << " " << episodes[a] << " " << std::setprecision(17) << last_return[a] << " " << last_test[a] << std::endl;
+    }
+  }
+  return curve;
+}
+
+}  // namespace grl

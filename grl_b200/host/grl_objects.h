@@ -1,0 +1,254 @@
+// grl_objects.h -- the GRL objects on the hot path, as Configurable types.
+//
+// Four new types carry the CUDA path (BASELINE north_star): `environment/model/cuda_batched`,
+// `projector/tile_coding/cuda`, `representation/linear/cuda`, `predictor/sarsa/cuda`.  They accept the
+// same parameters as the reference types they stand in for (modeled.cpp:35-57, tile_coding.cpp:35-43,
+// linear.cpp:35-64, sarsa.cpp:35-46) and keep their role interfaces (one-agent view).  The objects that
+// only carry parameters on this path (model, dynamics, task, agent, policy, discretizer, sampler, trace)
+// are registered under the reference's own type names so the shipped YAML files load with nothing but the
+// four `type:` lines changed.  `experiment/online_learning` gains an `agents` count.
+#pragma once
+#include "grl_host.h"
+#include "../../include/grlcu.h"
+
+namespace grl {
+
+// ---- role interfaces (signatures of the reference's L2 interfaces, one agent per call) -------------------
+typedef Vector Observation;
+typedef Vector Action;
+
+/// Sparse binary feature vector (reference: IndexProjection, projection.h:68-113).
+struct IndexProjection
+{
+  std::vector<size_t> indices;
+  static size_t invalid_index() { return (size_t)-1; }
+};
+typedef std::shared_ptr<IndexProjection> ProjectionPtr;
+
+class Environment : public Configurable
+{
+  public:
+    virtual void start(int test, Observation *obs) = 0;
+    virtual double step(const Action &action, Observation *obs, double *reward, int *terminal) = 0;
+};
+
+class Projector : public Configurable
+{
+  public:
+    virtual ProjectionPtr project(const Vector &in) const = 0;
+};
+
+class Representation : public Configurable
+{
+  public:
+    virtual double read(const ProjectionPtr &projection, Vector *result) const = 0;
+    virtual void write(const ProjectionPtr projection, const Vector &target, const Vector &alpha) = 0;
+    virtual void update(const ProjectionPtr projection, const Vector &delta) = 0;
+};
+
+class Predictor : public Configurable { };
+class Experiment : public Configurable
+{
+  public:
+    virtual std::vector<double> run() = 0;
+};
+
+// ---- parameter carriers registered under the reference's type names ---------------------------------------
+struct Dynamics : Configurable { int id = -1; };
+struct PendulumDynamics : Dynamics { TYPEINFO("dynamics/pendulum", "Pendulum dynamics based on the DCSC MOPS") PendulumDynamics() { id = GRLCU_DYN_PENDULUM; } };
+struct CartPoleDynamics : Dynamics
+{
+  TYPEINFO("dynamics/cart_pole", "Cart-pole dynamics from Barto et al.")
+  CartPoleDynamics() { id = GRLCU_DYN_CART_POLE; }
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+struct CartDoublePoleDynamics : Dynamics { TYPEINFO("dynamics/cart_double_pole", "Cart-double-pole dynamics from Zhong and Rock") CartDoublePoleDynamics() { id = GRLCU_DYN_CART_DOUBLE_POLE; } };
+
+struct DynamicalModel : Configurable
+{
+  TYPEINFO("model/dynamical", "State transition model that integrates equations of motion")
+  double tau = 0.05; int steps = 5; Dynamics *dynamics = nullptr;
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+
+struct Task : Configurable
+{
+  int dynamics_id = -1; double timeout = 0, randomization = 0;
+  Vector observation_min, observation_max, action_min, action_max;
+};
+struct PendulumSwingupTask : Task
+{
+  TYPEINFO("task/pendulum/swingup", "Pendulum swing-up task")
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+struct CartPoleSwingupTask : Task
+{
+  TYPEINFO("task/cart_pole/swingup", "Cart-pole swing-up task")
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+
+struct UniformDiscretizer : Configurable
+{
+  TYPEINFO("discretizer/uniform", "Uniform discretizer")
+  Vector min, max, steps;
+  std::vector<double> values;          // one action dimension on this path
+  void request(const std::string &role, ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+
+struct Sampler : Configurable { double epsilon = 0; };
+struct GreedySampler : Sampler
+{
+  TYPEINFO("sampler/greedy", "Maximum search")
+  void request(ConfigurationRequest *config) override;
+};
+struct EpsilonGreedySampler : Sampler
+{
+  TYPEINFO("sampler/epsilon_greedy", "Maximum search with an epsilon chance of randomness")
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+
+struct Trace : Configurable { int kind = GRLCU_TRACE_NONE; };
+struct ReplacingEnumeratedTrace : Trace { TYPEINFO("trace/enumerated/replacing", "Replacing eligibility trace using a queue of projections") ReplacingEnumeratedTrace() { kind = GRLCU_TRACE_REPLACING; } };
+struct AccumulatingEnumeratedTrace : Trace { TYPEINFO("trace/enumerated/accumulating", "Accumulating eligibility trace using a queue of projections") AccumulatingEnumeratedTrace() { kind = GRLCU_TRACE_ACCUMULATING; } };
+
+class CudaTileCodingProjector;
+class CudaLinearRepresentation;
+class CudaSARSAPredictor;
+
+struct QPolicy : Configurable
+{
+  TYPEINFO("mapping/policy/discrete/value/q", "Q-value based policy")
+  UniformDiscretizer *discretizer = nullptr; Projector *projector = nullptr;
+  Representation *representation = nullptr; Sampler *sampler = nullptr;
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+
+struct Agent : Configurable { QPolicy *policy = nullptr; };
+struct TDAgent : Agent
+{
+  TYPEINFO("agent/td", "Agent that learns from observed state transitions")
+  Predictor *predictor = nullptr;
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+struct FixedAgent : Agent
+{
+  TYPEINFO("agent/fixed", "Fixed-policy agent")
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+
+// ---- the four CUDA types ----------------------------------------------------------------------------------
+/// Shared device context of one experiment: the four objects contribute their parameters, the first
+/// call that needs the device creates it (hard part 8).
+struct CudaPath
+{
+  grlcu_config cfg;
+  grlcu_ctx *ctx = nullptr;
+  int agents = 1, device = 0;
+  long long first_agent_id = 0;
+  bool have_env = false, have_projector = false, have_representation = false, have_predictor = false;
+  CudaPath();
+  ~CudaPath();
+  grlcu_ctx *context();                  ///< creates the context on first use; throws grl::Exception
+  void release();
+  static void check(int rc);             ///< non-zero C-ABI return -> grl::Exception(grlcu_last_error())
+};
+
+class CudaBatchedEnvironment : public Environment
+{
+  public:
+    TYPEINFO("environment/model/cuda_batched", "Modeled environment stepped for many agents at once on a B200")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void reconfigure(const Configuration &config) override;
+    void start(int test, Observation *obs) override;
+    double step(const Action &action, Observation *obs, double *reward, int *terminal) override;
+    void contribute(CudaPath *path) const;
+    void attach(CudaPath *path) { path_ = path; }
+  private:
+    DynamicalModel *model_ = nullptr; Task *task_ = nullptr; int discrete_time_ = 1;
+    CudaPath *path_ = nullptr; Vector state_;
+};
+
+class CudaTileCodingProjector : public Projector
+{
+  public:
+    TYPEINFO("projector/tile_coding/cuda", "Hashed tile coding projector evaluated on a B200")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    ProjectionPtr project(const Vector &in) const override;
+    void contribute(CudaPath *path) const;
+    void attach(CudaPath *path) { path_ = path; }
+    int tilings() const { return tilings_; }
+    int memory() const { return memory_; }
+  private:
+    int tilings_ = 16, memory_ = 8 * 1024 * 1024, safe_ = 0; Vector resolution_, wrapping_;
+    CudaPath *path_ = nullptr;
+};
+
+class CudaLinearRepresentation : public Representation
+{
+  public:
+    TYPEINFO("representation/linear/cuda", "Per-agent hashed linear-in-parameters representation resident in HBM")
+    void request(const std::string &role, ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void reconfigure(const Configuration &config) override;       ///< action = reset | save | load
+    double read(const ProjectionPtr &projection, Vector *result) const override;
+    void write(const ProjectionPtr projection, const Vector &target, const Vector &alpha) override;
+    void update(const ProjectionPtr projection, const Vector &delta) override;
+    void contribute(CudaPath *path) const;
+    void attach(CudaPath *path) { path_ = path; }
+    int memory() const { return memory_; }
+  private:
+    Vector init_min_, init_max_, output_min_, output_max_; int memory_ = 8 * 1024 * 1024, outputs_ = 1, limit_ = 1;
+    CudaPath *path_ = nullptr;
+};
+
+class CudaSARSAPredictor : public Predictor
+{
+  public:
+    TYPEINFO("predictor/sarsa/cuda", "SARSA(lambda) value function predictor fused with the environment step on a B200")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void reconfigure(const Configuration &config) override;
+    void contribute(CudaPath *path) const;
+    Projector *projector() const { return projector_; }
+    Representation *representation() const { return representation_; }
+  private:
+    double alpha_ = 0.2, gamma_ = 0.97, lambda_ = 0.65;
+    Projector *projector_ = nullptr; Representation *representation_ = nullptr; Trace *trace_ = nullptr;
+};
+
+class OnlineLearningExperiment : public Experiment
+{
+  public:
+    TYPEINFO("experiment/online_learning", "Interactive learning experiment, batched over `agents` independent agents")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void reconfigure(const Configuration &config) override;
+    std::vector<double> run() override;
+    /// The C-ABI configuration this experiment resolves to (no device needed): used by --check and tests.
+    const grlcu_config &resolved() { assemble(); return path_.cfg; }
+    int agents() const { return agents_; }
+    CudaPath &cudaPath() { return path_; }
+    unsigned long long seed = 1;
+    std::string identity;
+  private:
+    void assemble();
+    int runs_ = 1, run_offset_ = 0, trials_ = 0, steps_ = 0, rate_ = 0, test_interval_ = -1, test_trials_ = 1;
+    int agents_ = 1, steps_per_launch_ = 100, device_ = 0;
+    std::string output_, load_file_, save_every_ = "never";
+    Environment *environment_ = nullptr; Agent *agent_ = nullptr, *test_agent_ = nullptr;
+    CudaPath path_;
+    bool assembled_ = false;
+};
+
+}  // namespace grl

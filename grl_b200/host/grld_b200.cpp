@@ -1,0 +1,75 @@
+// grld_b200 -- deployer for the batched CUDA path, command-line compatible with the reference's grld
+// (base/src/deployer.cpp:35-150): grld_b200 [-v] [-s seed] [-c] <yaml file>.
+//   -s seed   Philox seed of every agent stream (the reference seeds srand48 with it)
+//   -v        more log output (repeatable)
+//   -c        check only: load, instantiate and print the resolved C-ABI configuration as JSON; no GPU needed
+#include "grl_objects.h"
+
+#include <cstdlib>
+#include <cstring>
+#include <unistd.h>
+
+using namespace grl;
+
+static void print_config_json(const grlcu_config &c, int agents)
+{
+  auto vec = [](const double *v, int n) { std::string s = "["; char b[64]; for (int i = 0; i < n; ++i) { snprintf(b, sizeof(b), "%s%.17g", i ? ", " : "", v[i]); s += b; } return s + "]"; };
+  const int dims = c.obs_dims + 1;
+  printf("{\"agents\": %d, \"dynamics\": %d, \"integration_steps\": %d, \"control_step\": %.17g, \"timeout\": %.17g, "
+         "\"randomization\": %.17g, \"tilings\": %d, \"memory\": %d, \"obs_dims\": %d, \"n_actions\": %d, "
+         "\"resolution\": %s, \"wrapping\": %s, \"actions\": %s, \"alpha\": %.17g, \"gamma\": %.17g, \"lambda\": %.17g, "
+         "\"epsilon\": %.17g, \"trace\": %d, \"test_interval\": %d, \"init_min\": %.17g, \"init_max\": %.17g, \"seed\": %llu, \"algo\": %d}\n",
+         agents, c.dynamics, c.integration_steps, c.control_step, c.timeout, c.randomization, c.tilings, c.memory, c.obs_dims,
+         c.n_actions, vec(c.resolution, dims).c_str(), vec(c.wrapping, dims).c_str(), vec(c.actions, c.n_actions).c_str(),
+         c.alpha, c.gamma, c.lambda, c.epsilon, c.trace, c.test_interval, c.init_min, c.init_max, (unsigned long long)c.seed, c.algo);
+}
+
+int main(int argc, char **argv)
+{
+  unsigned long long seed = 1;
+  bool check = false;
+  int c;
+  while ((c = getopt(argc, argv, "vcs:")) != -1)
+    switch (c)
+    {
+      case 'v': grl_log_verbosity__++; break;
+      case 'c': check = true; break;
+      case 's': seed = strtoull(optarg, nullptr, 10); break;
+      default: return 1;
+    }
+  if (optind > argc - 1)
+  {
+    ERROR("Usage: " << std::endl << "  " << argv[0] << " [-v] [-c] [-s seed] <yaml file>");
+    return 1;
+  }
+  if (check && grl_log_verbosity__ == 3) grl_log_verbosity__ = 1;     // keep stdout to the JSON line
+  try
+  {
+    NOTICE("Loading configuration from '" << argv[optind] << "'");
+    std::shared_ptr<YamlNode> doc = loadYAMLFile(argv[optind]);
+    Configurator configurator;
+    NOTICE("Instantiating configuration");
+    configurator.instantiate(*doc);
+    OnlineLearningExperiment *experiment = dynamic_cast<OnlineLearningExperiment *>(configurator.object("experiment"));
+    if (!experiment)
+    {
+      ERROR("YAML configuration does not specify an experiment");
+      return 1;
+    }
+    experiment->seed = seed;
+    if (check)
+    {
+      print_config_json(experiment->resolved(), experiment->agents());
+      return 0;
+    }
+    NOTICE("Starting experiment");
+    experiment->run();
+    NOTICE("Exiting");
+  }
+  catch (Exception &e)
+  {
+    ERROR(e.what());
+    return 1;
+  }
+  return 0;
+}

@@ -151,6 +151,19 @@ int grlcu_project(grlcu_ctx *ctx, int64_t n, const double *in, uint32_t *hash, u
 int grlcu_model_step(grlcu_ctx *ctx, int64_t n, const double *state, const double *action,
                      double *next, double *obs, double *reward, int32_t *terminal);
 
+/* Task::start + Task::observe for n independent episodes (pendulum.cpp:97-121, cart_pole.cpp:155-190):
+ * u[n] are the uniform draws the reference takes from RandGen::get() (consumed even when the
+ * randomization is 0).  state: [n][S] row-major; obs: [n][obs_dims]; terminal may be NULL. */
+int grlcu_task_start(grlcu_ctx *ctx, int64_t n, int32_t test, const double *u, double *state, double *obs,
+                     int32_t *terminal);
+
+/* One-agent views of the representation, for the L2-signature shims:
+ * LinearRepresentation::read (linear.cpp:136-184): value = (sum of table[idx[i]], in order) / n_idx;
+ * LinearRepresentation::update(projection, delta) (linear.cpp:198-216): table[idx[i]] += delta for
+ * every idx[i] != (uint64_t)-1, sequentially (duplicates accumulate). */
+int grlcu_read(grlcu_ctx *ctx, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value);
+int grlcu_update(grlcu_ctx *ctx, int32_t agent, int32_t n_idx, const uint64_t *idx, double delta);
+
 /* Fused K1-K4: n_steps iterations of online_learning.cpp:186-221 for every agent
  * (episode start/end handled on device).  Asynchronous on the context's stream.
  * cohort > 0 runs the agents in groups of `cohort` (each group does all n_steps before

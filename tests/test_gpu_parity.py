@@ -198,3 +198,50 @@ def test_free_running_matches_oracle_statistically(G, orc):
     assert abs(g_mean - o_mean) < 4 * g_sd / np.sqrt(32) + 1e-9, (g_mean, o_mean, g_sd)
     # learning happened: mean return of the summed curve improves on the first episode's level
     assert g_mean > -4000
+
+
+def test_one_agent_views(G, orc):
+    """grlcu_task_start / grlcu_read / grlcu_update: the single-agent views the L2-signature shims use."""
+    for name, gcfg, ocfg, mem in _cfgs(G):
+        cfg = gcfg(memory=4096, randomization=1.0)
+        oc = ocfg(memory=4096, randomization=1.0)
+        b = G.Batch(cfg, 3)
+        try:
+            rng = np.random.default_rng(5)
+            u = rng.uniform(0, 1, 64)
+            st, obs, term = b.task_start(u, test=0)
+            st_t, obs_t, _ = b.task_start(u, test=1)
+            S = b.S
+            # Task::start (pendulum.cpp:97-105, cart_pole.cpp:155-166): the randomised coordinate only
+            k = 0 if cfg.dynamics == 0 else 1
+            want = np.pi + (u * 2 * np.pi if cfg.dynamics == 0 else (0.1 * u - 0.05))
+            assert np.array_equal(st[:, k], want), name
+            assert np.array_equal(st_t[:, k], np.full(64, np.pi)), name          # test episodes are not randomised
+            mask = np.ones(S, bool); mask[k] = False
+            assert not st[:, mask].any()
+            dp, i32p = C.POINTER(C.c_double), C.POINTER(C.c_int32)
+            for i in range(64):
+                o = np.empty(8); t = C.c_int32()
+                row = np.ascontiguousarray(np.concatenate([st[i], np.zeros(8 - S)]))
+                orc.orc_observe(C.byref(oc), row.ctypes.data_as(dp), o.ctypes.data_as(dp), C.byref(t))
+                assert np.allclose(obs[i], o[:cfg.obs_dims], rtol=1e-12, atol=0) and term[i] == t.value
+            # read / update on agent 1's table, duplicates and an invalidated index included
+            tbl = b.get_table(1)
+            idx = rng.integers(0, 4096, 16).astype(np.uint64)
+            idx[5] = idx[2]
+            want = 0.0
+            for x in idx:
+                want += tbl[int(x)]
+            assert b.read(1, idx) == want / 16
+            upd = idx.copy(); upd[7] = np.uint64(0xFFFFFFFFFFFFFFFF)
+            b.update(1, upd, 0.125)
+            ref = tbl.copy()
+            for x in upd:
+                if x != np.uint64(0xFFFFFFFFFFFFFFFF):
+                    ref[int(x)] += 0.125
+            assert np.array_equal(b.get_table(1), ref)
+            assert np.array_equal(b.get_table(0), b.get_table(0)) and not np.array_equal(b.get_table(0), ref)
+            with pytest.raises(G.GrlcuError):
+                b.read(1, np.array([4096], np.uint64))
+        finally:
+            b.close()

@@ -1,0 +1,136 @@
+"""The Configurable shims (grl_b200/host): YAML -> object tree -> grlcu_config, error behaviour, and (GPU) that
+grld_b200 driving the C ABI from C++ gives the same per-agent results as the ctypes harness."""
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "grl_b200", "host")
+GRLD = os.path.join(HOST, "grld_b200")
+REF_CFG = "/root/reference/cfg"
+
+
+@pytest.fixture(scope="module")
+def grld():
+    from grl_b200 import build
+    build.build()
+    subprocess.run(["make", "-s"], cwd=HOST, check=True)
+    return GRLD
+
+
+def check(grld, path, *extra):
+    out = subprocess.run([grld, "-c", *extra, path], capture_output=True, text=True)
+    return out.returncode, out.stdout, out.stderr
+
+
+def test_shipped_configs_resolve_to_the_harness_configs(grld):
+    import grl_b200
+    for yaml, mk, agents in (("cfg/pendulum/sarsa_tc_cuda.yaml", grl_b200.pendulum_config, 65536),
+                             ("cfg/cart_pole/sarsa_tc_cuda.yaml", grl_b200.cart_pole_config, 32768)):
+        rc, out, err = check(grld, os.path.join(ROOT, yaml))
+        assert rc == 0, err
+        got = json.loads(out)
+        want = mk(memory=got["memory"], randomization=1.0, test_interval=got["test_interval"])
+        assert got["agents"] == agents
+        for k in ("dynamics", "integration_steps", "control_step", "timeout", "randomization", "tilings", "memory",
+                  "obs_dims", "n_actions", "alpha", "gamma", "epsilon", "trace", "init_min", "init_max", "seed", "algo"):
+            assert got[k] == getattr(want, k), k
+        assert got["lambda"] == want.lambda_
+        dims = got["obs_dims"] + 1
+        assert got["resolution"] == list(want.resolution)[:dims]
+        assert got["wrapping"] == list(want.wrapping)[:dims]
+        assert got["actions"] == list(want.actions)[:3]
+
+
+def swap_types(text):
+    """The only edit a GRL user makes to an existing YAML: the four type names (+ a table size that fits)."""
+    text = text.replace("type: environment/modeled", "type: environment/model/cuda_batched")
+    text = re.sub(r"type: projector/tile_coding\b", "type: projector/tile_coding/cuda", text)
+    text = text.replace("type: representation/parameterized/linear", "type: representation/linear/cuda")
+    text = text.replace("type: predictor/critic/sarsa", "type: predictor/sarsa/cuda")
+    return text
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_CFG), reason="reference tree not present (GPU box)")
+@pytest.mark.parametrize("name,dyn,mem", [("pendulum/sarsa_tc.yaml", 0, 8388608), ("cart_pole/sarsa.yaml", 1, 67108864)])
+def test_reference_yaml_loads_with_only_the_type_names_swapped(grld, tmp_path, name, dyn, mem):
+    src = open(os.path.join(REF_CFG, name)).read()
+    dst = tmp_path / "swapped.yaml"
+    dst.write_text(swap_types(src))
+    rc, out, err = check(grld, str(dst), "-s", "7")
+    assert rc == 0, err
+    got = json.loads(out)
+    assert got["dynamics"] == dyn and got["memory"] == mem and got["seed"] == 7
+    assert got["test_interval"] == 10 and got["trace"] == 1 and got["agents"] == 1
+    assert got["actions"] == ([-3.0, 0.0, 3.0] if dyn == 0 else [-15.0, 0.0, 15.0])   # discretizer via task/action_min,max
+
+
+def test_error_behaviour(grld, tmp_path):
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
+    cases = {
+        "type: projector/tile_coding/cuda": ("type: projector/tile_coding", "Unknown object type"),
+        "wrapping: [6.283, 0, 0]": ("wrapping: [6.0, 0, 0]", "projector/tile_coding:wrapping"),
+        "memory: experiment/agent/policy/projector/memory": ("memory: 1024", "representation/linear/cuda:memory"),
+        "type: trace/enumerated/replacing": ("type: enumerated/nonesuch", "Unknown object type"),
+        "tilings: 16": ("tilings: 8", "projector/tile_coding/cuda:tilings"),
+        "projector: experiment/agent/policy/projector": ("projector: experiment/agent/policy/nothing", "does not name an object"),
+    }
+    for old, (new, msg) in cases.items():
+        assert old in base
+        p = tmp_path / "bad.yaml"
+        p.write_text(base.replace(old, new, 1))
+        rc, out, err = check(grld, str(p))
+        assert rc == 1 and msg in err, (old, err)
+    # unique type suffixes are accepted (configurable.cpp:106-125)
+    p = tmp_path / "suffix.yaml"
+    p.write_text(base.replace("type: trace/enumerated/replacing", "type: enumerated/accumulating"))
+    rc, out, err = check(grld, str(p))
+    assert rc == 0 and json.loads(out)["trace"] == 2
+
+
+def test_run_without_gpu_fails_loudly(grld):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    out = subprocess.run([grld, os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")], capture_output=True, text=True)
+    assert out.returncode == 1 and "no CPU fallback" in out.stderr
+
+
+@pytest.mark.gpu
+def test_grld_matches_ctypes_harness(grld, tmp_path):
+    import grl_b200
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
+    y = base.replace("agents: 65536", "agents: 96").replace("steps: 10000", "steps: 700") \
+            .replace("memory: 65536", "memory: 4096").replace("test_interval: -1", "test_interval: 2") \
+            .replace("  runs: 1", "  runs: 1\n  output: %s\n  save_every: run" % (tmp_path / "out"))
+    y = y.replace("      trace:\n        type: trace/enumerated/replacing",
+                  "      trace:\n        type: trace/enumerated/replacing\n  test_agent:\n    type: agent/fixed\n    policy:\n"
+                  "      type: mapping/policy/discrete/value/q\n      discretizer: experiment/agent/policy/discretizer\n"
+                  "      projector: experiment/agent/policy/projector\n      representation: experiment/agent/policy/representation\n"
+                  "      sampler:\n        type: sampler/greedy")
+    p = tmp_path / "small.yaml"
+    p.write_text(y)
+    out = subprocess.run([grld, "-s", "3", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    rows = [l.split() for l in open(str(tmp_path / "out") + "-0.txt") if l.startswith("# ") and l[2].isdigit()]
+    assert len(rows) == 96
+    cfg = grl_b200.pendulum_config(memory=4096, randomization=1.0, test_interval=2, seed=3)
+    b = grl_b200.Batch(cfg, 96)
+    launches = 0
+    while True:
+        b.run(100)
+        launches += 1
+        r = b.results()
+        if r["steps"].min() >= 700:
+            break
+    for a, row in enumerate(rows):
+        assert int(row[2]) == r["steps"][a] and int(row[3]) == r["episodes"][a]
+        assert float(row[4]) == r["last_return"][a] and float(row[5]) == r["last_test_return"][a]
+    # checkpoint in the reference's format (representation.h:201-263): raw doubles, path-derived name
+    ck = np.fromfile(str(tmp_path / "out") + "-run0-experiment_agent_policy_representation.dat", dtype=np.float64)
+    assert np.array_equal(ck, b.get_table(0))
+    b.close()
