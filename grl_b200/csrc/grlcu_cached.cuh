@@ -109,7 +109,7 @@ __device__ __forceinline__ void cache_close(const Params &p, const Agent<DYN, T>
     {
       const uint32_t x = c.idx(pos, j);
       if ((m >> j) & 1u) tbl[x] = c.val(pos * T + j);
-      else if (x & kAliasBit)
+      else if (x != kInvalidIndex && (x & kAliasBit))
       {
         const int jj = (int)(x & 15u);
         c.idx(pos, j) = ((m >> jj) & 1u) ? c.idx(pos, jj) : kInvalidIndex;
