@@ -71,6 +71,18 @@ def cart_pole_config(memory=262144, **kw):
     return _fill(c, **kw)
 
 
+def cart_double_pole_ac_config(memory=131072, **kw):
+    """cfg/cart_double_pole/ac.yaml of the reference (actor-critic, two tile-coded tables per agent)."""
+    c = Config()
+    res = [2.5, 0.0785375, 0.0785375, 2.5, 0.785375, 0.785375]
+    _fill(c, dynamics=DYN_CART_DOUBLE_POLE, integration_steps=5, control_step=0.05, timeout=4.99, randomization=0.0,
+          tilings=16, memory=memory, obs_dims=6, n_actions=0, resolution=res, actor_resolution=res,
+          alpha=0.2, gamma=0.97, lambda_=0.65, epsilon=0.0, trace=TRACE_REPLACING, test_interval=10,
+          init_min=0.0, init_max=1.0, seed=1, algo=ALGO_AC,
+          sigma=5.0, actor_alpha=0.01, action_min=-20.0, action_max=20.0)
+    return _fill(c, **kw)
+
+
 _P = C.POINTER
 _dp, _u32p, _i32p, _u64p = _P(C.c_double), _P(C.c_uint32), _P(C.c_int32), _P(C.c_uint64)
 
@@ -100,7 +112,8 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_set_hyper", "grlcu_project", "grlcu_model_step", "grlcu_run", "grlcu_sync",
            "grlcu_run_host", "grlcu_replay_step", "grlcu_get_results", "grlcu_get_table",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
-           "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update"]
+           "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update",
+           "grlcu_get_actor_table", "grlcu_set_actor_table"]
 
 _lib = None
 
@@ -129,6 +142,8 @@ def load(build=True):
     L.grlcu_get_results.argtypes = [vp, _P(Results)]
     L.grlcu_get_table.argtypes = [vp, C.c_int32, _dp]
     L.grlcu_set_table.argtypes = [vp, C.c_int32, _dp]
+    L.grlcu_get_actor_table.argtypes = [vp, C.c_int32, _dp]
+    L.grlcu_set_actor_table.argtypes = [vp, C.c_int32, _dp]
     L.grlcu_get_state.argtypes = [vp, C.c_int32, _dp, _dp, _i32p]
     L.grlcu_trace_capacity.argtypes = [vp]
     L.grlcu_launch_count.argtypes = [vp]
@@ -259,6 +274,11 @@ class Batch:
         assert v.size == self.cfg.memory
         self._chk(self.lib.grlcu_set_table(self.h, agent, _ptr(v, _dp)))
 
+    def get_actor_table(self, agent):
+        out = np.empty(self.cfg.memory)
+        self._chk(self.lib.grlcu_get_actor_table(self.h, agent, _ptr(out, _dp)))
+        return out
+
     def get_state(self, agent):
         st, act, ep = np.empty(self.S), C.c_double(), C.c_int32()
         self._chk(self.lib.grlcu_get_state(self.h, agent, _ptr(st, _dp), C.byref(act), C.byref(ep)))
@@ -275,6 +295,9 @@ class Batch:
     def replay_step(self, inp, want_trace=True):
         """inp: dict of SoA numpy arrays named like grlcu_replay_in; returns dict of outputs."""
         n, S, OBS, T, A = self.n, self.S, self.cfg.obs_dims, self.cfg.tilings, self.cfg.n_actions
+        HA = A
+        if self.cfg.algo == ALGO_AC:
+            A, HA = 4, 1       # see grlcu_replay_step in include/grlcu.h
         ri = ReplayIn()
         keep = []
         spec = dict(started=np.int32, start_state=np.float64, start_u=np.float64, start_r_explore=np.uint32,
@@ -290,7 +313,7 @@ class Batch:
             keep.append(arr)
             setattr(ri, k, _ptr(arr, ptrty[dt]))
         out = dict(next=np.empty((S, n)), obs=np.empty((OBS, n)), reward=np.empty(n), terminal=np.empty(n, np.int32),
-                   hash=np.zeros((A, T, n), np.uint32), index=np.zeros((A, T, n), np.uint32), q=np.zeros((A, n)),
+                   hash=np.zeros((HA, T, n), np.uint32), index=np.zeros((HA, T, n), np.uint32), q=np.zeros((A, n)),
                    action_index=np.empty(n, np.int32), start_q=np.zeros((A, n)),
                    start_action_index=np.zeros(n, np.int32), q_prev=np.empty(n), target=np.empty(n),
                    delta=np.empty(n), swept=np.empty(n, np.int32), trace_len=np.empty(n, np.int32))

@@ -2,6 +2,7 @@
 // needs a usable CUDA device and reports GRLCU_ERR_CUDA otherwise.
 #include "../../include/grlcu.h"
 #include "grlcu_kernels.cuh"
+#include "grlcu_ac.cuh"
 
 #include <cuda_runtime.h>
 #include <cmath>
@@ -36,6 +37,7 @@ struct grlcu_ctx
 {
   grlcu_config cfg;
   Params p;
+  ACParams ac;
   int device;
   cudaStream_t stream;
   int S, OBS;
@@ -73,16 +75,28 @@ static int grid_for(int64_t work, int block, int cap = 148 * 16)
 
 static int supported(const grlcu_config *cfg)
 {
-  if (cfg->algo != GRLCU_ALGO_SARSA)
-    return fail(GRLCU_ERR_UNSUPPORTED, "algo %d: only SARSA is built in this version", cfg->algo);
+  if (cfg->tilings != 16) return fail(GRLCU_ERR_UNSUPPORTED, "tilings %d: kernels are instantiated for 16", cfg->tilings);
+  if (cfg->memory < 1) return fail(GRLCU_ERR_ARG, "memory must be positive");
+  if (cfg->integration_steps < 1) return fail(GRLCU_ERR_ARG, "integration_steps must be >= 1");
+  if (cfg->algo == GRLCU_ALGO_AC)
+  {
+    if (cfg->dynamics != GRLCU_DYN_CART_DOUBLE_POLE)
+      return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for actor-critic (cart_double_pole only)", cfg->dynamics);
+    if (cfg->obs_dims != 6) return fail(GRLCU_ERR_ARG, "obs_dims %d does not match dynamics (6)", cfg->obs_dims);
+    for (int i = 0; i < cfg->obs_dims; ++i)
+      if (cfg->actor_resolution[i] != cfg->resolution[i] || cfg->actor_wrapping[i] != cfg->wrapping[i])
+        return fail(GRLCU_ERR_UNSUPPORTED, "actor and critic projectors must have the same resolution and wrapping "
+                    "(one index set addresses both tables; cfg/cart_double_pole/ac.yaml)");
+    if (!(cfg->action_min < cfg->action_max)) return fail(GRLCU_ERR_ARG, "action_min must be below action_max");
+    if (cfg->sigma < 0) return fail(GRLCU_ERR_ARG, "sigma must be >= 0");
+    return 0;
+  }
+  if (cfg->algo != GRLCU_ALGO_SARSA) return fail(GRLCU_ERR_UNSUPPORTED, "unknown algo %d", cfg->algo);
   if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE)
     return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for SARSA", cfg->dynamics);
-  if (cfg->tilings != 16) return fail(GRLCU_ERR_UNSUPPORTED, "tilings %d: kernels are instantiated for 16", cfg->tilings);
   if (cfg->n_actions != 3) return fail(GRLCU_ERR_UNSUPPORTED, "n_actions %d: kernels are instantiated for 3", cfg->n_actions);
   const int obs = cfg->dynamics == GRLCU_DYN_PENDULUM ? 2 : 4;
   if (cfg->obs_dims != obs) return fail(GRLCU_ERR_ARG, "obs_dims %d does not match dynamics (%d)", cfg->obs_dims, obs);
-  if (cfg->memory < 1) return fail(GRLCU_ERR_ARG, "memory must be positive");
-  if (cfg->integration_steps < 1) return fail(GRLCU_ERR_ARG, "integration_steps must be >= 1");
   return 0;
 }
 
@@ -134,7 +148,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   p.tau = cfg->control_step; p.isteps = cfg->integration_steps;
   p.timeout = cfg->timeout; p.randomization = cfg->randomization;
   // TileCodingProjector::configure (tile_coding.cpp:66-79)
-  const int dims = cfg->obs_dims + 1;
+  const bool is_ac = cfg->algo == GRLCU_ALGO_AC;
+  const int dims = is_ac ? cfg->obs_dims : cfg->obs_dims + 1;   // AC projects observations, SARSA (obs, action)
   for (int i = 0; i < dims; ++i)
   {
     p.proj.scaling[i] = cfg->tilings / cfg->resolution[i];
@@ -153,7 +168,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     const uint32_t m = 0x5bd1e995u;
     auto mix = [m](uint32_t k) { k *= m; k ^= k >> 24; k *= m; return k; };
     const int ia = cfg->obs_dims;                 // the action is the last projector input
-    for (int aa = 0; aa < cfg->n_actions; ++aa)
+    for (int aa = 0; aa < (is_ac ? 0 : cfg->n_actions); ++aa)
     {
       const int32_t qa = (int32_t)floor(cfg->actions[aa] * p.proj.scaling[ia]);
       for (int j = 0; j < cfg->tilings; ++j)
@@ -187,6 +202,13 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   const size_t n = (size_t)n_agents, T = (size_t)cfg->tilings;
   int r = 0;
   if (!r) r = dalloc(c, &p.table, n * (size_t)cfg->memory);
+  memset(&c->ac, 0, sizeof(c->ac));
+  if (!r && is_ac)
+  {
+    r = dalloc(c, &c->ac.actor, n * (size_t)cfg->memory);
+    c->ac.sigma = cfg->sigma; c->ac.actor_alpha = cfg->actor_alpha;
+    c->ac.action_min = cfg->action_min; c->ac.action_max = cfg->action_max;
+  }
   if (!r) r = dalloc(c, &p.state, n * c->S);
   if (!r) r = dalloc(c, &p.action, n);
   if (!r) r = dalloc(c, &p.prev_idx, n * T);
@@ -267,6 +289,12 @@ static int launch_reset(grlcu_ctx *c, int what)
     k_table_init<<<grid_for(work, 256, 148 * 32), 256, 0, c->stream>>>(
         p.table, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_TABLE);
     c->launches++;
+    if (c->ac.actor)
+    {
+      k_table_init<<<grid_for(work, 256, 148 * 32), 256, 0, c->stream>>>(
+          c->ac.actor, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_ACTOR_TABLE);
+      c->launches++;
+    }
   }
   if (what & GRLCU_RESET_AGENTS) { k_reset_agents<<<grd, blk, 0, c->stream>>>(p); c->launches++; }
   if (what & GRLCU_RESET_STATS) { k_reset_stats<<<grd, blk, 0, c->stream>>>(p); c->launches++; }
@@ -324,7 +352,14 @@ struct Scratch
   }
 };
 
-#define DISPATCH_DYN(c, CALL)                                   \
+#define DISPATCH_DYN(c, CALL)                                        \
+  do {                                                               \
+    if ((c)->cfg.dynamics == GRLCU_DYN_PENDULUM) { CALL(0); }        \
+    else if ((c)->cfg.dynamics == GRLCU_DYN_CART_POLE) { CALL(1); }  \
+    else { CALL(2); }                                                \
+  } while (0)
+// SARSA kernels are instantiated for pendulum and cart-pole only
+#define DISPATCH_SARSA(c, CALL)                                 \
   do {                                                          \
     if ((c)->cfg.dynamics == GRLCU_DYN_PENDULUM) { CALL(0); }   \
     else { CALL(1); }                                           \
@@ -335,7 +370,8 @@ extern "C" int grlcu_project(grlcu_ctx *c, int64_t n, const double *in, uint32_t
   if (!c || n < 0 || !in || !index) return fail(GRLCU_ERR_ARG, "grlcu_project: bad arguments");
   if (n == 0) return 0;
   CU(cudaSetDevice(c->device));
-  const int dims = c->cfg.obs_dims + 1, T = c->cfg.tilings;
+  const bool is_ac = c->cfg.algo == GRLCU_ALGO_AC;
+  const int dims = is_ac ? c->cfg.obs_dims : c->cfg.obs_dims + 1, T = c->cfg.tilings;
   Scratch s;
   double *d_in = s.get<double>((size_t)n * dims);
   uint32_t *d_h = s.get<uint32_t>((size_t)n * T), *d_i = s.get<uint32_t>((size_t)n * T);
@@ -343,7 +379,8 @@ extern "C" int grlcu_project(grlcu_ctx *c, int64_t n, const double *in, uint32_t
   CU(cudaMemcpyAsync(d_in, in, sizeof(double) * n * dims, cudaMemcpyHostToDevice, c->stream));
   const int grd = grid_for(n, 128);
 #define CALL(D) k_project<Dyn<D>::OBS + 1, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i)
-  DISPATCH_DYN(c, CALL);
+  if (is_ac) k_project<6, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i);
+  else DISPATCH_SARSA(c, CALL);
 #undef CALL
   c->launches++;
   CU(cudaGetLastError());
@@ -513,7 +550,8 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
       if (cached) k_run<D, 16, 3, true><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps); \
       else k_run<D, 16, 3, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps);      \
     } while (0)
-    DISPATCH_DYN(c, CALL);
+    if (c->cfg.algo == GRLCU_ALGO_AC) k_run_ac<2, 16><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps);
+    else DISPATCH_SARSA(c, CALL);
 #undef CALL
     CU(cudaEventRecord(e1, c->stream));
     c->ev_pending.push_back({e0, e1});
@@ -636,6 +674,28 @@ extern "C" int grlcu_set_table(grlcu_ctx *c, int32_t agent, const double *in)
   return 0;
 }
 
+extern "C" int grlcu_get_actor_table(grlcu_ctx *c, int32_t agent, double *out)
+{
+  if (!c || !out || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_get_actor_table: bad arguments");
+  if (!c->ac.actor) return fail(GRLCU_ERR_ARG, "grlcu_get_actor_table: not an actor-critic context");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(out, c->ac.actor + (size_t)agent * c->cfg.memory, sizeof(double) * c->cfg.memory,
+                     cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int grlcu_set_actor_table(grlcu_ctx *c, int32_t agent, const double *in)
+{
+  if (!c || !in || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_set_actor_table: bad arguments");
+  if (!c->ac.actor) return fail(GRLCU_ERR_ARG, "grlcu_set_actor_table: not an actor-critic context");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->ac.actor + (size_t)agent * c->cfg.memory, in, sizeof(double) * c->cfg.memory,
+                     cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
 extern "C" int grlcu_get_state(grlcu_ctx *c, int32_t agent, double *state, double *action, int32_t *in_episode)
 {
   if (!c || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_get_state: bad arguments");
@@ -658,13 +718,15 @@ extern "C" int grlcu_get_state(grlcu_ctx *c, int32_t agent, double *state, doubl
 extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_replay_out *out)
 {
   if (!c || !in || !out) return fail(GRLCU_ERR_ARG, "grlcu_replay_step: bad arguments");
+  const bool is_ac = c->cfg.algo == GRLCU_ALGO_AC;
   if (!in->started || !in->state || !in->action || !in->test || !in->obs || !in->reward || !in->terminal ||
-      !in->u || !in->r_explore || !in->r_tie || !in->start_state || !in->start_u || !in->start_r_explore ||
-      !in->start_r_tie)
+      !in->u || !in->start_state || !in->start_u ||
+      (!is_ac && (!in->r_explore || !in->r_tie || !in->start_r_explore || !in->start_r_tie)))
     return fail(GRLCU_ERR_ARG, "grlcu_replay_step: missing input array");
   CU(cudaSetDevice(c->device));
+  // AC mode: one projection row (the fed observation) and four value rows (pi(s'), V(s'), u, a')
   const size_t n = (size_t)c->p.n, S = (size_t)c->S, OBS = (size_t)c->OBS, T = (size_t)c->cfg.tilings,
-               A = (size_t)c->cfg.n_actions, cap = (size_t)c->p.trace_cap;
+               A = is_ac ? 4 : (size_t)c->cfg.n_actions, HA = is_ac ? 1 : A, cap = (size_t)c->p.trace_cap;
   Scratch s;
   ReplayIO io;
   memset(&io, 0, sizeof(io));
@@ -677,17 +739,18 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
     io.field = d;                                                                               \
   } while (0)
   UP(started, int32_t, n); UP(start_state, double, S * n); UP(start_u, double, n);
-  UP(start_r_explore, uint32_t, n); UP(start_r_tie, uint32_t, n);
+  if (!is_ac) { UP(start_r_explore, uint32_t, n); UP(start_r_tie, uint32_t, n); }
   UP(state, double, S * n); UP(action, double, n); UP(test, int32_t, n);
   UP(obs, double, OBS * n); UP(reward, double, n); UP(terminal, int32_t, n);
-  UP(u, double, n); UP(r_explore, uint32_t, n); UP(r_tie, uint32_t, n);
-  if (in->force_action) UP(force_action, int32_t, n);
+  UP(u, double, n);
+  if (!is_ac) { UP(r_explore, uint32_t, n); UP(r_tie, uint32_t, n); }
+  if (in->force_action && !is_ac) UP(force_action, int32_t, n);
 #undef UP
 #define OUTB(ofield, field, type, count) \
   do { if (out->field) { io.ofield = s.get<type>(count); if (!io.ofield) oom = true; } } while (0)
   OUTB(o_next, next, double, S * n); OUTB(o_obs, obs, double, OBS * n); OUTB(o_reward, reward, double, n);
-  OUTB(o_terminal, terminal, int32_t, n); OUTB(o_hash, hash, uint32_t, A * T * n);
-  OUTB(o_index, index, uint32_t, A * T * n); OUTB(o_q, q, double, A * n);
+  OUTB(o_terminal, terminal, int32_t, n); OUTB(o_hash, hash, uint32_t, HA * T * n);
+  OUTB(o_index, index, uint32_t, HA * T * n); OUTB(o_q, q, double, A * n);
   OUTB(o_action_index, action_index, int32_t, n); OUTB(o_start_q, start_q, double, A * n);
   OUTB(o_start_action_index, start_action_index, int32_t, n);
   OUTB(o_q_prev, q_prev, double, n); OUTB(o_target, target, double, n); OUTB(o_delta, delta, double, n);
@@ -697,15 +760,16 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
   if (oom) return fail(GRLCU_ERR_NOMEM, "grlcu_replay_step: device scratch allocation/copy failed");
   const int blk = 64, grd = ((int)n + blk - 1) / blk;
 #define CALL(D) k_replay<D, 16, 3><<<grd, blk, 0, c->stream>>>(c->p, io)
-  DISPATCH_DYN(c, CALL);
+  if (is_ac) k_replay_ac<2, 16><<<grd, blk, 0, c->stream>>>(c->p, c->ac, io);
+  else DISPATCH_SARSA(c, CALL);
 #undef CALL
   c->launches++;
   CU(cudaGetLastError());
 #define DOWN(ofield, field, type, count) \
   do { if (out->field) CU(cudaMemcpyAsync(out->field, io.ofield, sizeof(type) * (count), cudaMemcpyDeviceToHost, c->stream)); } while (0)
   DOWN(o_next, next, double, S * n); DOWN(o_obs, obs, double, OBS * n); DOWN(o_reward, reward, double, n);
-  DOWN(o_terminal, terminal, int32_t, n); DOWN(o_hash, hash, uint32_t, A * T * n);
-  DOWN(o_index, index, uint32_t, A * T * n); DOWN(o_q, q, double, A * n);
+  DOWN(o_terminal, terminal, int32_t, n); DOWN(o_hash, hash, uint32_t, HA * T * n);
+  DOWN(o_index, index, uint32_t, HA * T * n); DOWN(o_q, q, double, A * n);
   DOWN(o_action_index, action_index, int32_t, n); DOWN(o_start_q, start_q, double, A * n);
   DOWN(o_start_action_index, start_action_index, int32_t, n);
   DOWN(o_q_prev, q_prev, double, n); DOWN(o_target, target, double, n); DOWN(o_delta, delta, double, n);

@@ -60,11 +60,11 @@ typedef struct grlcu_config
   uint64_t seed;              /* Philox key; stream = global agent id */
   int32_t rng;                /* ignored (oracle field) */
   int32_t algo;               /* GRLCU_ALGO_* */
-  double  sigma;              /* policy/action sigma (AC) */
-  double  actor_alpha;        /* predictor/ac/action alpha (AC) */
-  double  action_min, action_max;
-  double  actor_resolution[GRLCU_MAX_DIMS];
-  double  actor_wrapping[GRLCU_MAX_DIMS];
+  double  sigma;              /* policy/parameterized/action sigma (AC; action.cpp:40) */
+  double  actor_alpha;        /* predictor/ac/action alpha (AC; ac.cpp:40) */
+  double  action_min, action_max;       /* task action_min/max = actor output_min/max (AC) */
+  double  actor_resolution[GRLCU_MAX_DIMS];  /* AC: the actor's projector; must equal resolution/wrapping, */
+  double  actor_wrapping[GRLCU_MAX_DIMS];    /* which describe the critic's (obs dims only, no action)     */
 } grlcu_config;
 
 typedef struct grlcu_ctx grlcu_ctx;
@@ -178,7 +178,12 @@ int grlcu_sync(grlcu_ctx *ctx);
 int grlcu_run_host(grlcu_ctx *ctx, const double *start_states, int64_t n_steps, int32_t cohort,
                    grlcu_results *results);
 
-/* One replayed agent-step for all agents (see grlcu_replay_in/out). */
+/* One replayed agent-step for all agents (see grlcu_replay_in/out).
+ * Actor-critic contexts (GRLCU_ALGO_AC) use the same structs: in.start_u / in.u carry the Gaussian
+ * exploration term n of ActionPolicy::act (action.cpp:146-149) instead of a uniform, the integer draws and
+ * force_action are ignored; out.hash / out.index hold ONE row of T (projection of in.obs; actor and
+ * critic projectors share it), out.q four rows [pi(s'), V(s'), u = pi(s) read by the update, a'] and
+ * out.start_q four rows [pi(s0), -, -, a0]; out.action_index / start_action_index are not written. */
 int grlcu_replay_step(grlcu_ctx *ctx, const grlcu_replay_in *in, grlcu_replay_out *out);
 
 int grlcu_get_results(grlcu_ctx *ctx, grlcu_results *results);
@@ -187,6 +192,11 @@ int grlcu_get_results(grlcu_ctx *ctx, grlcu_results *results);
  * raw-double checkpoint format of representation.h:201-263: `memory` doubles. */
 int grlcu_get_table(grlcu_ctx *ctx, int32_t agent, double *out);
 int grlcu_set_table(grlcu_ctx *ctx, int32_t agent, const double *in);
+
+/* Actor table of an actor-critic context (GRLCU_ALGO_AC; policy/parameterized/action's
+ * representation, policies/action.cpp:99-113): `memory` doubles, same checkpoint format. */
+int grlcu_get_actor_table(grlcu_ctx *ctx, int32_t agent, double *out);
+int grlcu_set_actor_table(grlcu_ctx *ctx, int32_t agent, const double *in);
 
 /* Environment state ([S]) and pending action of one agent. */
 int grlcu_get_state(grlcu_ctx *ctx, int32_t agent, double *state, double *action, int32_t *in_episode);

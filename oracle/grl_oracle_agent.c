@@ -47,7 +47,9 @@ struct orc_agent
   /* TDAgent state (agents/td.cpp) */
   double prev_obs[ORC_MAX_DIMS];
   double prev_action;
-  uint32_t prev_idx[ORC_MAX_TILINGS]; /* projection of (prev_obs, prev_action) */
+  uint32_t prev_idx[ORC_MAX_TILINGS]; /* projection of (prev_obs, prev_action); AC: critic projection of prev_obs */
+  uint32_t prev_aidx[ORC_MAX_TILINGS]; /* AC: actor projection of prev_obs */
+  double noise;                       /* AC: ActionPolicy::n_ */
   orc_trace trace;
   /* experiment (online_learning.cpp) */
   int in_episode, test;
@@ -364,10 +366,19 @@ orc_agent *orc_create(const orc_config *c, uint64_t agent_id)
      * then sampler/epsilon_greedy configure -> new Rand(), then the test agent's
      * sampler/greedy -> new Rand(). */
     srand48_r(lrand48(), &a->randgen);
-    table_init(a, a->table, STREAM_TABLE);
-    if (a->actor) table_init(a, a->actor, STREAM_ACTOR_TABLE);
-    srand48_r(lrand48(), &a->sampler);
-    srand48_r(lrand48(), &a->test_sampler);
+    if (a->actor)
+    {
+      /* AC YAML: the policy's (actor) representation is configured before the critic's; the action
+       * policies draw from RandGen itself, no sampler objects exist */
+      table_init(a, a->actor, STREAM_ACTOR_TABLE);
+      table_init(a, a->table, STREAM_TABLE);
+    }
+    else
+    {
+      table_init(a, a->table, STREAM_TABLE);
+      srand48_r(lrand48(), &a->sampler);
+      srand48_r(lrand48(), &a->test_sampler);
+    }
   }
   else
   {
@@ -517,5 +528,169 @@ uint64_t orc_run(orc_agent *a, uint64_t n_steps)
   return n;
 }
 
-/* actor-critic path (cfg 4) is added below */
-static int ac_step(orc_agent *a, orc_record *rec) { (void)a; (void)rec; abort(); return 0; }
+/* ---- actor-critic (cfg 4: cfg/cart_double_pole/ac.yaml) ----------------------------------
+ * agent/td with policy/parameterized/action (action.cpp:99-158) and predictor/ac/action
+ * (ac.cpp:72-110, update_method = proportional, no step limit) around predictor/critic/td
+ * (predictors/td.cpp:68-91).  Actor and critic each own a projector and a table; the projectors
+ * hash with the same function (tile_coding.h:78-151 has no per-object seed).
+ * Record layout in AC mode: hash/index rows 0 = actor projection of obs', row 1 = critic projection
+ * of obs'; q[0] = pi(s') (actor read, clamped), q[1] = V(s'), q[2] = u = pi(s) read inside update(),
+ * q[3] = a' = clamp(pi(s') + n); noise / start_noise = the Gaussian term n. */
+
+/* Rand::getNormal (utils.h:120-125): Box-Muller on two uniforms, U1 first */
+static double get_normal(orc_agent *a, double mu, double sigma)
+{
+  double U1, U2;
+  if (a->c.rng == ORC_RNG_GLIBC)
+  {
+    drand48_r(&a->randgen, &U1);
+    drand48_r(&a->randgen, &U2);
+  }
+  else
+  {
+    uint32_t w[4];
+    philox_for(a, STREAM_NOISE, a->act_counter++, w);
+    U1 = u53(w[0], w[1]);
+    U2 = u53(w[2], w[3]);
+  }
+  return sqrt(-2 * log(U1)) * cos(2 * M_PI * U2) * sigma + mu;
+}
+
+/* ActionPolicy::act(time, in, out) (action.cpp:129-158), one action dimension, theta = 1,
+ * decay_ = 1 (decay_rate default 1).  test: the test agent's policy has sigma = 0. */
+static double ac_act(orc_agent *a, const double *obs, int test, int time_is_zero,
+                     uint32_t *hash, uint32_t *idx, double *pi, double *noise)
+{
+  const orc_config *c = &a->c;
+  orc_project(c->actor_resolution, c->actor_wrapping, c->obs_dims, c->tilings, c->memory, obs, hash, idx);
+  double out = table_read(a->actor, idx, c->tilings, c->action_min, c->action_max);   /* ActionPolicy::read */
+  *pi = out;
+  *noise = 0;
+  if (time_is_zero) a->noise = 0.;                       /* n_ = ConstantVector(size, 0.) */
+  if (!test && c->sigma)
+  {
+    a->noise = (1 - 1.) * a->noise + get_normal(a, 0., 1. * c->sigma);
+    out += a->noise;
+    *noise = a->noise;
+  }
+  return fmin(fmax(out, c->action_min), c->action_max);
+}
+
+/* ActionACPredictor::update (ac.cpp:72-110) around TDPredictor::criticize (td.cpp:68-91), tau = 1 */
+static void ac_update(orc_agent *a, double reward, const uint32_t *next_cidx /* NULL if absorbing */, orc_record *rec)
+{
+  const orc_config *c = &a->c;
+  const int T = c->tilings;
+  /* ap = projector_->project(prev_obs); u = representation_->read(ap) */
+  double u = table_read(a->actor, a->prev_aidx, T, c->action_min, c->action_max);
+  /* critic */
+  double target = reward;
+  if (next_cidx)
+    target += c->gamma * table_read(a->table, next_cidx, T, -DBL_MAX, DBL_MAX);
+  double vp = table_read(a->table, a->prev_idx, T, -DBL_MAX, DBL_MAX);
+  double delta = target - vp;
+  int swept = 0, entries = 0;
+  table_write(a->table, a->prev_idx, T, target, a->alpha, -DBL_MAX, DBL_MAX);
+  if (c->trace != ORC_TRACE_NONE)
+  {
+    double e = c->gamma * a->lambda;
+    trace_sweep(&a->trace, a->table, T, a->alpha * delta, e, -DBL_MAX, DBL_MAX, &swept, &entries);
+    trace_add(&a->trace, c->trace, a->prev_idx, T, e);
+  }
+  /* actor: delta = critique * (prev_action - u); target_u = u + delta; write(ap, target_u, alpha) */
+  double du = delta * (a->prev_action - u);
+  double target_u = u + du;
+  table_write(a->actor, a->prev_aidx, T, target_u, c->actor_alpha, c->action_min, c->action_max);
+  a->swept_total += (uint64_t)swept;
+  if (rec)
+  {
+    rec->q_prev = vp; rec->target = target; rec->delta = delta;
+    rec->swept = swept; rec->swept_entries = entries; rec->q[2] = u;
+  }
+}
+
+static int ac_step(orc_agent *a, orc_record *rec)
+{
+  const orc_config *c = &a->c;
+  const int T = c->tilings;
+  uint32_t ahash[ORC_MAX_TILINGS], aidx[ORC_MAX_TILINGS], chash[ORC_MAX_TILINGS], cidx[ORC_MAX_TILINGS];
+  double obs[ORC_MAX_DIMS], next[ORC_MAX_STATE], reward, pi, noise;
+  int32_t terminal;
+  if (rec) memset(rec, 0, sizeof(*rec));
+
+  if (!a->in_episode)
+  {
+    a->test = (c->test_interval >= 0 &&
+               a->tt % (uint64_t)(c->test_interval + 1) == (uint64_t)c->test_interval);
+    double r = task_start(a, a->test, a->state);
+    orc_observe(c, a->state, obs, &terminal);
+    if (!a->test)
+      trace_clear(&a->trace);                         /* TDAgent::start -> predictor finalize -> critic trace */
+    a->action = ac_act(a, obs, a->test, 1, ahash, aidx, &pi, &noise);
+    orc_project(c->resolution, c->wrapping, c->obs_dims, T, c->memory, obs, chash, cidx);
+    memcpy(a->prev_obs, obs, sizeof(obs));
+    a->prev_action = a->action;
+    memcpy(a->prev_aidx, aidx, (size_t)T * sizeof(uint32_t));
+    memcpy(a->prev_idx, cidx, (size_t)T * sizeof(uint32_t));
+    a->total_reward = 0;
+    a->in_episode = 1;
+    if (rec)
+    {
+      rec->started = 1; rec->start_draw = r;
+      memcpy(rec->start_state, a->state, sizeof(double) * (size_t)a->S);
+      rec->start_noise = noise; rec->start_q[0] = pi; rec->start_q[3] = a->action;
+    }
+  }
+
+  orc_env_step(c, a->state, a->action, next, obs, &reward, &terminal);
+  a->total_reward += reward;
+  if (rec)
+  {
+    memcpy(rec->state, a->state, sizeof(double) * (size_t)a->S);
+    rec->action = a->action;
+    memcpy(rec->next, next, sizeof(double) * (size_t)a->S);
+    memcpy(rec->obs, obs, sizeof(double) * (size_t)c->obs_dims);
+    rec->reward = reward; rec->terminal = terminal; rec->test = a->test;
+    rec->action_index = -1;
+  }
+
+  if (terminal == 2)
+  {
+    if (!a->test) ac_update(a, reward, NULL, rec);
+  }
+  else
+  {
+    double action = ac_act(a, obs, a->test, 0, ahash, aidx, &pi, &noise);
+    orc_project(c->resolution, c->wrapping, c->obs_dims, T, c->memory, obs, chash, cidx);
+    if (rec)
+    {
+      memcpy(&rec->hash[0], ahash, (size_t)T * sizeof(uint32_t));
+      memcpy(&rec->index[0], aidx, (size_t)T * sizeof(uint32_t));
+      memcpy(&rec->hash[ORC_MAX_TILINGS], chash, (size_t)T * sizeof(uint32_t));
+      memcpy(&rec->index[ORC_MAX_TILINGS], cidx, (size_t)T * sizeof(uint32_t));
+      rec->q[0] = pi; rec->q[1] = table_read(a->table, cidx, T, -DBL_MAX, DBL_MAX);
+      rec->q[3] = action; rec->noise = noise;
+    }
+    if (!a->test) ac_update(a, reward, cidx, rec);
+    memcpy(a->prev_obs, obs, sizeof(obs));
+    a->prev_action = action;
+    memcpy(a->prev_aidx, aidx, (size_t)T * sizeof(uint32_t));
+    memcpy(a->prev_idx, cidx, (size_t)T * sizeof(uint32_t));
+    a->action = action;
+  }
+  if (rec) dump_trace(a, rec);
+
+  memcpy(a->state, next, sizeof(double) * (size_t)a->S);
+  int counted = !a->test;
+  if (counted) a->ss++;
+  if (terminal)
+  {
+    a->in_episode = 0;
+    a->tt++;
+    a->episodes++;
+    if (a->test) a->last_test_return = a->total_reward;
+    else a->last_return = a->total_reward;
+    if (rec) { rec->episode_done = 1; rec->episode_return = a->total_reward; }
+  }
+  return counted;
+}

@@ -98,6 +98,25 @@ def cart_pole_config(memory=262144, **kw):
     return c
 
 
+def cart_double_pole_ac_config(memory=131072, **kw):
+    """cfg/cart_double_pole/ac.yaml (reference): actor-critic with two tile-coded tables per agent."""
+    c = Config()
+    c.dynamics, c.integration_steps, c.control_step = DYN_CART_DOUBLE_POLE, 5, 0.05
+    c.timeout, c.randomization = 4.99, 0.0
+    c.tilings, c.memory, c.obs_dims, c.n_actions = 16, memory, 6, 0
+    for i, v in enumerate([2.5, 0.0785375, 0.0785375, 2.5, 0.785375, 0.785375]):
+        c.resolution[i] = v
+        c.actor_resolution[i] = v
+    c.alpha, c.gamma, c.lambda_, c.epsilon = 0.2, 0.97, 0.65, 0.0
+    c.trace, c.test_interval = TRACE_REPLACING, 10
+    c.init_min, c.init_max, c.seed = 0.0, 1.0, 1
+    c.rng, c.algo = RNG_PHILOX, ALGO_AC
+    c.sigma, c.actor_alpha, c.action_min, c.action_max = 5.0, 0.01, -20.0, 20.0
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
 _lib = None
 
 
@@ -173,12 +192,18 @@ class OracleBatch:
     def table(self, i):
         return self.np.ctypeslib.as_array(self.L.orc_table(self.agents[i]), shape=(self.cfg.memory,))
 
+    def actor_table(self, i):
+        return self.np.ctypeslib.as_array(self.L.orc_actor_table(self.agents[i]), shape=(self.cfg.memory,))
+
     def set_hyper(self, alpha, lambda_, epsilon):
         for i, a in enumerate(self.agents):
             self.L.orc_set_hyper(a, float(alpha[i]), float(lambda_[i]), float(epsilon[i]))
 
     def step(self):
         np, n, S, OBS, T, A = self.np, self.n, self.S, self.cfg.obs_dims, self.cfg.tilings, self.cfg.n_actions
+        ac = self.cfg.algo == ALGO_AC
+        if ac:
+            A = 4          # AC record: q rows = pi(s'), V(s'), u, a'; hash/index rows = actor, critic projection
         for a, r in zip(self.agents, self.recs):
             self.L.orc_step(a, C.byref(r))
         R = self.recs
@@ -196,14 +221,19 @@ class OracleBatch:
                  q_prev=f64("q_prev"), target=f64("target"), delta=f64("delta"),
                  swept=i32("swept"), trace_len=i32("trace_len"),
                  episode_done=i32("episode_done"), episode_return=f64("episode_return"))
-        hs = np.zeros((A, T, n), np.uint32)
-        ix = np.zeros((A, T, n), np.uint32)
+        HA = 2 if ac else A
+        hs = np.zeros((HA, T, n), np.uint32)
+        ix = np.zeros((HA, T, n), np.uint32)
         for i, r in enumerate(R):
             h = np.ctypeslib.as_array(r.hash).reshape(MAX_ACTIONS, MAX_TILINGS)
             x = np.ctypeslib.as_array(r.index).reshape(MAX_ACTIONS, MAX_TILINGS)
-            hs[:, :, i] = h[:A, :T]
-            ix[:, :, i] = x[:A, :T]
+            hs[:, :, i] = h[:HA, :T]
+            ix[:, :, i] = x[:HA, :T]
         d["hash"], d["index"] = hs, ix
+        if ac:
+            # the draw that is fed in replay mode is the Gaussian exploration term itself
+            d["noise"], d["start_noise"] = f64("noise"), f64("start_noise")
+            d["u"], d["start_u"] = d["noise"], d["start_noise"]
         return d
 
     def trace(self, cap):

@@ -88,3 +88,31 @@ def test_trace_length_bound_and_V(orc):
         mx_len, mx_v = max(mx_len, rec.trace_len), max(mx_v, rec.swept)
     orc.orc_destroy(a)
     assert mx_len == 9 and 0 < mx_v <= 144
+
+
+def test_actor_critic_oracle_learns_and_respects_limits(orc):
+    """cfg 4 (cart-double-pole AC): the oracle's actor-critic balances longer with training, the actor table
+    stays inside [action_min, action_max] (linear.cpp:207-211) and test episodes draw no noise."""
+    import ctypes as C
+    import numpy as np
+    import _oracle as O
+    c = O.cart_double_pole_ac_config(memory=1 << 20, test_interval=10)
+    a = orc.orc_create(C.byref(c), 3)
+    rec = O.Record()
+    tests, lens, cur = [], [], 0
+    try:
+        while len(tests) < 60:
+            orc.orc_step(a, C.byref(rec))
+            cur += 1
+            if rec.test:
+                assert rec.noise == 0.0 and rec.start_noise == 0.0
+            assert -20.0 <= rec.action <= 20.0
+            if rec.episode_done:
+                if rec.test:
+                    tests.append(rec.episode_return)
+                lens.append(cur); cur = 0
+        actor = np.ctypeslib.as_array(orc.orc_actor_table(a), shape=(1 << 20,))
+        assert actor.min() >= -20.0 and actor.max() <= 20.0
+        assert np.mean(tests[-15:]) > 1.5 * np.mean(tests[:15])      # 6.2 per balanced step: longer episodes
+    finally:
+        orc.orc_destroy(a)
