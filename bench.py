@@ -30,6 +30,50 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 STEPS_PER_PASS = 100
 METRIC = "agent-steps/sec (step+tilecode+SARSA update)"
 
+# BASELINE.json configs: [1] is the headline (default); the others are selectable for the result tables.
+#   name: (config maker, agents per GPU, table entries per agent, table bytes formula, description)
+WORKLOADS = {
+    "pendulum": ("pendulum_config", 65536, 65536,
+                 "pendulum swing-up SARSA(lambda) tile coding (cfg/pendulum/sarsa_tc.yaml)"),
+    "cart_pole": ("cart_pole_config", 32768, 262144,
+                  "cart-pole swing-up SARSA(lambda) tile coding (cfg/cart_pole/sarsa.yaml), 4-D state, 3 actions"),
+    "cart_double_pole_ac": ("cart_double_pole_ac_config", 65536, 131072,
+                            "cart-double-pole actor-critic, two tile-coded tables per agent (cfg/cart_double_pole/ac.yaml)"),
+    "sweep": ("pendulum_config", 131072, 32768,
+              "pendulum SARSA-TC alpha x lambda x epsilon sweep (4 x 8 x 4 grid), per-agent hyper-parameters"),
+}
+SWEEP_ALPHA = [0.05, 0.1, 0.2, 0.4]
+SWEEP_LAMBDA = [0.0, 0.2, 0.4, 0.5, 0.65, 0.75, 0.85, 0.9]
+SWEEP_EPSILON = [0.01, 0.02, 0.05, 0.1]
+
+
+def make_config(mod, args):
+    """The workload's config from `mod` (grl_b200 or the oracle harness: same maker names, same fields)."""
+    maker = WORKLOADS[args.workload][0]
+    kw = dict(memory=args.memory, test_interval=-1)
+    if args.workload != "cart_double_pole_ac":
+        kw["randomization"] = 1.0
+    if args.workload == "sweep":
+        kw["lambda_"] = max(SWEEP_LAMBDA)          # trace ring sized for the largest lambda of the grid
+    return getattr(mod, maker)(**kw)
+
+
+def sweep_hyper(first_id, n):
+    """Per-agent (alpha, lambda, epsilon): grid cell = global agent id mod 128, seeds fill the rest."""
+    import numpy as np
+    gid = np.arange(first_id, first_id + n)
+    cell = gid % (len(SWEEP_ALPHA) * len(SWEEP_LAMBDA) * len(SWEEP_EPSILON))
+    a = np.array(SWEEP_ALPHA)[cell % len(SWEEP_ALPHA)]
+    l = np.array(SWEEP_LAMBDA)[(cell // len(SWEEP_ALPHA)) % len(SWEEP_LAMBDA)]
+    e = np.array(SWEEP_EPSILON)[cell // (len(SWEEP_ALPHA) * len(SWEEP_LAMBDA))]
+    return a, l, e
+
+
+def table_bytes_per_step(workload, V):
+    """algorithmic table bytes per agent-step (8-byte entries, each touched entry once per read and
+    once per write): SARSA 8*A*T + 8*T + 8*T + 16*V = 640 + 16 V; AC 8*T + 16*T + 2*8*T + 8*T + 16*V = 768 + 16 V."""
+    return (768 if workload == "cart_double_pole_ac" else 640) + 16 * V
+
 
 def peaks():
     try:
@@ -40,13 +84,15 @@ def peaks():
 
 
 # ---------------------------------------------------------------- CPU oracle timing (reference arm)
-def _cpu_worker(args):
-    memory, agent_id, n_steps, dynamics = args
+def _cpu_worker(wargs):
+    args, agent_id, n_steps = wargs
     import _oracle as O
     L = O.lib()
-    mk = O.pendulum_config if dynamics == 0 else O.cart_pole_config
-    cfg = mk(memory=memory, randomization=1.0, test_interval=-1)
+    cfg = make_config(O, args)
     a = L.orc_create(C.byref(cfg), agent_id)
+    if args.workload == "sweep":
+        al, la, ep = sweep_hyper(agent_id, 1)
+        L.orc_set_hyper(a, float(al[0]), float(la[0]), float(ep[0]))
     L.orc_run(a, 2000)                         # warm the table/caches
     t0 = time.perf_counter()
     done = L.orc_run(a, n_steps)
@@ -55,7 +101,7 @@ def _cpu_worker(args):
     return done, dt
 
 
-def cpu_oracle_rate(memory, steps_per_proc, dynamics=0, procs=None):
+def cpu_oracle_rate(args, steps_per_proc, procs=None):
     """One oracle process per host core (the reference's grld is single-agent, single-thread);
     aggregate agent-steps / wall time of the slowest process."""
     import _oracle as O
@@ -63,7 +109,7 @@ def cpu_oracle_rate(memory, steps_per_proc, dynamics=0, procs=None):
     procs = procs or os.cpu_count() or 1
     t0 = time.perf_counter()
     with mp.get_context("fork").Pool(procs) as pool:
-        res = pool.map(_cpu_worker, [(memory, i, steps_per_proc, dynamics) for i in range(procs)])
+        res = pool.map(_cpu_worker, [(args, i, steps_per_proc) for i in range(procs)])
     wall = time.perf_counter() - t0
     total = sum(r[0] for r in res)
     slowest = max(r[1] for r in res)
@@ -75,13 +121,13 @@ def reference_arm(args):
     if rank != 0:
         return
     # size the sample so K+W steps finish within a few minutes: calibrate with a short run
-    rate0, procs, _ = cpu_oracle_rate(args.memory, 50000)
+    rate0, procs, _ = cpu_oracle_rate(args, 50000)
     per_proc = max(int(rate0 / procs * 4.0), 10000)           # ~4 s of CPU work per step
     for _ in range(args.warmup):
-        cpu_oracle_rate(args.memory, per_proc // 4)
+        cpu_oracle_rate(args, per_proc // 4)
     rates, t0 = [], time.perf_counter()
     for _ in range(args.steps):
-        r, procs, _ = cpu_oracle_rate(args.memory, per_proc)
+        r, procs, _ = cpu_oracle_rate(args, per_proc)
         rates.append(r)
     wall = time.perf_counter() - t0
     value = sum(rates) / len(rates)
@@ -101,13 +147,17 @@ def reference_arm(args):
 
 
 def workload_config(args, n_gpus):
-    return {"workload": "pendulum swing-up SARSA(lambda) tile coding (cfg/pendulum/sarsa_tc.yaml), "
-                        "%d independent agents per GPU" % args.agents,
-            "agents_per_gpu": args.agents, "agents_total": args.agents * n_gpus, "memory_per_agent": args.memory,
-            "agent_steps_per_pass": STEPS_PER_PASS, "tilings": 16, "actions": 3, "trace": "replacing",
-            "randomization": 1.0, "test_interval": -1, "cohort": args.cohort,
-            "l2": "tables (agents*memory*8 B = %.1f GiB per GPU) are far larger than L2; no flush needed"
-                  % (args.agents * args.memory * 8 / 2**30)}
+    tables = 2 if args.workload == "cart_double_pole_ac" else 1
+    cfg = {"workload": "%s, %d independent agents per GPU" % (WORKLOADS[args.workload][3], args.agents),
+           "name": args.workload, "agents_per_gpu": args.agents, "agents_total": args.agents * n_gpus,
+           "memory_per_agent": args.memory, "tables_per_agent": tables,
+           "agent_steps_per_pass": STEPS_PER_PASS, "tilings": 16, "trace": "replacing",
+           "test_interval": -1, "cohort": args.cohort,
+           "l2": "tables (agents*memory*8 B*%d = %.1f GiB per GPU) are far larger than L2; no flush needed"
+                 % (tables, tables * args.agents * args.memory * 8 / 2**30)}
+    if args.workload == "sweep":
+        cfg["grid"] = {"alpha": SWEEP_ALPHA, "lambda": SWEEP_LAMBDA, "epsilon": SWEEP_EPSILON}
+    return cfg
 
 
 # ---------------------------------------------------------------- clocks sampler
@@ -160,13 +210,15 @@ def ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    cfg = grl_b200.pendulum_config(memory=args.memory, randomization=1.0, test_interval=-1)
+    cfg = make_config(grl_b200, args)
     stream = torch.cuda.current_stream().cuda_stream
     from grl_b200.dist import shard
     first_id, _ = shard(rank, world, args.agents)
     batch = grl_b200.Batch(cfg, args.agents, first_agent_id=first_id, device=local, stream=stream)
     n, S = args.agents, batch.S
     bufs = batch.result_buffers()
+    if args.workload == "sweep":
+        batch.set_hyper(*sweep_hyper(first_id, n))
 
     # ---- device-resident throughput
     for _ in range(args.warmup):
@@ -195,13 +247,22 @@ def ours(args):
     rng = np.random.default_rng(1234 + rank)
     start = torch.zeros((n, S), dtype=torch.float64).pin_memory()
     start_np = start.numpy()
-    start_np[:, 0] = np.pi + rng.uniform(0, 2 * np.pi, n)
+    def new_starts():
+        # Task::start of the workload's task on the host (pendulum.cpp:97-105, cart_pole.cpp:155-166,
+        # cart_double_pole.cpp:250-262): synthetic start-state batch for the end-to-end leg
+        if cfg.dynamics == 0:
+            start_np[:, 0] = np.pi + rng.uniform(0, 2 * np.pi, n)
+        elif cfg.dynamics == 1:
+            start_np[:, 1] = np.pi + (0.1 * rng.uniform(0, 1, n) - 0.05)
+        else:
+            start_np[:, 1] = 0.01 * rng.uniform(0, 1, n) - 0.005
+    new_starts()
     for _ in range(max(1, min(args.warmup, 2))):
         batch.run_host(start_np, STEPS_PER_PASS, args.cohort, bufs)
     barrier()
     t0 = time.perf_counter()
     for k in range(args.steps):
-        start_np[:, 0] = np.pi + rng.uniform(0, 2 * np.pi, n)
+        new_starts()
         batch.run_host(start_np, STEPS_PER_PASS, args.cohort, bufs)
         _ = float(bufs["last_return"][0])
     barrier()
@@ -220,7 +281,7 @@ def ours(args):
     if rank == 0:
         peak, peak_src = peaks()
         V = swept_all / max(steps_all, 1)
-        B = 8 * 3 * 16 + 8 * 16 + 8 * 16 + 16 * V          # 640 + 16 V bytes per agent-step
+        B = table_bytes_per_step(args.workload, V)
         per_gpu_steps = steps_all / world
         achieved = per_gpu_steps * B / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
         value = steps_all / (dev_ms * 1e-3)
@@ -235,15 +296,16 @@ def ours(args):
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "bytes_per_agent_step": B, "V_mean": V, "kernel": "grlcu::k_run",
+                         "bytes_per_agent_step": B, "V_mean": V,
+                         "kernel": "grlcu::k_run_ac" if args.workload == "cart_double_pole_ac" else "grlcu::k_run",
                          "kernel_ms_per_launch": kern_ms / max(kern_launches, 1),
                          "kernel_launches": int(kern_launches)},
             "mean_last_return": mean_return,
         }
         if world == 1 and not args.no_cpu:
-            rate0, procs, _ = cpu_oracle_rate(args.memory, 50000)
+            rate0, procs, _ = cpu_oracle_rate(args, 50000)
             per_proc = max(int(rate0 / procs * 12.0), 10000)
-            rate, procs, wall = cpu_oracle_rate(args.memory, per_proc)
+            rate, procs, wall = cpu_oracle_rate(args, per_proc)
             line["cpu_baseline"] = {"value": rate, "unit": "agent-steps/s", "cores": procs, "kind": "port",
                                     "sample": "%d oracle processes (one per core) x %d agent-steps, memory=%d, %.1f s"
                                               % (procs, per_proc, args.memory, wall)}
@@ -259,11 +321,16 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--agents", type=int, default=65536, help="agents per GPU")
-    ap.add_argument("--memory", type=int, default=65536, help="table entries per agent")
+    ap.add_argument("--workload", default="pendulum", choices=sorted(WORKLOADS))
+    ap.add_argument("--agents", type=int, default=None, help="agents per GPU (default: the workload's)")
+    ap.add_argument("--memory", type=int, default=None, help="table entries per agent (default: the workload's)")
     ap.add_argument("--cohort", type=int, default=0, help="agents per L2-resident cohort (0 = all at once)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    if args.agents is None:
+        args.agents = WORKLOADS[args.workload][1]
+    if args.memory is None:
+        args.memory = WORKLOADS[args.workload][2]
     if args.impl == "reference":
         reference_arm(args)
     else:
