@@ -242,6 +242,7 @@ def ours(args):
     r1 = batch.results()
     steps_done = int((r1["steps"] - r0["steps"]).sum())
     swept = int((r1["swept"] - r0["swept"]).sum())
+    writes = int((r1["table_writes"] - r0["table_writes"]).sum())
 
     # ---- end to end through the host-buffer call (pinned start states in, results out)
     rng = np.random.default_rng(1234 + rank)
@@ -270,12 +271,12 @@ def ours(args):
     clocks.stop_flag = True
     clocks.join(timeout=2)
     h2d = n * S * 8
-    d2h = n * (8 * 3 + 8 + 4 + 8)
+    d2h = n * (8 * 3 + 8 + 4 + 8 + 8)
 
     # ---- max over ranks; the only collective: final statistics gather over NCCL
     from grl_b200.dist import finalize
-    (dev_ms, e2e_s, kern_ms), (steps_all, swept_all), ret = finalize(
-        [dev_ms, e2e_s, kern_ms], [steps_done, swept], r1["last_return"], "cuda")
+    (dev_ms, e2e_s, kern_ms), (steps_all, swept_all, writes_all), ret = finalize(
+        [dev_ms, e2e_s, kern_ms], [steps_done, swept, writes], r1["last_return"], "cuda")
     mean_return = float(ret.mean())
 
     if rank == 0:
@@ -284,6 +285,35 @@ def ours(args):
         B = table_bytes_per_step(args.workload, V)
         per_gpu_steps = steps_all / world
         achieved = per_gpu_steps * B / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
+        # DRAM traffic of one launch, from the committed ncu capture of this exact workload (if there is one)
+        traffic, traffic_src = None, None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                t = json.load(f).get("%s:%d:%d" % (args.workload, args.agents, args.memory))
+            if t:
+                traffic, traffic_src = t["dram_bytes_per_launch"], t["capture"]
+        except Exception:
+            pass
+        # What actually bounds the path: every table access is a hash-random 8-byte word.  Ceilings measured on
+        # this GPU type (profiles/random_access_ceilings.json); accesses counted on the device.
+        random_access = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "random_access_ceilings.json")) as f:
+                ceil = json.load(f)
+            ac = args.workload == "cart_double_pole_ac"
+            cached = args.workload in ("pendulum", "cart_pole") and os.environ.get("GRLCU_MODE", "0") == "0"
+            W = writes_all / max(steps_all, 1)
+            R = (4 * 16 if ac else 3 * 16 + 16) + (0 if cached else V)      # cached path: the sweep runs on the dense cache
+            floor_ns = R / ceil["read_G_per_s"] + W / ceil["write_G_per_s"]
+            got_ns = kern_ms * 1e6 / max(per_gpu_steps, 1)
+            random_access = {"reads_per_agent_step": R, "writes_per_agent_step": W,
+                             "read_ceiling_G_per_s": ceil["read_G_per_s"], "write_ceiling_G_per_s": ceil["write_G_per_s"],
+                             "ns_per_agent_step_at_ceiling": floor_ns, "ns_per_agent_step": got_ns,
+                             "frac": floor_ns / got_ns if got_ns > 0 else None,
+                             "note": "time the measured counts of random 8-byte table reads and writes would take at "
+                                     "the measured B200 ceilings, over the kernel's measured time"}
+        except Exception:
+            pass
         value = steps_all / (dev_ms * 1e-3)
         e2e_val = args.agents * world * STEPS_PER_PASS * args.steps / e2e_s
         line = {
@@ -295,7 +325,8 @@ def ours(args):
             "gpu_launches": int(launches),
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src, "random_access": random_access,
                          "bytes_per_agent_step": B, "V_mean": V,
                          "kernel": "grlcu::k_run_ac" if args.workload == "cart_double_pole_ac" else "grlcu::k_run",
                          "kernel_ms_per_launch": kern_ms / max(kern_launches, 1),

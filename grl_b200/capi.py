@@ -105,7 +105,7 @@ class ReplayOut(C.Structure):
 
 class Results(C.Structure):
     _fields_ = [("last_return", _dp), ("last_test_return", _dp), ("return_sum", _dp),
-                ("steps", _u64p), ("episodes", _u32p), ("swept", _u64p)]
+                ("steps", _u64p), ("episodes", _u32p), ("swept", _u64p), ("table_writes", _u64p)]
 
 
 EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy", "grlcu_reset",
@@ -243,12 +243,14 @@ class Batch:
         r.last_return, r.last_test_return = _ptr(bufs["last_return"], _dp), _ptr(bufs["last_test_return"], _dp)
         r.return_sum, r.steps = _ptr(bufs["return_sum"], _dp), _ptr(bufs["steps"], _u64p)
         r.episodes, r.swept = _ptr(bufs["episodes"], _u32p), _ptr(bufs["swept"], _u64p)
+        r.table_writes = _ptr(bufs["table_writes"], _u64p)
         return r
 
     def result_buffers(self):
         n = self.n
         return dict(last_return=np.empty(n), last_test_return=np.empty(n), return_sum=np.empty(n),
-                    steps=np.empty(n, np.uint64), episodes=np.empty(n, np.uint32), swept=np.empty(n, np.uint64))
+                    steps=np.empty(n, np.uint64), episodes=np.empty(n, np.uint32), swept=np.empty(n, np.uint64),
+                    table_writes=np.empty(n, np.uint64))
 
     def results(self, bufs=None):
         bufs = bufs or self.result_buffers()

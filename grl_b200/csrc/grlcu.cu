@@ -226,6 +226,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   if (!r) r = dalloc(c, &p.tt, n);
   if (!r) r = dalloc(c, &p.ss, n);
   if (!r) r = dalloc(c, &p.swept, n);
+  if (!r) r = dalloc(c, &p.tblw, n);
   if (!r) r = dalloc(c, &p.episodes, n);
   if (!r) r = dalloc(c, &p.total_reward, n);
   if (!r) r = dalloc(c, &p.last_return, n);
@@ -268,7 +269,7 @@ __global__ void k_reset_stats(Params p)
 {
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= p.n) return;
-  p.ss[a] = 0; p.swept[a] = 0; p.episodes[a] = 0;
+  p.ss[a] = 0; p.swept[a] = 0; p.tblw[a] = 0; p.episodes[a] = 0;
   p.last_return[a] = 0; p.last_test_return[a] = 0; p.return_sum[a] = 0;
 }
 
@@ -611,6 +612,7 @@ static int results_async(grlcu_ctx *c, grlcu_results *r)
   if (int e = d2h(c, r->steps, p.ss, n)) return e;
   if (int e = d2h(c, r->episodes, p.episodes, n)) return e;
   if (int e = d2h(c, r->swept, p.swept, n)) return e;
+  if (int e = d2h(c, r->table_writes, p.tblw, n)) return e;
   return 0;
 }
 

@@ -78,6 +78,7 @@ __device__ __forceinline__ void ac_update(const Params &p, const ACParams &ac, A
     for (int j = 0; j < T; ++j)                            // duplicate indices: sequential, clamped each time
       actor[ag.pidx[j]] = clampd(actor[ag.pidx[j]] + dw, ac.action_min, ac.action_max);
   }
+  ag.dtblw += (uint32_t)T;                                  // actor stores (the critic's are counted by sarsa_update)
   u_out = u;
 }
 

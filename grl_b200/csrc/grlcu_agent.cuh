@@ -43,6 +43,7 @@ struct Params
   double   *cache_val;        // [cap*T][n] cached trace weights (grlcu_cached.cuh)
   uint32_t *cache_mask;       // [cap][n] valid bits per trace entry
   uint64_t *act_ctr, *test_act_ctr, *episode_ctr, *tt, *ss, *swept;
+  uint64_t *tblw;             // random 8-byte table stores issued (roofline accounting)
   uint32_t *episodes;
   double   *total_reward, *last_return, *last_test_return, *return_sum;
   const double *alpha_a, *lambda_a, *epsilon_a;   // optional per-agent hyper-parameters
@@ -123,6 +124,7 @@ struct Agent
   uint64_t act_ctr;
   double   alpha, e, epsilon;       // e = gamma*lambda = pow(gamma*lambda, tau) for tau = 1
   uint32_t dsteps, dswept;          // learning steps / swept indices since load()
+  uint32_t dtblw;                   // table stores since load()
 
   __device__ __forceinline__ void load(const Params &p, int a)
   {
@@ -137,7 +139,7 @@ struct Agent
     alpha = p.alpha_a ? p.alpha_a[a] : p.alpha;
     e = p.gamma * (p.lambda_a ? p.lambda_a[a] : p.lambda);
     epsilon = p.epsilon_a ? p.epsilon_a[a] : p.epsilon;
-    dsteps = 0; dswept = 0;
+    dsteps = 0; dswept = 0; dtblw = 0;
   }
   __device__ __forceinline__ void store(const Params &p, int a) const
   {
@@ -149,7 +151,7 @@ struct Agent
     p.trace_len[a] = len; p.trace_head[a] = head; p.flags[a] = flags; p.dupmask[a] = dupmask;
     p.total_decay[a] = total_decay; p.total_reward[a] = total_reward;
     p.act_ctr[a] = act_ctr;
-    p.ss[a] += dsteps; p.swept[a] += dswept;
+    p.ss[a] += dsteps; p.swept[a] += dswept; p.tblw[a] += dtblw;
   }
   // online_learning.cpp:223-262 bookkeeping at the end of an episode
   __device__ __forceinline__ void episode_end(const Params &p, int a, bool test)
@@ -433,6 +435,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
     }
   }
   ag.dswept += (uint32_t)swept;
+  ag.dtblw += (uint32_t)(T + swept);
   o_qp = qp; o_target = target; o_delta = delta; o_swept = swept;
 }
 

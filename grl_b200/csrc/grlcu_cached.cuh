@@ -55,19 +55,20 @@ __device__ __forceinline__ double resolve(const Cache<T> &c, double raw)
 
 // Write the cached values of one entry back into the table (plain representation).
 template <int T>
-__device__ __forceinline__ void flush_entry(const Cache<T> &c, double *tbl, int pos)
+__device__ __forceinline__ uint32_t flush_entry(const Cache<T> &c, double *tbl, int pos)
 {
   const uint32_t m = c.mask(pos);
 #pragma unroll
   for (int j = 0; j < T; ++j)
     if ((m >> j) & 1u) tbl[c.idx(pos, j)] = c.val(pos * T + j);
+  return (uint32_t)__popc(m);          // table stores issued
 }
 
 // Kernel entry: the ring is in the plain representation (kInvalidIndex = invalidated).  Build the valid
 // masks, fold duplicate indices inside an entry onto their first occurrence, pull the cached weights out
 // of the table and leave sentinels behind.
 template <int DYN, int T>
-__device__ __forceinline__ void cache_open(const Params &p, const Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+__device__ __forceinline__ void cache_open(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
 {
   for (int k = 0; k < ag.len; ++k)
   {
@@ -85,6 +86,7 @@ __device__ __forceinline__ void cache_open(const Params &p, const Agent<DYN, T> 
           if (((m >> j) & 1u) && ((m >> jj) & 1u) && ix[j] == ix[jj]) { m &= ~(1u << j); c.idx(pos, j) = kAliasBit | (uint32_t)jj; }
     }
     c.mask(pos) = m;
+    ag.dtblw += (uint32_t)__popc(m);
 #pragma unroll
     for (int j = 0; j < T; ++j)
       if ((m >> j) & 1u)
@@ -98,12 +100,13 @@ __device__ __forceinline__ void cache_open(const Params &p, const Agent<DYN, T> 
 // Kernel exit: back to the plain representation (values in the table, kInvalidIndex in the ring for
 // invalidated slots, alias slots showing the index they duplicate).
 template <int DYN, int T>
-__device__ __forceinline__ void cache_close(const Params &p, const Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+__device__ __forceinline__ void cache_close(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
 {
   for (int k = 0; k < ag.len; ++k)
   {
     const int pos = ring_pos(ag.head, k, p.trace_cap);
     const uint32_t m = c.mask(pos);
+    ag.dtblw += (uint32_t)__popc(m);
 #pragma unroll
     for (int j = 0; j < T; ++j)
     {
@@ -123,7 +126,7 @@ __device__ __forceinline__ void cache_close(const Params &p, const Agent<DYN, T>
 template <int DYN, int T>
 __device__ __forceinline__ void cache_clear(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
 {
-  for (int k = 0; k < ag.len; ++k) flush_entry<T>(c, tbl, ring_pos(ag.head, k, p.trace_cap));
+  for (int k = 0; k < ag.len; ++k) ag.dtblw += flush_entry<T>(c, tbl, ring_pos(ag.head, k, p.trace_cap));
   ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0;
 }
 
@@ -261,6 +264,7 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
       c.idx(pos, j) = x;
     }
     c.mask(pos) = owner;
+    ag.dtblw += (uint32_t)__popc(owner);           // directory sentinels written
   }
   ag.len++;
   ag.dupmask = (ag.dupmask << 1) | (pdup ? 1u : 0u);
@@ -268,7 +272,7 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
   while (ag.total_decay < dc && ag.len > 1)
   {
     ag.total_decay /= e;
-    flush_entry<T>(c, tbl, ring_pos(ag.head, ag.len - 1, cap));
+    ag.dtblw += flush_entry<T>(c, tbl, ring_pos(ag.head, ag.len - 1, cap));
     ag.len--;
   }
   ag.dswept += (uint32_t)swept;

@@ -117,6 +117,7 @@ typedef struct grlcu_results
   uint64_t *steps;             /* learning steps (ss, online_learning.cpp:219) */
   uint32_t *episodes;          /* finished episodes (learning + test) */
   uint64_t *swept;             /* sum of V over learning steps */
+  uint64_t *table_writes;      /* random 8-byte table stores issued (roofline accounting) */
 } grlcu_results;
 
 const char *grlcu_last_error(void);

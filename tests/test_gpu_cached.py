@@ -46,7 +46,8 @@ def test_cached_equals_uncached(case):
     assert not np.isnan(t0).any()                      # no directory sentinel left in a table
     assert np.array_equal(t0, t1)
     for k in r0:
-        assert np.array_equal(r0[k], r1[k]), k
+        if k != "table_writes":               # roofline accounting: differs between the two paths by design
+            assert np.array_equal(r0[k], r1[k]), k
     for a, b in zip(s0, s1):
         assert np.array_equal(a[0], b[0]) and a[1:] == b[1:]
     assert int(r0["steps"].sum()) > 0 and int(r0["swept"].sum()) >= 0
