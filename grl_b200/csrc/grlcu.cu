@@ -44,6 +44,7 @@ struct grlcu_ctx
   std::vector<void *> allocs;
   double *d_alpha, *d_lambda, *d_epsilon, *d_start;
   int64_t launches;
+  bool cache_live;            // the trace value cache of the fused kernel is live (tables hold directory sentinels)
   // run-kernel timing (events recorded around every k_run launch)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending;
   std::vector<cudaEvent_t> ev_pool;
@@ -113,6 +114,7 @@ static int trace_capacity_for(double e, int kind)
 }
 
 static int launch_reset(grlcu_ctx *c, int what);
+static int ensure_plain(grlcu_ctx *c);
 
 extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t first_agent_id,
                             int32_t device, void *stream, grlcu_ctx **out)
@@ -139,6 +141,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   c->OBS = cfg->obs_dims;
   c->d_alpha = c->d_lambda = c->d_epsilon = c->d_start = nullptr;
   c->launches = 0;
+  c->cache_live = false;
   c->block = 64;
   if (const char *b = getenv("GRLCU_BLOCK")) { int v = atoi(b); if (v >= 32 && v <= kMaxBlock && v % 32 == 0) c->block = v; }
 
@@ -303,10 +306,24 @@ static int launch_reset(grlcu_ctx *c, int what)
   return 0;
 }
 
+// Tables and trace rings in the plain representation the reference (and every other entry point) expects.
+static int ensure_plain(grlcu_ctx *c)
+{
+  if (!c->cache_live) return 0;
+  const int blk = 64, grd = (c->p.n + blk - 1) / blk;
+  if (c->cfg.dynamics == GRLCU_DYN_PENDULUM) k_cache_close<0, 16><<<grd, blk, 0, c->stream>>>(c->p);
+  else k_cache_close<1, 16><<<grd, blk, 0, c->stream>>>(c->p);
+  c->launches++;
+  CU(cudaGetLastError());
+  c->cache_live = false;
+  return 0;
+}
+
 extern "C" int grlcu_reset(grlcu_ctx *c, int32_t what)
 {
   if (!c) return fail(GRLCU_ERR_ARG, "null context");
   CU(cudaSetDevice(c->device));
+  if (int r = ensure_plain(c)) return r;
   return launch_reset(c, what);
 }
 
@@ -491,6 +508,7 @@ static int table_view(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t
 {
   if (!c || agent < 0 || agent >= c->p.n || n_idx < 1 || !idx) return fail(GRLCU_ERR_ARG, "grlcu_read/update: bad arguments");
   CU(cudaSetDevice(c->device));
+  if (int r = ensure_plain(c)) return r;
   Scratch s;
   uint64_t *d_i = s.get<uint64_t>(n_idx);
   double *d_v = s.get<double>(1);
@@ -538,6 +556,10 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
   CU(cudaSetDevice(c->device));
   const int n = c->p.n;
   if (cohort <= 0 || cohort > n) cohort = n;
+  // the cache stays live between launches (values return to the tables lazily, see ensure_plain) unless the
+  // agents run in cohorts or GRLCU_EAGER_CLOSE is set
+  const bool lazy = cohort == n && !getenv("GRLCU_EAGER_CLOSE");
+  if (!lazy) if (int r = ensure_plain(c)) return r;
   for (int begin = 0; begin < n; begin += cohort)
   {
     const int end = begin + cohort < n ? begin + cohort : n;
@@ -548,12 +570,13 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
     const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 32;
 #define CALL(D)                                                                                    \
     do {                                                                                           \
-      if (cached) k_run<D, 16, 3, true><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps); \
-      else k_run<D, 16, 3, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps);      \
+      if (cached) k_run<D, 16, 3, true><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
+      else k_run<D, 16, 3, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0);      \
     } while (0)
     if (c->cfg.algo == GRLCU_ALGO_AC) k_run_ac<2, 16><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps);
     else DISPATCH_SARSA(c, CALL);
 #undef CALL
+    if (cached && lazy && begin + cohort >= n) c->cache_live = true;
     CU(cudaEventRecord(e1, c->stream));
     c->ev_pending.push_back({e0, e1});
     c->launches++;
@@ -660,6 +683,7 @@ extern "C" int grlcu_get_table(grlcu_ctx *c, int32_t agent, double *out)
 {
   if (!c || !out || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_get_table: bad arguments");
   CU(cudaSetDevice(c->device));
+  if (int r = ensure_plain(c)) return r;
   CU(cudaMemcpyAsync(out, c->p.table + (size_t)agent * c->cfg.memory, sizeof(double) * c->cfg.memory,
                      cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -670,6 +694,7 @@ extern "C" int grlcu_set_table(grlcu_ctx *c, int32_t agent, const double *in)
 {
   if (!c || !in || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_set_table: bad arguments");
   CU(cudaSetDevice(c->device));
+  if (int r = ensure_plain(c)) return r;
   CU(cudaMemcpyAsync(c->p.table + (size_t)agent * c->cfg.memory, in, sizeof(double) * c->cfg.memory,
                      cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
@@ -726,6 +751,7 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
       (!is_ac && (!in->r_explore || !in->r_tie || !in->start_r_explore || !in->start_r_tie)))
     return fail(GRLCU_ERR_ARG, "grlcu_replay_step: missing input array");
   CU(cudaSetDevice(c->device));
+  if (int r = ensure_plain(c)) return r;
   // AC mode: one projection row (the fed observation) and four value rows (pi(s'), V(s'), u, a')
   const size_t n = (size_t)c->p.n, S = (size_t)c->S, OBS = (size_t)c->OBS, T = (size_t)c->cfg.tilings,
                A = is_ac ? 4 : (size_t)c->cfg.n_actions, HA = is_ac ? 1 : A, cap = (size_t)c->p.trace_cap;

@@ -192,7 +192,7 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, co
 // 148 SMs (448 threads/SM), which bounds the kernel at 144 registers per thread.
 template <int DYN, int T, int A, bool CACHED>
 __global__ void __launch_bounds__(kMaxBlock, 7)
-k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
+k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, int do_close)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
   __shared__ uint32_t s_idx[A * T][kMaxBlock];
@@ -205,7 +205,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
   const uint64_t gid = (uint64_t)(p.first_id + a);
   Cache<T> c;
   c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (size_t)p.n;
-  if (CACHED) cache_open<DYN, T>(p, ag, c, tbl);
+  if (CACHED && do_open) cache_open<DYN, T>(p, ag, c, tbl);
 
   for (int64_t step = 0; step < n_steps; ++step)
   {
@@ -250,7 +250,22 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps)
     if (!test) ag.dsteps++;
     if (terminal) ag.episode_end(p, a, test);
   }
-  if (CACHED) cache_close<DYN, T>(p, ag, c, tbl);
+  if (CACHED && do_close) cache_close<DYN, T>(p, ag, c, tbl);
+  ag.store(p, a);
+}
+
+// Back to the plain representation (see grlcu_cached.cuh) when the host wants to look at tables or traces:
+// the fused kernel leaves the trace value cache live between launches.
+template <int DYN, int T>
+__global__ void k_cache_close(Params p)
+{
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= p.n) return;
+  Agent<DYN, T> ag;
+  ag.load(p, a);
+  Cache<T> c;
+  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (size_t)p.n;
+  cache_close<DYN, T>(p, ag, c, p.table + (size_t)a * p.proj.memory);
   ag.store(p, a);
 }
 
