@@ -57,7 +57,7 @@ __device__ __forceinline__ void ac_update(const Params &p, const ACParams &ac, A
   // u = representation_->read(ap): sequential sum / T, clamped
   double ua[T], vp[T];
 #pragma unroll
-  for (int j = 0; j < T; ++j) { ua[j] = actor[ag.pidx[j]]; vp[j] = critic[ag.pidx[j]]; }
+  for (int j = 0; j < T; ++j) { ua[j] = ld_tbl(actor + ag.pidx[j]); vp[j] = ld_tbl(critic + ag.pidx[j]); }
   double u = 0;
 #pragma unroll
   for (int j = 0; j < T; ++j) u += ua[j];
@@ -76,7 +76,7 @@ __device__ __forceinline__ void ac_update(const Params &p, const ACParams &ac, A
   else
   {
     for (int j = 0; j < T; ++j)                            // duplicate indices: sequential, clamped each time
-      actor[ag.pidx[j]] = clampd(actor[ag.pidx[j]] + dw, ac.action_min, ac.action_max);
+      actor[ag.pidx[j]] = clampd(ld_tbl(actor + ag.pidx[j]) + dw, ac.action_min, ac.action_max);
   }
   ag.dtblw += (uint32_t)T;                                  // actor stores (the critic's are counted by sarsa_update)
   u_out = u;
@@ -103,7 +103,7 @@ __device__ __forceinline__ void ac_half(const Params &p, const ACParams &ac, Age
   project_obs<OBS, T>(p, obs, nidx, hash_out, (size_t)p.n);
   double wa[T], wc[T];
 #pragma unroll
-  for (int j = 0; j < T; ++j) { wa[j] = actor[nidx[j]]; wc[j] = critic[nidx[j]]; }
+  for (int j = 0; j < T; ++j) { wa[j] = ld_tbl(actor + nidx[j]); wc[j] = ld_tbl(critic + nidx[j]); }
   double pi = 0, vnext = 0;
 #pragma unroll
   for (int j = 0; j < T; ++j) { pi += wa[j]; vnext += wc[j]; }

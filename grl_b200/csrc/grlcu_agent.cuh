@@ -211,7 +211,7 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
       {
         const uint32_t ix = index_of(aa, j);
         sid[(aa * T + j) * kMaxBlock] = ix;
-        w[aa][j] = tbl[ix];
+        w[aa][j] = ld_tbl(tbl + ix);
       }
 #pragma unroll
     for (int aa = 0; aa < A - 1; ++aa)
@@ -230,12 +230,12 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
     {
       const uint32_t ix = index_of(A - 1, j);
       sid[((A - 1) * T + j) * kMaxBlock] = ix;
-      w[j] = tbl[ix];
+      w[j] = ld_tbl(tbl + ix);
     }
     if (WITH_P)
     {
 #pragma unroll
-      for (int j = 0; j < T; ++j) vp[j] = tbl[pidx[j]];
+      for (int j = 0; j < T; ++j) vp[j] = ld_tbl(tbl + pidx[j]);
     }
     double r = 0;
 #pragma unroll
@@ -365,7 +365,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
         for (int j = 0; j < T; ++j) ix[j] = ent[j * n];
 #pragma unroll
         for (int j = 0; j < T; ++j)
-          if (sw && ix[j] != kInvalidIndex) v[j] = tbl[ix[j]];
+          if (sw && ix[j] != kInvalidIndex) v[j] = ld_tbl(tbl + ix[j]);
 #pragma unroll
         for (int j = 0; j < T; ++j) v[j] += inc;
         if ((ag.dupmask >> k) & 1u)
@@ -400,7 +400,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
   }
   else
   {
-    for (int j = 0; j < T; ++j) tbl[ag.pidx[j]] += dw;        // sequential: duplicates accumulate
+    for (int j = 0; j < T; ++j) tbl[ag.pidx[j]] = ld_tbl(tbl + ag.pidx[j]) + dw;   // sequential: duplicates accumulate
     if (p.trace_kind != 0)
     {
       // Representation::update(trace, ...) (representation.h:79-83): newest -> oldest
@@ -412,7 +412,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
         for (int j = 0; j < T; ++j)
         {
           uint32_t ix = ent[j * n];
-          if (ix != kInvalidIndex) { tbl[ix] += inc; ++swept; }
+          if (ix != kInvalidIndex) { tbl[ix] = ld_tbl(tbl + ix) + inc; ++swept; }
         }
         weight *= e;
       }

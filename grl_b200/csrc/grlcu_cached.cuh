@@ -91,7 +91,7 @@ __device__ __forceinline__ void cache_open(const Params &p, Agent<DYN, T> &ag, c
     for (int j = 0; j < T; ++j)
       if ((m >> j) & 1u)
       {
-        c.val(pos * T + j) = tbl[ix[j]];
+        c.val(pos * T + j) = ld_tbl(tbl + ix[j]);
         tbl[ix[j]] = make_sentinel(pos * T + j);
       }
   }

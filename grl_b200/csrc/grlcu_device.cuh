@@ -17,6 +17,17 @@ constexpr int kMaxDims = 8;
 enum { STREAM_ACT = 0, STREAM_START = 1, STREAM_TABLE = 2, STREAM_TEST_ACT = 3,
        STREAM_ACTOR_TABLE = 4, STREAM_NOISE = 5 };
 
+// Gather of one hashed table word.  A plain ld.global of a random 8-byte word makes L2 fetch the whole
+// 128-byte line from DRAM (127 B per access measured); the .L2::64B prefetch-size qualifier halves that
+// (63.8 B per access, profiles/r01_randbench3_ncu.txt) -- and DRAM bytes are what this path runs out of.
+// volatile + "memory": the gathers keep their program order with respect to the table stores of the update.
+__device__ __forceinline__ double ld_tbl(const double *p)
+{
+  double v;
+  asm volatile("ld.global.L2::64B.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // ---- Philox4x32-10 (Salmon et al., SC'11) -------------------------------------------------
 struct Philox4 { uint32_t w[4]; };
 

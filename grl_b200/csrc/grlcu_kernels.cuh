@@ -156,7 +156,7 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, co
     if (!test)
     {
 #pragma unroll
-      for (int j = 0; j < T; ++j) vp[j] = tbl[ag.pidx[j]];
+      for (int j = 0; j < T; ++j) vp[j] = ld_tbl(tbl + ag.pidx[j]);
       if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, tbl, reward, false, 0., vp, qp, target, delta, swept);
       else sarsa_update<DYN, T>(p, ag, tbl, a, reward, false, 0., vp, qp, target, delta, swept);
     }
