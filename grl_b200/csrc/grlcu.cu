@@ -203,6 +203,11 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   }
 
   const size_t n = (size_t)n_agents, T = (size_t)cfg->tilings;
+  if (n * T * (size_t)p.trace_cap >= (1ull << 31))
+  {
+    delete c;
+    return fail(GRLCU_ERR_UNSUPPORTED, "n_agents * tilings * trace capacity (%d) must stay below 2^31 per context", p.trace_cap);
+  }
   int r = 0;
   if (!r) r = dalloc(c, &p.table, n * (size_t)cfg->memory);
   memset(&c->ac, 0, sizeof(c->ac));

@@ -178,41 +178,42 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
 {
   constexpr int OBS = Dyn<DYN>::OBS;
   const uint32_t m = 0x5bd1e995u;
-  int32_t qz[OBS];
-#pragma unroll
-  for (int i = 0; i < OBS; ++i) qz[i] = (int32_t)floor(obs[i] * p.proj.scaling[i]);
-  uint32_t pre[T];
-#pragma unroll
-  for (int j = 0; j < T; ++j)
+  // Phase 1: the A*T indices into the stash.  Pure integer work, rolled over the tilings on purpose: unrolled it
+  // is ~100 KB of SASS per call site and the fused kernels are instruction-fetch bound.
   {
-    uint32_t h = 449u ^ (uint32_t)(OBS + 2);
+    int32_t qz[OBS];
 #pragma unroll
-    for (int i = 0; i < OBS; ++i)
+    for (int i = 0; i < OBS; ++i) qz[i] = (int32_t)floor(obs[i] * p.proj.scaling[i]);
+#pragma unroll 1
+    for (int j = 0; j < T; ++j)
     {
-      int32_t c = qz[i] - safe_mod(qz[i] - j * (1 + 2 * i), T);
-      if (p.proj.wrap[i] != 0) c = safe_mod(c, p.proj.wrap[i]);
-      h = (h * m) ^ murmur_mix((uint32_t)c);
+      uint32_t h = 449u ^ (uint32_t)(OBS + 2);
+#pragma unroll
+      for (int i = 0; i < OBS; ++i)
+      {
+        int32_t c = qz[i] - safe_mod(qz[i] - j * (1 + 2 * i), T);
+        if (p.proj.wrap[i] != 0) c = safe_mod(c, p.proj.wrap[i]);
+        h = (h * m) ^ murmur_mix((uint32_t)c);
+      }
+#pragma unroll
+      for (int aa = 0; aa < A; ++aa)
+      {
+        uint32_t g = (h * m) ^ p.kact[aa][j];
+        g = (g * m) ^ p.kj[j];
+        g ^= g >> 13; g *= m; g ^= g >> 15;
+        if (hash_out) hash_out[((size_t)aa * T + j) * n + a] = g;
+        sid[(aa * T + j) * kMaxBlock] = reduce_index(p, g);
+      }
     }
-    pre[j] = h;
   }
-  auto index_of = [&](int aa, int j) -> uint32_t {
-    uint32_t h = (pre[j] * m) ^ p.kact[aa][j];
-    h = (h * m) ^ p.kj[j];
-    h ^= h >> 13; h *= m; h ^= h >> 15;
-    if (hash_out) hash_out[((size_t)aa * T + j) * n + a] = h;
-    return reduce_index(p, h);
-  };
+  // Phase 2: the gathers, issued in two groups (actions 0..A-2, then action A-1 together with p's T words) to
+  // bound the registers holding loads in flight.
   {
     double w[A - 1][T];
 #pragma unroll
     for (int aa = 0; aa < A - 1; ++aa)
 #pragma unroll
-      for (int j = 0; j < T; ++j)
-      {
-        const uint32_t ix = index_of(aa, j);
-        sid[(aa * T + j) * kMaxBlock] = ix;
-        w[aa][j] = ld_tbl(tbl + ix);
-      }
+      for (int j = 0; j < T; ++j) w[aa][j] = ld_tbl(tbl + sid[(aa * T + j) * kMaxBlock]);
 #pragma unroll
     for (int aa = 0; aa < A - 1; ++aa)
     {
@@ -222,16 +223,10 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
       q[aa] = r / T;    // clamp to +-DBL_MAX is the identity for finite values (linear.cpp:179-180)
     }
   }
-  asm volatile("" ::: "memory");
   {
     double w[T];
 #pragma unroll
-    for (int j = 0; j < T; ++j)
-    {
-      const uint32_t ix = index_of(A - 1, j);
-      sid[((A - 1) * T + j) * kMaxBlock] = ix;
-      w[j] = ld_tbl(tbl + ix);
-    }
+    for (int j = 0; j < T; ++j) w[j] = ld_tbl(tbl + sid[((A - 1) * T + j) * kMaxBlock]);
     if (WITH_P)
     {
 #pragma unroll
@@ -260,6 +255,57 @@ __device__ __forceinline__ bool has_duplicates(const uint32_t (&ix)[T])
 #pragma unroll
     for (int j = 0; j < i; ++j) dup |= (ix[i] == ix[j]);
   return dup;
+}
+
+// ---- duplicate indices inside one projection (a hash collision between tilings) -------------------------
+// Rare (about T*T/2 / memory per projection), so everything about them is kept out of line and rolled: the
+// fused kernels are instruction-fetch bound when their code does not fit the instruction cache.
+
+// bit j set: pidx[j] is the first occurrence of its index
+__device__ __noinline__ uint32_t dup_owner_mask(const uint32_t *pidx, int T)
+{
+  uint32_t owner = (1u << T) - 1u;
+#pragma unroll 1
+  for (int j = 1; j < T; ++j)
+#pragma unroll 1
+    for (int jj = 0; jj < j; ++jj)
+      if (((owner >> jj) & 1u) && pidx[jj] == pidx[j]) { owner &= ~(1u << j); break; }
+  return owner;
+}
+
+// 4 bits per tiling jj: how many later entries duplicate owner jj (T <= 16)
+__device__ __noinline__ uint64_t dup_counts(const uint32_t *pidx, uint32_t owner, int T)
+{
+  uint64_t counts = 0;
+#pragma unroll 1
+  for (int j = 1; j < T; ++j)
+    if (!((owner >> j) & 1u))
+#pragma unroll 1
+      for (int jj = 0; jj < j; ++jj)
+        if (((owner >> jj) & 1u) && pidx[jj] == pidx[j]) { counts += 1ull << (4 * jj); break; }
+  return counts;
+}
+
+// 4 bits per tiling j: how many earlier tilings hold the same (valid) index
+__device__ __noinline__ uint64_t dup_prior_counts(const uint32_t *ix, int T)
+{
+  uint64_t counts = 0;
+#pragma unroll 1
+  for (int j = 1; j < T; ++j)
+    if (ix[j] != kInvalidIndex)
+#pragma unroll 1
+      for (int jj = 0; jj < j; ++jj)
+        if (ix[jj] == ix[j]) counts += 1ull << (4 * j);
+  return counts;
+}
+
+// the owner (first occurrence) of the index at tiling j
+__device__ __noinline__ int dup_owner_of(const uint32_t *pidx, uint32_t owner, int j)
+{
+#pragma unroll 1
+  for (int jj = 0; jj < j; ++jj)
+    if (((owner >> jj) & 1u) && pidx[jj] == pidx[j]) return jj;
+  return j;
 }
 
 // Install the projection chosen by the policy (read back from the index stash) as the agent's
@@ -337,15 +383,11 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
     {
       // p holds duplicate indices (hash collision between tilings): the reference adds dw once per
       // occurrence, one after the other.  The last occurrence's store carries the full sum and lands last.
+      uint32_t lp[T];
 #pragma unroll
-      for (int j = 0; j < T; ++j)
-      {
-        double v = vp[j] + dw;
-#pragma unroll
-        for (int jj = 0; jj < j; ++jj)
-          if (ag.pidx[jj] == ag.pidx[j]) v += dw;
-        tbl[ag.pidx[j]] = v;
-      }
+      for (int j = 0; j < T; ++j) lp[j] = ag.pidx[j];
+#pragma unroll 1
+      for (int j = 0; j < T; ++j) tbl[lp[j]] = ld_tbl(tbl + lp[j]) + dw;
     }
     if (p.trace_kind == 1)
     {
@@ -371,11 +413,13 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
         if ((ag.dupmask >> k) & 1u)
         {
           // duplicate indices inside this entry: one more sequential += inc per earlier occurrence
+          uint32_t lx[T];
 #pragma unroll
-          for (int j = T - 1; j > 0; --j)
+          for (int j = 0; j < T; ++j) lx[j] = ix[j];
+          const uint64_t prior = dup_prior_counts(lx, T);
 #pragma unroll
-            for (int jj = 0; jj < j; ++jj)
-              if (ix[jj] == ix[j] && ix[j] != kInvalidIndex) v[j] += inc;
+          for (int j = 1; j < T; ++j)
+            for (int r = (int)((prior >> (4 * j)) & 15u); r > 0; --r) v[j] += inc;
         }
 #pragma unroll
         for (int j = 0; j < T; ++j)

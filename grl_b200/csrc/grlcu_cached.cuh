@@ -40,11 +40,29 @@ struct Cache
   double   *cv;      // + a
   uint32_t *vmask;   // + a
   uint32_t *ring;    // trace_idx + a
-  size_t    n;
-  __device__ __forceinline__ double &val(int slot) const { return cv[(size_t)slot * n]; }
-  __device__ __forceinline__ uint32_t &mask(int pos) const { return vmask[(size_t)pos * n]; }
-  __device__ __forceinline__ uint32_t &idx(int pos, int j) const { return ring[((size_t)pos * T + j) * n]; }
+  uint32_t  n;       // element indices fit 32 bits: trace_cap * T * n < 2^31 is checked by grlcu_create
+  __device__ __forceinline__ double &val(int slot) const { return cv[(uint32_t)slot * n]; }
+  __device__ __forceinline__ uint32_t &mask(int pos) const { return vmask[(uint32_t)pos * n]; }
+  __device__ __forceinline__ uint32_t &idx(int pos, int j) const { return ring[(uint32_t)(pos * T + j) * n]; }
 };
+
+// 4 bits per slot jj of ring entry `pos`: how many alias slots of the entry duplicate the (valid) slot jj
+template <int T>
+__device__ __noinline__ uint64_t alias_counts(const Cache<T> &c, int pos, uint32_t m)
+{
+  uint64_t counts = 0;
+#pragma unroll 1
+  for (int j = 1; j < T; ++j)
+  {
+    const uint32_t x = c.idx(pos, j);
+    if (!((m >> j) & 1u) && x != kInvalidIndex && (x & kAliasBit))
+    {
+      const int jj = (int)(x & 15u);
+      if ((m >> jj) & 1u) counts += 1ull << (4 * jj);
+    }
+  }
+  return counts;
+}
 
 // table read through the directory
 template <int T>
@@ -55,7 +73,7 @@ __device__ __forceinline__ double resolve(const Cache<T> &c, double raw)
 
 // Write the cached values of one entry back into the table (plain representation).
 template <int T>
-__device__ __forceinline__ uint32_t flush_entry(const Cache<T> &c, double *tbl, int pos)
+__device__ __noinline__ uint32_t flush_entry(const Cache<T> c, double *tbl, int pos)
 {
   const uint32_t m = c.mask(pos);
 #pragma unroll
@@ -67,26 +85,27 @@ __device__ __forceinline__ uint32_t flush_entry(const Cache<T> &c, double *tbl, 
 // Kernel entry: the ring is in the plain representation (kInvalidIndex = invalidated).  Build the valid
 // masks, fold duplicate indices inside an entry onto their first occurrence, pull the cached weights out
 // of the table and leave sentinels behind.
-template <int DYN, int T>
-__device__ __forceinline__ void cache_open(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+template <int T>
+__device__ __noinline__ uint32_t cache_open_core(const Cache<T> c, double *tbl, int cap, int head, int len, uint32_t dupmask)
 {
-  for (int k = 0; k < ag.len; ++k)
+  uint32_t stores = 0;
+  for (int k = 0; k < len; ++k)
   {
-    const int pos = ring_pos(ag.head, k, p.trace_cap);
+    const int pos = ring_pos(head, k, cap);
     uint32_t ix[T];
     uint32_t m = 0;
 #pragma unroll
     for (int j = 0; j < T; ++j) { ix[j] = c.idx(pos, j); if (ix[j] != kInvalidIndex) m |= 1u << j; }
-    if ((ag.dupmask >> k) & 1u)
+    if ((dupmask >> k) & 1u)
     {
-#pragma unroll
+#pragma unroll 1
       for (int j = 1; j < T; ++j)
-#pragma unroll
+#pragma unroll 1
         for (int jj = j - 1; jj >= 0; --jj)
           if (((m >> j) & 1u) && ((m >> jj) & 1u) && ix[j] == ix[jj]) { m &= ~(1u << j); c.idx(pos, j) = kAliasBit | (uint32_t)jj; }
     }
     c.mask(pos) = m;
-    ag.dtblw += (uint32_t)__popc(m);
+    stores += (uint32_t)__popc(m);
 #pragma unroll
     for (int j = 0; j < T; ++j)
       if ((m >> j) & 1u)
@@ -95,18 +114,26 @@ __device__ __forceinline__ void cache_open(const Params &p, Agent<DYN, T> &ag, c
         tbl[ix[j]] = make_sentinel(pos * T + j);
       }
   }
+  return stores;
+}
+
+template <int DYN, int T>
+__device__ __forceinline__ void cache_open(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+{
+  ag.dtblw += cache_open_core<T>(c, tbl, p.trace_cap, ag.head, ag.len, ag.dupmask);
 }
 
 // Kernel exit: back to the plain representation (values in the table, kInvalidIndex in the ring for
 // invalidated slots, alias slots showing the index they duplicate).
-template <int DYN, int T>
-__device__ __forceinline__ void cache_close(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+template <int T>
+__device__ __noinline__ uint32_t cache_close_core(const Cache<T> c, double *tbl, int cap, int head, int len)
 {
-  for (int k = 0; k < ag.len; ++k)
+  uint32_t stores = 0;
+  for (int k = 0; k < len; ++k)
   {
-    const int pos = ring_pos(ag.head, k, p.trace_cap);
+    const int pos = ring_pos(head, k, cap);
     const uint32_t m = c.mask(pos);
-    ag.dtblw += (uint32_t)__popc(m);
+    stores += (uint32_t)__popc(m);
 #pragma unroll
     for (int j = 0; j < T; ++j)
     {
@@ -120,13 +147,28 @@ __device__ __forceinline__ void cache_close(const Params &p, Agent<DYN, T> &ag, 
       else c.idx(pos, j) = kInvalidIndex;
     }
   }
+  return stores;
+}
+
+template <int DYN, int T>
+__device__ __forceinline__ void cache_close(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
+{
+  ag.dtblw += cache_close_core<T>(c, tbl, p.trace_cap, ag.head, ag.len);
 }
 
 // trace.clear() (sarsa.cpp:126-132 via TDAgent::start): cached weights go back to the table.
+template <int T>
+__device__ __noinline__ uint32_t cache_clear_core(const Cache<T> c, double *tbl, int cap, int head, int len)
+{
+  uint32_t stores = 0;
+  for (int k = 0; k < len; ++k) stores += flush_entry<T>(c, tbl, ring_pos(head, k, cap));
+  return stores;
+}
+
 template <int DYN, int T>
 __device__ __forceinline__ void cache_clear(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl)
 {
-  for (int k = 0; k < ag.len; ++k) ag.dtblw += flush_entry<T>(c, tbl, ring_pos(ag.head, k, p.trace_cap));
+  if (ag.len > 0) ag.dtblw += cache_clear_core<T>(c, tbl, p.trace_cap, ag.head, ag.len);
   ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0;
 }
 
@@ -163,26 +205,22 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
 
   // write(p): += dw per occurrence, in tiling order.  Duplicates are folded onto the first occurrence.
   uint32_t owner = 0xFFFFu;                     // bit j: slot j owns its index (first occurrence)
+  uint64_t dups = 0;                            // 4 bits per owner: number of its duplicates
   if (pdup)
   {
+    uint32_t lp[T];
 #pragma unroll
-    for (int j = 1; j < T; ++j)
-#pragma unroll
-      for (int jj = 0; jj < j; ++jj)
-        if (((owner >> jj) & 1u) && ((owner >> j) & 1u) && ag.pidx[jj] == ag.pidx[j]) owner &= ~(1u << j);
+    for (int j = 0; j < T; ++j) lp[j] = ag.pidx[j];
+    owner = dup_owner_mask(lp, T);
+    dups = dup_counts(lp, owner, T);
   }
 #pragma unroll
   for (int j = 0; j < T; ++j) np[j] += dw;
   if (pdup)
   {
 #pragma unroll
-    for (int j = 1; j < T; ++j)
-      if (!((owner >> j) & 1u))
-      {
-#pragma unroll
-        for (int jj = 0; jj < j; ++jj)
-          if (((owner >> jj) & 1u) && ag.pidx[jj] == ag.pidx[j]) np[jj] += dw;
-      }
+    for (int j = 0; j < T; ++j)
+      for (int r = (int)((dups >> (4 * j)) & 15u); r > 0; --r) np[j] += dw;
   }
   // indices that an older entry holds: that slot receives p's write now and the sweep's increment below
 #pragma unroll
@@ -209,21 +247,10 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
       if ((ag.dupmask >> k) & 1u)
       {
         // alias slots: one more sequential += inc on the slot they duplicate (if it is still valid)
+        const uint64_t ac_ = alias_counts<T>(c, pos, m);
 #pragma unroll
-        for (int j = 1; j < T; ++j)
-        {
-          const uint32_t x = c.idx(pos, j);
-          if (!((m >> j) & 1u) && x != kInvalidIndex && (x & kAliasBit))
-          {
-            const int jj = (int)(x & 15u);
-            if ((m >> jj) & 1u)
-            {
-#pragma unroll
-              for (int t = 0; t < T; ++t) if (t == jj) v[t] += inc;
-              ++swept;
-            }
-          }
-        }
+        for (int j = 0; j < T; ++j)
+          for (int r = (int)((ac_ >> (4 * j)) & 15u); r > 0; --r) { v[j] += inc; ++swept; }
       }
 #pragma unroll
       for (int j = 0; j < T; ++j)
@@ -249,19 +276,22 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
 #pragma unroll
     for (int j = 0; j < T; ++j)
     {
-      uint32_t x = ag.pidx[j];
+      const uint32_t x = ag.pidx[j];
       if ((owner >> j) & 1u)
       {
         c.val(pos * T + j) = np[j];
         tbl[x] = make_sentinel(pos * T + j);
       }
-      else
-      {
-#pragma unroll
-        for (int jj = 0; jj < j; ++jj)
-          if (((owner >> jj) & 1u) && ag.pidx[jj] == ag.pidx[j]) x = kAliasBit | (uint32_t)jj;
-      }
       c.idx(pos, j) = x;
+    }
+    if (pdup)
+    {
+      uint32_t lp[T];
+#pragma unroll
+      for (int j = 0; j < T; ++j) lp[j] = ag.pidx[j];
+#pragma unroll 1
+      for (int j = 1; j < T; ++j)
+        if (!((owner >> j) & 1u)) c.idx(pos, j) = kAliasBit | (uint32_t)dup_owner_of(lp, owner, j);
     }
     c.mask(pos) = owner;
     ag.dtblw += (uint32_t)__popc(owner);           // directory sentinels written

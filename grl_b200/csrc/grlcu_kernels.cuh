@@ -204,7 +204,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
   double *tbl = p.table + (size_t)a * p.proj.memory;
   const uint64_t gid = (uint64_t)(p.first_id + a);
   Cache<T> c;
-  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (size_t)p.n;
+  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
   if (CACHED && do_open) cache_open<DYN, T>(p, ag, c, tbl);
 
   for (int64_t step = 0; step < n_steps; ++step)
@@ -264,7 +264,7 @@ __global__ void k_cache_close(Params p)
   Agent<DYN, T> ag;
   ag.load(p, a);
   Cache<T> c;
-  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (size_t)p.n;
+  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
   cache_close<DYN, T>(p, ag, c, p.table + (size_t)a * p.proj.memory);
   ag.store(p, a);
 }
