@@ -171,10 +171,10 @@ struct Agent
 // Indices go to the shared-memory stash `sid` (element (aa*T+j) at sid[(aa*T+j)*kMaxBlock]).
 // The gathers are issued in two groups (actions 0..A-2, then action A-1 together with the T entries of
 // the previous projection p) to bound the registers holding loads in flight.
-template <int DYN, int T, int A, bool WITH_P, typename Resolve>
+template <int DYN, int T, int A, typename Resolve>
 __device__ __forceinline__ void q_values(const Params &p, const double *tbl, const double (&obs)[Dyn<DYN>::OBS],
                                          uint32_t *sid, double (&q)[A], const uint32_t (&pidx)[T],
-                                         double (&vp)[T], uint32_t *hash_out, int n, int a, Resolve resolve)
+                                         double (&vp)[T], bool with_p, uint32_t *hash_out, int n, int a, Resolve resolve)
 {
   constexpr int OBS = Dyn<DYN>::OBS;
   const uint32_t m = 0x5bd1e995u;
@@ -227,7 +227,7 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
     double w[T];
 #pragma unroll
     for (int j = 0; j < T; ++j) w[j] = ld_tbl(tbl + sid[((A - 1) * T + j) * kMaxBlock]);
-    if (WITH_P)
+    if (with_p)
     {
 #pragma unroll
       for (int j = 0; j < T; ++j) vp[j] = ld_tbl(tbl + pidx[j]);

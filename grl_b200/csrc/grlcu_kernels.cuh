@@ -107,14 +107,65 @@ template <int T> struct CacheResolve
   __device__ __forceinline__ double operator()(double v) const { return resolve<T>(c, v); }
 };
 
+// The agent's part of one loop iteration, written ONCE (the fused kernels are instruction-fetch bound, so the
+// episode-start and the step/end paths share one copy of the hashing, the gathers and the update):
+//   act   : there is a next action to choose (TDAgent::start / step; false for TDAgent::end, td.cpp:76-81)
+//   learn : there is a transition to learn from (TDAgent::step / end of a learning episode, td.cpp:63-81)
+// Returns the policy's own action choice (-1 when !act); commits `force` instead when force >= 0 (replay).
+template <int DYN, int T, int A, bool CACHED>
+__device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
+                                          uint32_t *sid, int a,
+                                          const double (&obs)[Dyn<DYN>::OBS], double reward, bool act, bool learn,
+                                          bool test, const Draws &d, int force, uint32_t *hash_out, double *o_q,
+                                          double &qp, double &target, double &delta, int &swept)
+{
+  qp = target = delta = 0; swept = 0;
+  double vp[T];
+  double qn = 0;
+  int own = -1, ai = 0;
+  if (act)
+  {
+    // act on the new observation first (td.cpp:63-74), then update with (s,a,r,s',a')
+    double q[A];
+    if (CACHED) q_values<DYN, T, A>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, p.n, a, CacheResolve<T>{c});
+    else q_values<DYN, T, A>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, p.n, a, NoResolve());
+    own = sample_action<A>(q, d, ag.epsilon, test);
+    ai = force >= 0 ? force : own;
+    if (o_q)
+    {
+#pragma unroll
+      for (int aa = 0; aa < A; ++aa) o_q[(size_t)aa * p.n + a] = q[aa];
+    }
+    qn = q[0];
+#pragma unroll
+    for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
+  }
+  else if (learn)
+  {
+#pragma unroll
+    for (int j = 0; j < T; ++j) vp[j] = ld_tbl(tbl + ag.pidx[j]);
+  }
+  if (learn)
+  {
+    if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, tbl, reward, act, qn, vp, qp, target, delta, swept);
+    else sarsa_update<DYN, T>(p, ag, tbl, a, reward, act, qn, vp, qp, target, delta, swept);
+  }
+  if (act)
+  {
+    set_prev_projection<DYN, T>(ag, sid, ai);
+    ag.action = p.actions[ai];
+  }
+  return own;
+}
+
 // Episode start (online_learning.cpp:160-178): observe the start state, TDAgent::start /
-// FixedAgent::start (trace clear + first act).
+// FixedAgent::start (trace clear + first act).  Used by the replay kernel; k_run inlines the same sequence.
 template <int DYN, int T, int A, bool CACHED>
 __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                               uint32_t *sid, int a, const Draws &d, bool test, double *o_q, int *o_ai)
 {
   constexpr int OBS = Dyn<DYN>::OBS;
-  double obs[OBS], q[A], vp[T];
+  double obs[OBS];
   int term;
   observe<DYN>(ag.x, p.timeout, obs, term);
   if (!test)
@@ -123,24 +174,15 @@ __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag
     if (CACHED) cache_clear<DYN, T>(p, ag, c, tbl);
     else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
   }
-  if (CACHED) q_values<DYN, T, A, false>(p, tbl, obs, sid, q, ag.pidx, vp, nullptr, p.n, a, CacheResolve<T>{c});
-  else q_values<DYN, T, A, false>(p, tbl, obs, sid, q, ag.pidx, vp, nullptr, p.n, a, NoResolve());
-  const int ai = sample_action<A>(q, d, ag.epsilon, test);
-  ag.action = p.actions[ai];
   ag.total_reward = 0;
   ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
-  set_prev_projection<DYN, T>(ag, sid, ai);
-  if (o_q)
-  {
-#pragma unroll
-    for (int aa = 0; aa < A; ++aa) o_q[(size_t)aa * p.n + a] = q[aa];
-  }
+  double qp, target, delta; int swept;
+  const int ai = agent_core<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, 0., true, false, test, d, -1, nullptr, o_q,
+                                               qp, target, delta, swept);
   if (o_ai) *o_ai = ai;
 }
 
 // The agent half of one step (TDAgent::step / end, td.cpp:63-81; FixedAgent for test episodes).
-// Returns the policy's own action choice (-1 when the observation is absorbing); commits `force`
-// instead when force >= 0 (replay mode).
 template <int DYN, int T, int A, bool CACHED>
 __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                           uint32_t *sid, int a,
@@ -148,42 +190,8 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, co
                                           const Draws &d, int force, uint32_t *hash_out, double *o_q,
                                           double &qp, double &target, double &delta, int &swept)
 {
-  qp = target = delta = 0; swept = 0;
-  double vp[T];
-  if (terminal == 2)
-  {
-    // TDAgent::end (td.cpp:76-81): update without bootstrap
-    if (!test)
-    {
-#pragma unroll
-      for (int j = 0; j < T; ++j) vp[j] = ld_tbl(tbl + ag.pidx[j]);
-      if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, tbl, reward, false, 0., vp, qp, target, delta, swept);
-      else sarsa_update<DYN, T>(p, ag, tbl, a, reward, false, 0., vp, qp, target, delta, swept);
-    }
-    return -1;
-  }
-  // TDAgent::step (td.cpp:63-74): act on the new observation, then update with (s,a,r,s',a')
-  double q[A];
-  if (CACHED) q_values<DYN, T, A, true>(p, tbl, obs, sid, q, ag.pidx, vp, hash_out, p.n, a, CacheResolve<T>{c});
-  else q_values<DYN, T, A, true>(p, tbl, obs, sid, q, ag.pidx, vp, hash_out, p.n, a, NoResolve());
-  const int own = sample_action<A>(q, d, ag.epsilon, test);
-  const int ai = force >= 0 ? force : own;
-  if (o_q)
-  {
-#pragma unroll
-    for (int aa = 0; aa < A; ++aa) o_q[(size_t)aa * p.n + a] = q[aa];
-  }
-  double qn = q[0];
-#pragma unroll
-  for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
-  if (!test)
-  {
-    if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, tbl, reward, true, qn, vp, qp, target, delta, swept);
-    else sarsa_update<DYN, T>(p, ag, tbl, a, reward, true, qn, vp, qp, target, delta, swept);
-  }
-  set_prev_projection<DYN, T>(ag, sid, ai);
-  ag.action = p.actions[ai];
-  return own;
+  return agent_core<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !test, test, d, force,
+                                       hash_out, o_q, qp, target, delta, swept);
 }
 
 // Fused K1-K4: each thread owns one agent and runs n_steps iterations of the hot loop with the
@@ -207,12 +215,19 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
   c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
   if (CACHED && do_open) cache_open<DYN, T>(p, ag, c, tbl);
 
-  for (int64_t step = 0; step < n_steps; ++step)
+  // One loop iteration is either an episode start (observe the start state, first action; consumes no step) or
+  // one environment step + TDAgent::step/end.  Both go through the single agent_core call below.
+  for (int64_t step = 0; step < n_steps;)
   {
-    if (!(ag.flags & 1))
+    const bool starting = !(ag.flags & 1);
+    double obs[OBS];
+    double reward = 0;
+    int terminal = 0;
+    bool test;
+    if (starting)
     {
-      const bool test = p.test_interval >= 0 &&
-                        p.tt[a] % (uint64_t)(p.test_interval + 1) == (uint64_t)p.test_interval;
+      // online_learning.cpp:160-178
+      test = p.test_interval >= 0 && p.tt[a] % (uint64_t)(p.test_interval + 1) == (uint64_t)p.test_interval;
       const uint64_t ep = p.episode_ctr[a];
       p.episode_ctr[a] = ep + 1;
       if (p.start_override && (ag.flags & 4))
@@ -225,30 +240,43 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
         Philox4 w = philox_for(p.seed, gid, STREAM_START, ep);
         task_start<DYN>(u53(w.w[0], w.w[1]), p.randomization, test ? 1 : 0, ag.x);
       }
-      const Draws d = next_draws<DYN, T>(p, ag, a, gid, test);
-      episode_start<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, d, test, nullptr, nullptr);
+      int term0;
+      observe<DYN>(ag.x, p.timeout, obs, term0);
+      if (!test)
+      {
+        // predictor finalize -> trace clear
+        if (CACHED) cache_clear<DYN, T>(p, ag, c, tbl);
+        else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
+      }
+      ag.total_reward = 0;
+      ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
     }
-    const bool test = (ag.flags & 2) != 0;
-
-    // ModeledEnvironment::step (modeled.cpp:160-213)
-    double next[S], obs[OBS];
-    int terminal;
+    else
+    {
+      // ModeledEnvironment::step (modeled.cpp:160-213)
+      test = (ag.flags & 2) != 0;
+      double next[S];
 #pragma unroll
-    for (int i = 0; i < S; ++i) next[i] = ag.x[i];
-    rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(ag.action), next);
-    observe<DYN>(next, p.timeout, obs, terminal);
-    const double reward = evaluate<DYN>(ag.x, ag.action, next);
-    ag.total_reward += reward;
+      for (int i = 0; i < S; ++i) next[i] = ag.x[i];
+      rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(ag.action), next);
+      observe<DYN>(next, p.timeout, obs, terminal);
+      reward = evaluate<DYN>(ag.x, ag.action, next);
+      ag.total_reward += reward;
 #pragma unroll
-    for (int i = 0; i < S; ++i) ag.x[i] = next[i];
+      for (int i = 0; i < S; ++i) ag.x[i] = next[i];
+    }
 
     double qp, target, delta; int swept;
     Draws d; d.u = 1.; d.r_explore = 0; d.r_tie = 0;
     if (terminal != 2) d = next_draws<DYN, T>(p, ag, a, gid, test);
-    agent_half<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, reward, terminal, test, d, -1, nullptr, nullptr,
-                                  qp, target, delta, swept);
-    if (!test) ag.dsteps++;
-    if (terminal) ag.episode_end(p, a, test);
+    agent_core<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !starting && !test, test, d, -1,
+                                  nullptr, nullptr, qp, target, delta, swept);
+    if (!starting)
+    {
+      if (!test) ag.dsteps++;
+      if (terminal) ag.episode_end(p, a, test);
+      ++step;
+    }
   }
   if (CACHED && do_close) cache_close<DYN, T>(p, ag, c, tbl);
   ag.store(p, a);
