@@ -124,6 +124,7 @@ def load(build=True):
     if _lib is not None:
         return _lib
     path = _build.build() if build else _build.LIB
+    path = os.environ.get("GRLCU_LIB", path)      # A/B of two builds of this same library (tools/gpu_*.sh)
     if not os.path.exists(path):
         raise GrlcuError("libgrlcu.so is missing (%s): run grl_b200/build.py; there is no CPU fallback" % path)
     L = C.CDLL(path)

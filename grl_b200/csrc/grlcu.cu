@@ -44,6 +44,7 @@ struct grlcu_ctx
   std::vector<void *> allocs;
   double *d_alpha, *d_lambda, *d_epsilon, *d_start;
   int64_t launches;
+  int sm_count;
   bool cache_live;            // the trace value cache of the fused kernel is live (tables hold directory sentinels)
   // run-kernel timing (events recorded around every k_run launch)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending;
@@ -143,6 +144,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   c->launches = 0;
   c->cache_live = false;
   c->block = 64;
+  c->sm_count = 148;
+  cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
   if (const char *b = getenv("GRLCU_BLOCK")) { int v = atoi(b); if (v >= 32 && v <= kMaxBlock && v % 32 == 0) c->block = v; }
 
   Params &p = c->p;
@@ -317,7 +320,8 @@ static int ensure_plain(grlcu_ctx *c)
   if (!c->cache_live) return 0;
   const int blk = 64, grd = (c->p.n + blk - 1) / blk;
   if (c->cfg.dynamics == GRLCU_DYN_PENDULUM) k_cache_close<0, 16><<<grd, blk, 0, c->stream>>>(c->p);
-  else k_cache_close<1, 16><<<grd, blk, 0, c->stream>>>(c->p);
+  else if (c->cfg.dynamics == GRLCU_DYN_CART_POLE) k_cache_close<1, 16><<<grd, blk, 0, c->stream>>>(c->p);
+  else k_cache_close<2, 16><<<grd, blk, 0, c->stream>>>(c->p);
   c->launches++;
   CU(cudaGetLastError());
   c->cache_live = false;
@@ -573,12 +577,23 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
     CU(cudaEventRecord(e0, c->stream));
     // the trace value cache applies to the replacing trace (unique owner slot per index)
     const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 32;
+    // at most 8 warps per SM: the 255-register instantiation (see k_run)
+    const int ctas_per_sm = (grd + c->sm_count - 1) / c->sm_count;
+    const bool roomy = ctas_per_sm * (c->block / 32) <= 8 && !getenv("GRLCU_MINB7");
 #define CALL(D)                                                                                    \
     do {                                                                                           \
-      if (cached) k_run<D, 16, 3, true><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
-      else k_run<D, 16, 3, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0);      \
+      if (cached && roomy) k_run<D, 16, 3, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
+      else if (cached) k_run<D, 16, 3, true, 7><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
+      else if (roomy) k_run<D, 16, 3, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0); \
+      else k_run<D, 16, 3, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0);      \
     } while (0)
-    if (c->cfg.algo == GRLCU_ALGO_AC) k_run_ac<2, 16><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps);
+    if (c->cfg.algo == GRLCU_ALGO_AC)
+    {
+      if (cached && roomy) k_run_ac<2, 16, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1);
+      else if (cached) k_run_ac<2, 16, true, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1);
+      else if (roomy) k_run_ac<2, 16, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0);
+      else k_run_ac<2, 16, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0);
+    }
     else DISPATCH_SARSA(c, CALL);
 #undef CALL
     if (cached && lazy && begin + cohort >= n) c->cache_live = true;

@@ -13,6 +13,7 @@
 // and on every read (linear.cpp:179-180).
 #pragma once
 #include "grlcu_agent.cuh"
+#include "grlcu_cached.cuh"
 
 namespace grlcu {
 
@@ -22,19 +23,20 @@ struct ACParams
   double  sigma, actor_alpha, action_min, action_max;
 };
 
-// TileCodingProjector::_project of an observation (no action coordinate): OBS + 1 ints per hash.
+// TileCodingProjector::_project of an observation (no action coordinate): OBS + 1 ints per hash.  Rolled over
+// the tilings (code size, see q_values); the indices go to the shared-memory stash sid[j * kMaxBlock].
 template <int OBS, int T>
-__device__ __forceinline__ void project_obs(const Params &p, const double (&obs)[OBS], uint32_t (&idx)[T],
+__device__ __forceinline__ void project_obs(const Params &p, const double (&obs)[OBS], uint32_t *sid,
                                             uint32_t *hash_out, size_t stride)
 {
   int32_t q[OBS];
   quantize<OBS, T>(p.proj, obs, q);
-#pragma unroll
+#pragma unroll 1
   for (int j = 0; j < T; ++j)
   {
     const uint32_t h = tile_hash_of<OBS, T>(p.proj, q, j);
     if (hash_out) hash_out[(size_t)j * stride] = h;
-    idx[j] = reduce_index(p, h);
+    sid[j * kMaxBlock] = reduce_index(p, h);
   }
 }
 
@@ -49,21 +51,22 @@ __device__ __forceinline__ double box_muller(double U1, double U2, double sigma)
 struct ACOut { double pi, vnext, u, action; };
 
 // ActionACPredictor::update for the transition (p, prev_action, reward [, s', a']).
-template <int DYN, int T>
-__device__ __forceinline__ void ac_update(const Params &p, const ACParams &ac, Agent<DYN, T> &ag, double *critic,
-                                          double *actor, int a, double reward, bool bootstrap, double vnext,
+//   ua[j] / vp[j]: actor / critic table words at pidx[j], read before any store of this step (vp raw: value or
+//   directory sentinel when CACHED).
+template <int DYN, int T, bool CACHED>
+__device__ __forceinline__ void ac_update(const Params &p, const ACParams &ac, Agent<DYN, T> &ag, const Cache<T> &c,
+                                          double *critic, double *actor, int a, double reward, bool bootstrap,
+                                          double vnext, const double (&ua)[T], const double (&vp)[T],
                                           double &u_out, double &qp, double &target, double &delta, int &swept)
 {
   // u = representation_->read(ap): sequential sum / T, clamped
-  double ua[T], vp[T];
-#pragma unroll
-  for (int j = 0; j < T; ++j) { ua[j] = ld_tbl(actor + ag.pidx[j]); vp[j] = ld_tbl(critic + ag.pidx[j]); }
   double u = 0;
 #pragma unroll
   for (int j = 0; j < T; ++j) u += ua[j];
   u = clampd(u / T, ac.action_min, ac.action_max);
   // critique = critic_->criticize(transition, u)
-  sarsa_update<DYN, T>(p, ag, critic, a, reward, bootstrap, vnext, vp, qp, target, delta, swept);
+  if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, critic, reward, bootstrap, vnext, vp, qp, target, delta, swept);
+  else sarsa_update<DYN, T>(p, ag, critic, a, reward, bootstrap, vnext, vp, qp, target, delta, swept);
   // delta = critique * (prev_action - u); target_u = u + delta; representation_->write(ap, target_u, alpha)
   const double du = delta * (ag.action - u);
   const double target_u = u + du;
@@ -75,92 +78,118 @@ __device__ __forceinline__ void ac_update(const Params &p, const ACParams &ac, A
   }
   else
   {
+    uint32_t lp[T];
+#pragma unroll
+    for (int j = 0; j < T; ++j) lp[j] = ag.pidx[j];
+#pragma unroll 1
     for (int j = 0; j < T; ++j)                            // duplicate indices: sequential, clamped each time
-      actor[ag.pidx[j]] = clampd(ld_tbl(actor + ag.pidx[j]) + dw, ac.action_min, ac.action_max);
+      actor[lp[j]] = clampd(ld_tbl(actor + lp[j]) + dw, ac.action_min, ac.action_max);
   }
   ag.dtblw += (uint32_t)T;                                  // actor stores (the critic's are counted by sarsa_update)
   u_out = u;
 }
 
-// ActionPolicy::act on obs (learning: with exploration noise n; test: sigma = 0) and, unless this is an
-// episode start, the update that TDAgent::step performs right after it.  have_n: n is supplied (replay).
-template <int DYN, int T>
-__device__ __forceinline__ void ac_half(const Params &p, const ACParams &ac, Agent<DYN, T> &ag, double *critic,
-                                        double *actor, int a, uint64_t gid, const double (&obs)[Dyn<DYN>::OBS],
-                                        double reward, int terminal, bool test, bool starting, bool have_n, double n_fed,
+// The agent's part of one loop iteration, written once (see agent_core in grlcu_kernels.cuh):
+//   act   : ActionPolicy::act on obs (learning: with exploration noise n; test: sigma = 0)
+//   learn : the update that TDAgent::step / end performs right after it
+// have_n: n is supplied (replay).
+template <int DYN, int T, bool CACHED>
+__device__ __forceinline__ void ac_core(const Params &p, const ACParams &ac, Agent<DYN, T> &ag, const Cache<T> &c,
+                                        double *critic, double *actor, uint32_t *sid, int a, uint64_t gid,
+                                        const double (&obs)[Dyn<DYN>::OBS], double reward, bool act, bool learn,
+                                        bool test, bool have_n, double n_fed,
                                         uint32_t *hash_out, uint32_t *index_out, ACOut &o, double &noise,
                                         double &qp, double &target, double &delta, int &swept)
 {
   constexpr int OBS = Dyn<DYN>::OBS;
   qp = target = delta = 0; swept = 0; noise = 0;
   o.pi = o.vnext = o.u = o.action = 0;
-  if (terminal == 2)
+  double pi = 0, vnext = 0, action = 0;
+  if (act)
   {
-    if (!test && !starting) ac_update<DYN, T>(p, ac, ag, critic, actor, a, reward, false, 0., o.u, qp, target, delta, swept);
-    return;
-  }
-  uint32_t nidx[T];
-  project_obs<OBS, T>(p, obs, nidx, hash_out, (size_t)p.n);
-  double wa[T], wc[T];
+    project_obs<OBS, T>(p, obs, sid, hash_out, (size_t)p.n);
+    double wa[T], wc[T];
 #pragma unroll
-  for (int j = 0; j < T; ++j) { wa[j] = ld_tbl(actor + nidx[j]); wc[j] = ld_tbl(critic + nidx[j]); }
-  double pi = 0, vnext = 0;
-#pragma unroll
-  for (int j = 0; j < T; ++j) { pi += wa[j]; vnext += wc[j]; }
-  pi = clampd(pi / T, ac.action_min, ac.action_max);
-  vnext /= T;
-  double out = pi;
-  if (!test && ac.sigma != 0.)
-  {
-    double n;
-    if (have_n) n = n_fed;
-    else
+    for (int j = 0; j < T; ++j)
     {
-      const Philox4 w = philox_for(p.seed, gid, STREAM_NOISE, ag.act_ctr);
-      n = (1 - 1.) * 0. + box_muller(u53(w.w[0], w.w[1]), u53(w.w[2], w.w[3]), 1. * ac.sigma);
+      const uint32_t x = sid[j * kMaxBlock];
+      wa[j] = ld_tbl(actor + x); wc[j] = ld_tbl(critic + x);
     }
-    ag.act_ctr++;
-    out += n;
-    noise = n;
-  }
-  const double action = clampd(out, ac.action_min, ac.action_max);
-  if (!test && !starting)
-    ac_update<DYN, T>(p, ac, ag, critic, actor, a, reward, true, vnext, o.u, qp, target, delta, swept);
 #pragma unroll
-  for (int j = 0; j < T; ++j) ag.pidx[j] = nidx[j];
-  ag.flags = (ag.flags & ~8) | (has_duplicates<T>(ag.pidx) ? 8 : 0);
-  ag.action = action;
-  if (index_out)
+    for (int j = 0; j < T; ++j) { pi += wa[j]; vnext += CACHED ? resolve<T>(c, wc[j]) : wc[j]; }
+    pi = clampd(pi / T, ac.action_min, ac.action_max);
+    vnext /= T;
+    double out = pi;
+    if (!test && ac.sigma != 0.)
+    {
+      double n;
+      if (have_n) n = n_fed;
+      else
+      {
+        const Philox4 w = philox_for(p.seed, gid, STREAM_NOISE, ag.act_ctr);
+        n = (1 - 1.) * 0. + box_muller(u53(w.w[0], w.w[1]), u53(w.w[2], w.w[3]), 1. * ac.sigma);
+      }
+      ag.act_ctr++;
+      out += n;
+      noise = n;
+    }
+    action = clampd(out, ac.action_min, ac.action_max);
+  }
+  if (learn)
+  {
+    double ua[T], vp[T];
+#pragma unroll
+    for (int j = 0; j < T; ++j) { ua[j] = ld_tbl(actor + ag.pidx[j]); vp[j] = ld_tbl(critic + ag.pidx[j]); }
+    ac_update<DYN, T, CACHED>(p, ac, ag, c, critic, actor, a, reward, act, vnext, ua, vp, o.u, qp, target, delta, swept);
+  }
+  if (act)
   {
 #pragma unroll
-    for (int j = 0; j < T; ++j) index_out[(size_t)j * p.n] = nidx[j];
+    for (int j = 0; j < T; ++j) ag.pidx[j] = sid[j * kMaxBlock];
+    ag.flags = (ag.flags & ~8) | (has_duplicates<T>(ag.pidx) ? 8 : 0);
+    ag.action = action;
+    if (index_out)
+    {
+#pragma unroll
+      for (int j = 0; j < T; ++j) index_out[(size_t)j * p.n] = ag.pidx[j];
+    }
+    o.pi = pi; o.vnext = vnext; o.action = action;
   }
-  o.pi = pi; o.vnext = vnext; o.action = action;
 }
 
 // Fused loop, one thread per agent: n_steps iterations of online_learning.cpp:186-221 with the AC agent.
-template <int DYN, int T>
-__global__ void __launch_bounds__(kMaxBlock, 7)
-k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps)
+// One loop iteration is an episode start (no step consumed) or one environment step + TDAgent::step/end.
+template <int DYN, int T, bool CACHED, int MINB>
+__global__ void __launch_bounds__(kMaxBlock, MINB)
+k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps, int do_open, int do_close)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
+  __shared__ uint32_t s_idx[T][kMaxBlock];
   const int a = agent_begin + blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= agent_end) return;
+  uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
   double *critic = p.table + (size_t)a * p.proj.memory;
   double *actor = ac.actor + (size_t)a * p.proj.memory;
   const uint64_t gid = (uint64_t)(p.first_id + a);
+  Cache<T> c;
+  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
+  if (CACHED && do_open) cache_open<DYN, T>(p, ag, c, critic);
   ACOut o;
   double noise, qp, target, delta;
   int swept;
 
-  for (int64_t step = 0; step < n_steps; ++step)
+  for (int64_t step = 0; step < n_steps;)
   {
-    if (!(ag.flags & 1))
+    const bool starting = !(ag.flags & 1);
+    double obs[OBS];
+    double reward = 0;
+    int terminal = 0;
+    bool test;
+    if (starting)
     {
-      const bool test = p.test_interval >= 0 &&
-                        p.tt[a] % (uint64_t)(p.test_interval + 1) == (uint64_t)p.test_interval;
+      test = p.test_interval >= 0 && p.tt[a] % (uint64_t)(p.test_interval + 1) == (uint64_t)p.test_interval;
       const uint64_t ep = p.episode_ctr[a];
       p.episode_ctr[a] = ep + 1;
       if (p.start_override && (ag.flags & 4))
@@ -173,31 +202,40 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps)
         Philox4 w = philox_for(p.seed, gid, STREAM_START, ep);
         task_start<DYN>(u53(w.w[0], w.w[1]), p.randomization, test ? 1 : 0, ag.x);
       }
-      double obs0[OBS];
       int term0;
-      observe<DYN>(ag.x, p.timeout, obs0, term0);
-      if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }     // TDAgent::start -> finalize -> trace clear
+      observe<DYN>(ag.x, p.timeout, obs, term0);
+      if (!test)
+      {
+        // TDAgent::start -> finalize -> trace clear
+        if (CACHED) cache_clear<DYN, T>(p, ag, c, critic);
+        else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
+      }
       ag.total_reward = 0;
       ag.flags = 1 | (test ? 2 : 0);
-      ac_half<DYN, T>(p, ac, ag, critic, actor, a, gid, obs0, 0., 0, test, true, false, 0., nullptr, nullptr, o, noise,
-                      qp, target, delta, swept);
     }
-    const bool test = (ag.flags & 2) != 0;
-    double next[S], obs[OBS];
-    int terminal;
+    else
+    {
+      test = (ag.flags & 2) != 0;
+      double next[S];
 #pragma unroll
-    for (int i = 0; i < S; ++i) next[i] = ag.x[i];
-    rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(ag.action), next);
-    observe<DYN>(next, p.timeout, obs, terminal);
-    const double reward = evaluate<DYN>(ag.x, ag.action, next);
-    ag.total_reward += reward;
+      for (int i = 0; i < S; ++i) next[i] = ag.x[i];
+      rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(ag.action), next);
+      observe<DYN>(next, p.timeout, obs, terminal);
+      reward = evaluate<DYN>(ag.x, ag.action, next);
+      ag.total_reward += reward;
 #pragma unroll
-    for (int i = 0; i < S; ++i) ag.x[i] = next[i];
-    ac_half<DYN, T>(p, ac, ag, critic, actor, a, gid, obs, reward, terminal, test, false, false, 0., nullptr, nullptr, o,
-                    noise, qp, target, delta, swept);
-    if (!test) ag.dsteps++;
-    if (terminal) ag.episode_end(p, a, test);
+      for (int i = 0; i < S; ++i) ag.x[i] = next[i];
+    }
+    ac_core<DYN, T, CACHED>(p, ac, ag, c, critic, actor, sid, a, gid, obs, reward, terminal != 2, !starting && !test,
+                            test, false, 0., nullptr, nullptr, o, noise, qp, target, delta, swept);
+    if (!starting)
+    {
+      if (!test) ag.dsteps++;
+      if (terminal) ag.episode_end(p, a, test);
+      ++step;
+    }
   }
+  if (CACHED && do_close) cache_close<DYN, T>(p, ag, c, critic);
   ag.store(p, a);
 }
 
@@ -210,9 +248,11 @@ __global__ void __launch_bounds__(kMaxBlock)
 k_replay_ac(Params p, ACParams ac, ReplayIO io)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
+  __shared__ uint32_t s_idx[T][kMaxBlock];
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = p.n;
   if (a >= n) return;
+  uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
   double *critic = p.table + (size_t)a * p.proj.memory;
@@ -233,8 +273,8 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
     if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
     ag.total_reward = 0;
     ag.flags = 1 | (test ? 2 : 0);
-    ac_half<DYN, T>(p, ac, ag, critic, actor, a, gid, obs0, 0., 0, test, true, true, io.start_u[a], nullptr, nullptr, o,
-                    noise, qp, target, delta, swept);
+    ac_core<DYN, T, false>(p, ac, ag, Cache<T>(), critic, actor, sid, a, gid, obs0, 0., true, false, test, true,
+                           io.start_u[a], nullptr, nullptr, o, noise, qp, target, delta, swept);
     if (io.o_start_q) { io.o_start_q[a] = o.pi; io.o_start_q[(size_t)3 * n + a] = o.action; }
     p.episode_ctr[a] += 1;
   }
@@ -260,9 +300,9 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
   terminal = io.terminal[a];
   ag.total_reward += reward;
   ag.action = act;                       // the action that was applied is the transition's prev_action
-  ac_half<DYN, T>(p, ac, ag, critic, actor, a, gid, obs, reward, terminal, test, false, true, io.u[a],
-                  io.o_hash ? io.o_hash + a : nullptr, io.o_index ? io.o_index + a : nullptr, o, noise,
-                  qp, target, delta, swept);
+  ac_core<DYN, T, false>(p, ac, ag, Cache<T>(), critic, actor, sid, a, gid, obs, reward, terminal != 2, !test, test,
+                         true, io.u[a], io.o_hash ? io.o_hash + a : nullptr, io.o_index ? io.o_index + a : nullptr, o,
+                         noise, qp, target, delta, swept);
   if (io.o_q)
   {
     io.o_q[a] = o.pi; io.o_q[(size_t)n + a] = o.vnext; io.o_q[(size_t)2 * n + a] = o.u; io.o_q[(size_t)3 * n + a] = o.action;

@@ -234,23 +234,31 @@ __device__ __forceinline__ void rk4(double tau, int steps, double u, double (&x)
   const double h = tau / steps;
   for (int ii = 0; ii < steps; ++ii)
   {
-    double xd[S], k1[S], k2[S], k3[S], k4[S], tmp[S];
-    Dyn<DYN>::eom(x, u, xd);
+    // The four stages go through ONE copy of the equations of motion (code size: the fused kernels are
+    // instruction-fetch bound).  Same arithmetic as the reference's integrator (modeled.cpp:254-276):
+    //   tmp = x + k/2 (stages 1,2: k * 0.5 == k / 2 exactly) or x + k (stage 3);
+    //   x += (((k1 + 2 k2) + 2 k3) + k4) / 6, summed in that order.
+    double tmp[S], acc[S];
 #pragma unroll
-    for (int i = 0; i < S; ++i) { k1[i] = h * xd[i]; tmp[i] = x[i] + k1[i] / 2; }
-    Dyn<DYN>::eom(tmp, u, xd);
-#pragma unroll
-    for (int i = 0; i < S; ++i) { k2[i] = h * xd[i]; tmp[i] = x[i] + k2[i] / 2; }
-    Dyn<DYN>::eom(tmp, u, xd);
-#pragma unroll
-    for (int i = 0; i < S; ++i) { k3[i] = h * xd[i]; tmp[i] = x[i] + k3[i]; }
-    Dyn<DYN>::eom(tmp, u, xd);
-#pragma unroll
-    for (int i = 0; i < S; ++i)
+    for (int i = 0; i < S; ++i) tmp[i] = x[i];
+    // (the pendulum's equations are a handful of instructions: unrolled there)
+#pragma unroll (DYN == 0 ? 4 : 1)
+    for (int stage = 0; stage < 4; ++stage)
     {
-      k4[i] = h * xd[i];
-      x[i] = x[i] + (((k1[i] + 2 * k2[i]) + 2 * k3[i]) + k4[i]) / 6;
+      double xd[S];
+      Dyn<DYN>::eom(tmp, u, xd);
+      const double cn = stage < 2 ? 0.5 : 1.;     // weight of this k in the next stage's argument
+      const double wk = (stage == 1 || stage == 2) ? 2. : 1.;
+#pragma unroll
+      for (int i = 0; i < S; ++i)
+      {
+        const double k = h * xd[i];
+        acc[i] = stage == 0 ? k : acc[i] + wk * k;
+        tmp[i] = x[i] + k * cn;
+      }
     }
+#pragma unroll
+    for (int i = 0; i < S; ++i) x[i] = x[i] + acc[i] / 6;
   }
 }
 

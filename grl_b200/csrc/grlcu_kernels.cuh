@@ -197,9 +197,12 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, co
 // Fused K1-K4: each thread owns one agent and runs n_steps iterations of the hot loop with the
 // agent's state in registers; only the hashed table and the trace ring are in memory.
 // 64 threads x 7 blocks per SM keeps all 65,536 agents of BASELINE configs[1] resident at once on
-// 148 SMs (448 threads/SM), which bounds the kernel at 144 registers per thread.
-template <int DYN, int T, int A, bool CACHED>
-__global__ void __launch_bounds__(kMaxBlock, 7)
+// 148 SMs (448 threads/SM = 14 warps/SM).  The register file is split over the SM's four sub-partitions,
+// so 14 warps means 4 warps on some of them and the kernel is bounded at 128 registers per thread
+// (MINB = 7).  Launches with at most 8 warps per SM (BASELINE configs[2], [3]: 32,768 agents) use the
+// MINB = 4 instantiation, which may use up to 255 registers and does not spill.
+template <int DYN, int T, int A, bool CACHED, int MINB>
+__global__ void __launch_bounds__(kMaxBlock, MINB)
 k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, int do_close)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;

@@ -21,6 +21,8 @@ def _run(G, mk, mode, n, launches, **kw):
             b.run(k)
         res = b.results()
         tables = np.stack([b.get_table(i) for i in range(n)])
+        if mk is G.cart_double_pole_ac_config:
+            tables = np.concatenate([tables, np.stack([b.get_actor_table(i) for i in range(n)])], axis=1)
         states = [b.get_state(i) for i in range(n)]
     finally:
         b.close()
@@ -35,14 +37,20 @@ def _run(G, mk, mode, n, launches, **kw):
     dict(which="cart_pole", n=32, memory=1031, launches=[400], test_interval=-1, epsilon=0.5),
     dict(which="pendulum", n=32, memory=8192, launches=[130], test_interval=-1, lambda_=0.0),  # decay < 0.01
     dict(which="pendulum", n=32, memory=8192, launches=[260], test_interval=-1, lambda_=0.9),  # long trace
+    # actor-critic (BASELINE configs[3]): the critic's trace goes through the cache, the actor table does not
+    dict(which="ac", n=64, memory=131072, launches=[90, 1, 310], test_interval=3),
+    dict(which="ac", n=32, memory=509, launches=[350], test_interval=-1, actor_alpha=0.5, sigma=15.0),
 ])
 def test_cached_equals_uncached(case):
     import grl_b200 as G
     case = dict(case)
-    mk = G.pendulum_config if case.pop("which") == "pendulum" else G.cart_pole_config
+    which = case.pop("which")
+    mk = {"pendulum": G.pendulum_config, "cart_pole": G.cart_pole_config, "ac": G.cart_double_pole_ac_config}[which]
     n, launches = case.pop("n"), case.pop("launches")
-    r1, t1, s1 = _run(G, mk, 1, n, launches, randomization=1.0, **case)
-    r0, t0, s0 = _run(G, mk, 0, n, launches, randomization=1.0, **case)
+    if which != "ac":
+        case["randomization"] = 1.0
+    r1, t1, s1 = _run(G, mk, 1, n, launches, **case)
+    r0, t0, s0 = _run(G, mk, 0, n, launches, **case)
     assert not np.isnan(t0).any()                      # no directory sentinel left in a table
     assert np.array_equal(t0, t1)
     for k in r0:
