@@ -301,7 +301,7 @@ def ours(args):
             with open(os.path.join(ROOT, "profiles", "random_access_ceilings.json")) as f:
                 ceil = json.load(f)
             ac = args.workload == "cart_double_pole_ac"
-            cached = args.workload in ("pendulum", "cart_pole", "cart_double_pole_ac") and os.environ.get("GRLCU_MODE", "0") == "0"
+            cached = args.workload in ("pendulum", "cart_pole", "cart_double_pole_ac", "sweep") and os.environ.get("GRLCU_MODE", "0") == "0"
             W = writes_all / max(steps_all, 1)
             R = (4 * 16 if ac else 3 * 16 + 16) + (0 if cached else V)      # cached path: the sweep runs on the dense cache
             floor_ns = R / ceil["read_G_per_s"] + W / ceil["write_G_per_s"]

@@ -576,7 +576,7 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
     cudaEvent_t e0 = get_event(c), e1 = get_event(c);
     CU(cudaEventRecord(e0, c->stream));
     // the trace value cache applies to the replacing trace (unique owner slot per index)
-    const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 32;
+    const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64;
     // at most 8 warps per SM: the 255-register instantiation (see k_run)
     const int ctas_per_sm = (grd + c->sm_count - 1) / c->sm_count;
     const bool roomy = ctas_per_sm * (c->block / 32) <= 8 && !getenv("GRLCU_MINB7");

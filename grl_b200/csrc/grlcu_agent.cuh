@@ -37,7 +37,7 @@ struct Params
   int32_t  *trace_len, *trace_head;
   double   *total_decay;
   int32_t  *flags;            // bit0 in_episode, bit1 test, bit2 start override pending, bit3 prev projection has duplicate indices
-  uint32_t *dupmask;          // bit k: trace entry of age k holds duplicate indices
+  uint64_t *dupmask;          // bit k: trace entry of age k holds duplicate indices (fast paths: cap <= 64)
   int32_t  force_slow;        // 1: always take the sequential update path (A/B testing)
   int32_t  mode;              // 0: trace value cache where eligible, 1: uncached
   double   *cache_val;        // [cap*T][n] cached trace weights (grlcu_cached.cuh)
@@ -119,7 +119,7 @@ struct Agent
   double   action;
   uint32_t pidx[T];
   int32_t  len, head, flags;
-  uint32_t dupmask;
+  uint64_t dupmask;
   double   total_decay, total_reward;
   uint64_t act_ctr;
   double   alpha, e, epsilon;       // e = gamma*lambda = pow(gamma*lambda, tau) for tau = 1
@@ -330,7 +330,7 @@ __device__ __forceinline__ void trace_push(const Params &p, Agent<DYN, T> &ag, u
 #pragma unroll
   for (int j = 0; j < T; ++j) dst[j * n] = ag.pidx[j];
   ag.len++;
-  ag.dupmask = (ag.dupmask << 1) | ((ag.flags & 8) ? 1u : 0u);
+  ag.dupmask = (ag.dupmask << 1) | ((ag.flags & 8) ? 1ull : 0ull);
   ag.total_decay *= e;
   while (ag.total_decay < dc && ag.len > 1) { ag.total_decay /= e; ag.len--; }
 }
@@ -369,7 +369,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
   const double e = ag.e;
   const double ad = ag.alpha * delta;
   const double dc = p.trace_kind == 1 ? 0.01 : 0.0001;
-  const bool fast = !p.force_slow && p.trace_kind != 2 && cap <= 32;
+  const bool fast = !p.force_slow && p.trace_kind != 2 && cap <= 64;
   int swept = 0;
 
   if (fast)
@@ -410,7 +410,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
           if (sw && ix[j] != kInvalidIndex) v[j] = ld_tbl(tbl + ix[j]);
 #pragma unroll
         for (int j = 0; j < T; ++j) v[j] += inc;
-        if ((ag.dupmask >> k) & 1u)
+        if ((ag.dupmask >> k) & 1ull)
         {
           // duplicate indices inside this entry: one more sequential += inc per earlier occurrence
           uint32_t lx[T];

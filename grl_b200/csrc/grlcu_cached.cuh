@@ -86,7 +86,7 @@ __device__ __noinline__ uint32_t flush_entry(const Cache<T> c, double *tbl, int 
 // masks, fold duplicate indices inside an entry onto their first occurrence, pull the cached weights out
 // of the table and leave sentinels behind.
 template <int T>
-__device__ __noinline__ uint32_t cache_open_core(const Cache<T> c, double *tbl, int cap, int head, int len, uint32_t dupmask)
+__device__ __noinline__ uint32_t cache_open_core(const Cache<T> c, double *tbl, int cap, int head, int len, uint64_t dupmask)
 {
   uint32_t stores = 0;
   for (int k = 0; k < len; ++k)
@@ -96,7 +96,7 @@ __device__ __noinline__ uint32_t cache_open_core(const Cache<T> c, double *tbl, 
     uint32_t m = 0;
 #pragma unroll
     for (int j = 0; j < T; ++j) { ix[j] = c.idx(pos, j); if (ix[j] != kInvalidIndex) m |= 1u << j; }
-    if ((dupmask >> k) & 1u)
+    if ((dupmask >> k) & 1ull)
     {
 #pragma unroll 1
       for (int j = 1; j < T; ++j)
@@ -244,7 +244,7 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
 #pragma unroll
       for (int j = 0; j < T; ++j) v[j] += inc;
       swept += __popc(m);
-      if ((ag.dupmask >> k) & 1u)
+      if ((ag.dupmask >> k) & 1ull)
       {
         // alias slots: one more sequential += inc on the slot they duplicate (if it is still valid)
         const uint64_t ac_ = alias_counts<T>(c, pos, m);
@@ -297,7 +297,7 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
     ag.dtblw += (uint32_t)__popc(owner);           // directory sentinels written
   }
   ag.len++;
-  ag.dupmask = (ag.dupmask << 1) | (pdup ? 1u : 0u);
+  ag.dupmask = (ag.dupmask << 1) | (pdup ? 1ull : 0ull);
   ag.total_decay *= e;
   while (ag.total_decay < dc && ag.len > 1)
   {

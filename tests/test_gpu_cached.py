@@ -10,13 +10,19 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _run(G, mk, mode, n, launches, **kw):
+def _run(G, mk, mode, n, launches, sweep=False, **kw):
     os.environ["GRLCU_MODE"] = str(mode)
     try:
         b = G.Batch(mk(**kw), n)
     finally:
         os.environ.pop("GRLCU_MODE", None)
     try:
+        if sweep:
+            # per-agent hyperparameters (MultiExperiment / grlo sweeps): trace lengths differ inside a warp
+            i = np.arange(n)
+            lam = np.array([0.0, 0.2, 0.4, 0.5, 0.65, 0.75, 0.85, 0.9])[i % 8]
+            b.set_hyper(alpha=np.array([0.05, 0.1, 0.2, 0.4])[(i // 8) % 4], lambda_=lam,
+                        epsilon=np.array([0.01, 0.05, 0.1, 0.3])[(i // 32) % 4])
         for k in launches:
             b.run(k)
         res = b.results()
@@ -37,6 +43,9 @@ def _run(G, mk, mode, n, launches, **kw):
     dict(which="cart_pole", n=32, memory=1031, launches=[400], test_interval=-1, epsilon=0.5),
     dict(which="pendulum", n=32, memory=8192, launches=[130], test_interval=-1, lambda_=0.0),  # decay < 0.01
     dict(which="pendulum", n=32, memory=8192, launches=[260], test_interval=-1, lambda_=0.9),  # long trace
+    # trace capacity 35 (> 32 entries: the duplicate mask is 64 bits wide) with per-agent hyperparameters
+    dict(which="pendulum", n=128, memory=65536, launches=[120, 260], test_interval=5, lambda_=0.9, sweep=True),
+    dict(which="pendulum", n=64, memory=521, launches=[300], test_interval=-1, lambda_=0.9, sweep=True),
     # actor-critic (BASELINE configs[3]): the critic's trace goes through the cache, the actor table does not
     dict(which="ac", n=64, memory=131072, launches=[90, 1, 310], test_interval=3),
     dict(which="ac", n=32, memory=509, launches=[350], test_interval=-1, actor_alpha=0.5, sigma=15.0),

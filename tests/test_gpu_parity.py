@@ -99,12 +99,15 @@ def test_table_init_bit_exact(G, orc):
         b.close(); ob.close()
 
 
-def _replay(G, gcfg, ocfg, n, steps, mem, check_tables=True, **kw):
+def _replay(G, gcfg, ocfg, n, steps, mem, check_tables=True, hyper=None, **kw):
     cfg, oc = gcfg(memory=mem, **kw), ocfg(memory=mem, **kw)
     b = G.Batch(cfg, n)
     ob = O.OracleBatch(oc, n)
     mism_actions = 0
     try:
+        if hyper is not None:
+            b.set_hyper(*hyper)
+            ob.set_hyper(*hyper)
         for t in range(steps):
             d = ob.step()
             inp = dict(d)
@@ -161,6 +164,20 @@ def test_replay_pendulum_small_table_collisions(G, orc):
 def test_replay_cart_pole(G, orc):
     _replay(G, G.cart_pole_config, O.cart_pole_config, n=32, steps=500, mem=262144,
             randomization=1.0, test_interval=3, epsilon=0.3)
+
+
+def test_replay_per_agent_hyperparameters(G, orc):
+    """The sweep workload (MultiExperiment / grlo grids): alpha, lambda, epsilon per agent; lambda = 0.9 needs a
+    35-entry trace ring (more than 32: the fast update paths carry a 64-bit duplicate mask)."""
+    n = 64
+    i = np.arange(n)
+    hyper = (np.array([0.05, 0.1, 0.2, 0.4])[i % 4],
+             np.array([0.0, 0.2, 0.4, 0.5, 0.65, 0.75, 0.85, 0.9])[(i // 4) % 8],
+             np.array([0.01, 0.3])[i // 32])
+    _replay(G, G.pendulum_config, O.pendulum_config, n=n, steps=320, mem=65536, hyper=hyper,
+            randomization=1.0, test_interval=4, lambda_=0.9)
+    _replay(G, G.pendulum_config, O.pendulum_config, n=n, steps=200, mem=307, hyper=hyper,
+            randomization=1.0, test_interval=-1, lambda_=0.9)
 
 
 def test_replay_accumulating_and_no_trace(G, orc):
