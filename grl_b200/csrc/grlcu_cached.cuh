@@ -76,9 +76,15 @@ template <int T>
 __device__ __noinline__ uint32_t flush_entry(const Cache<T> c, double *tbl, int pos)
 {
   const uint32_t m = c.mask(pos);
+  // all loads first, then all stores: the compiler cannot hoist a load over a store that may alias it, and one
+  // load -> store round trip per tiling was the largest stall of the fused kernels (profiles/r01_ncu_*_v6_*)
+  uint32_t ix[T];
+  double v[T];
+#pragma unroll
+  for (int j = 0; j < T; ++j) { ix[j] = c.idx(pos, j); v[j] = c.val(pos * T + j); }
 #pragma unroll
   for (int j = 0; j < T; ++j)
-    if ((m >> j) & 1u) tbl[c.idx(pos, j)] = c.val(pos * T + j);
+    if ((m >> j) & 1u) tbl[ix[j]] = v[j];
   return (uint32_t)__popc(m);          // table stores issued
 }
 
@@ -238,9 +244,9 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
       weight *= e;
       const uint32_t m = c.mask(pos);
       double v[T];
+      // unconditional loads: the values do not wait for the mask (invalid slots are loaded and never stored)
 #pragma unroll
-      for (int j = 0; j < T; ++j)
-        if ((m >> j) & 1u) v[j] = c.val(pos * T + j);
+      for (int j = 0; j < T; ++j) v[j] = c.val(pos * T + j);
 #pragma unroll
       for (int j = 0; j < T; ++j) v[j] += inc;
       swept += __popc(m);
@@ -262,9 +268,11 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
   // and its weight moves into p's new slot.
 #pragma unroll
   for (int j = 0; j < T; ++j)
+    if (((owner >> j) & 1u) && sp[j] >= 0) np[j] = c.val(sp[j]);      // loads first (see flush_entry)
+#pragma unroll
+  for (int j = 0; j < T; ++j)
     if (((owner >> j) & 1u) && sp[j] >= 0)
     {
-      np[j] = c.val(sp[j]);
       const int pos = sp[j] / T, jj = sp[j] - pos * T;
       c.mask(pos) &= ~(1u << jj);
     }
