@@ -113,7 +113,7 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_run_host", "grlcu_replay_step", "grlcu_get_results", "grlcu_get_table",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
            "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update",
-           "grlcu_get_actor_table", "grlcu_set_actor_table"]
+           "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor"]
 
 _lib = None
 
@@ -153,6 +153,8 @@ def load(build=True):
     L.grlcu_task_start.argtypes = [vp, C.c_int64, C.c_int32, _dp, _dp, _dp, _i32p]
     L.grlcu_read.argtypes = [vp, C.c_int32, C.c_int32, _u64p, _dp]
     L.grlcu_update.argtypes = [vp, C.c_int32, C.c_int32, _u64p, C.c_double]
+    L.grlcu_read_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, _dp]
+    L.grlcu_update_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, C.c_double]
     _lib = L
     return L
 
@@ -221,17 +223,19 @@ class Batch:
                                             _ptr(term, _i32p)))
         return st, obs, term
 
-    def read(self, agent, indices):
-        """LinearRepresentation::read of one projection on one agent's table."""
+    def read(self, agent, indices, actor=False):
+        """LinearRepresentation::read of one projection on one agent's table (actor=True: the AC actor table)."""
         idx = np.ascontiguousarray(indices, dtype=np.uint64)
         v = C.c_double()
-        self._chk(self.lib.grlcu_read(self.h, int(agent), idx.shape[0], _ptr(idx, _u64p), C.byref(v)))
+        f = self.lib.grlcu_read_actor if actor else self.lib.grlcu_read
+        self._chk(f(self.h, int(agent), idx.shape[0], _ptr(idx, _u64p), C.byref(v)))
         return v.value
 
-    def update(self, agent, indices, delta):
+    def update(self, agent, indices, delta, actor=False):
         """LinearRepresentation::update(projection, delta) on one agent's table."""
         idx = np.ascontiguousarray(indices, dtype=np.uint64)
-        self._chk(self.lib.grlcu_update(self.h, int(agent), idx.shape[0], _ptr(idx, _u64p), C.c_double(delta)))
+        f = self.lib.grlcu_update_actor if actor else self.lib.grlcu_update
+        self._chk(f(self.h, int(agent), idx.shape[0], _ptr(idx, _u64p), C.c_double(delta)))
 
     def run(self, n_steps, cohort=0):
         self._chk(self.lib.grlcu_run(self.h, n_steps, cohort))

@@ -5,6 +5,7 @@
 #include "grlcu_ac.cuh"
 
 #include <cuda_runtime.h>
+#include <cfloat>
 #include <cmath>
 #include <cstdio>
 #include <cstdarg>
@@ -492,7 +493,10 @@ extern "C" int grlcu_task_start(grlcu_ctx *c, int64_t n, int32_t test, const dou
 }
 
 // one thread: the reference's sequential order is the contract (linear.cpp:147-151, 207-215)
-__global__ void k_table_read(const double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double *value, int *bad)
+// [lo, hi]: the representation's output_min / output_max (+-DBL_MAX when unset, linear.cpp:88-98); the read is
+// clamped to it (linear.cpp:179-180) and, with limit = 1, so is every updated weight (linear.cpp:207-211)
+__global__ void k_table_read(const double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
+                             double *value, int *bad)
 {
   double r = 0;
   for (int i = 0; i < n_idx; ++i)
@@ -500,22 +504,24 @@ __global__ void k_table_read(const double *tbl, int n_idx, const uint64_t *idx, 
     if (idx[i] >= memory) { *bad = 1; return; }
     r += tbl[idx[i]];
   }
-  *value = r / n_idx;
+  *value = fmin(fmax(r / n_idx, lo), hi);
 }
 
-__global__ void k_table_update(double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double delta, int *bad)
+__global__ void k_table_update(double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
+                               double delta, int *bad)
 {
   for (int i = 0; i < n_idx; ++i)
   {
     if (idx[i] == ~0ull) continue;                    // IndexProjection::invalid_index()
     if (idx[i] >= memory) { *bad = 1; return; }
-    tbl[idx[i]] += delta;
+    tbl[idx[i]] = fmin(fmax(tbl[idx[i]] + delta, lo), hi);
   }
 }
 
-static int table_view(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value, double delta)
+static int table_view(grlcu_ctx *c, bool actor, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value, double delta)
 {
   if (!c || agent < 0 || agent >= c->p.n || n_idx < 1 || !idx) return fail(GRLCU_ERR_ARG, "grlcu_read/update: bad arguments");
+  if (actor && c->cfg.algo != GRLCU_ALGO_AC) return fail(GRLCU_ERR_UNSUPPORTED, "no actor table: not an actor-critic context");
   CU(cudaSetDevice(c->device));
   if (int r = ensure_plain(c)) return r;
   Scratch s;
@@ -525,9 +531,10 @@ static int table_view(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t
   if (!d_i || !d_v || !d_bad) return fail(GRLCU_ERR_NOMEM, "grlcu_read/update: out of device memory");
   CU(cudaMemcpyAsync(d_i, idx, sizeof(uint64_t) * n_idx, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
-  double *tbl = c->p.table + (size_t)agent * c->cfg.memory;
-  if (value) k_table_read<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, d_v, d_bad);
-  else k_table_update<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, delta, d_bad);
+  double *tbl = (actor ? c->ac.actor : c->p.table) + (size_t)agent * c->cfg.memory;
+  const double lo = actor ? c->ac.action_min : -DBL_MAX, hi = actor ? c->ac.action_max : DBL_MAX;
+  if (value) k_table_read<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, d_v, d_bad);
+  else k_table_update<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, delta, d_bad);
   c->launches++;
   CU(cudaGetLastError());
   int bad = 0;
@@ -541,12 +548,23 @@ static int table_view(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t
 extern "C" int grlcu_read(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value)
 {
   if (!value) return fail(GRLCU_ERR_ARG, "grlcu_read: null output");
-  return table_view(c, agent, n_idx, idx, value, 0.);
+  return table_view(c, false, agent, n_idx, idx, value, 0.);
 }
 
 extern "C" int grlcu_update(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double delta)
 {
-  return table_view(c, agent, n_idx, idx, nullptr, delta);
+  return table_view(c, false, agent, n_idx, idx, nullptr, delta);
+}
+
+extern "C" int grlcu_read_actor(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value)
+{
+  if (!value) return fail(GRLCU_ERR_ARG, "grlcu_read_actor: null output");
+  return table_view(c, true, agent, n_idx, idx, value, 0.);
+}
+
+extern "C" int grlcu_update_actor(grlcu_ctx *c, int32_t agent, int32_t n_idx, const uint64_t *idx, double delta)
+{
+  return table_view(c, true, agent, n_idx, idx, nullptr, delta);
 }
 
 // ---- fused run -------------------------------------------------------------------------------

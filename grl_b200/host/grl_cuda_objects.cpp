@@ -13,6 +13,8 @@ REGISTER_CONFIGURABLE(CudaBatchedEnvironment)
 REGISTER_CONFIGURABLE(CudaTileCodingProjector)
 REGISTER_CONFIGURABLE(CudaLinearRepresentation)
 REGISTER_CONFIGURABLE(CudaSARSAPredictor)
+REGISTER_CONFIGURABLE(CudaTDPredictor)
+REGISTER_CONFIGURABLE(CudaACPredictor)
 
 // ---- environment/model/cuda_batched (stands in for environment/modeled, modeled.cpp:35-121) ---------------
 void CudaBatchedEnvironment::request(ConfigurationRequest *config)
@@ -37,7 +39,7 @@ void CudaBatchedEnvironment::configure(Configuration &config)
   model_ = dynamic_cast<DynamicalModel *>(config["model"].ptr());
   task_ = dynamic_cast<Task *>(config["task"].ptr());
   if (!model_) throw Exception(path() + ": model must be a model/dynamical");
-  if (!task_) throw Exception(path() + ": task must be one of the batched tasks (pendulum/swingup, cart_pole/swingup)");
+  if (!task_) throw Exception(path() + ": task must be one of the batched tasks (pendulum/swingup, cart_pole/swingup, cart_double_pole/balancing)");
   if ((int)config["window"] != 1) throw bad_param("environment/model/cuda_batched:window");
   if ((int)config["stride"] != 1) throw bad_param("environment/model/cuda_batched:stride");
   if (!config["delta"].v().empty()) throw bad_param("environment/model/cuda_batched:delta");
@@ -70,7 +72,8 @@ void CudaBatchedEnvironment::contribute(CudaPath *p) const
 void CudaBatchedEnvironment::start(int test, Observation *obs)
 {
   if (!path_) throw Exception(path() + ": not attached to an experiment");
-  const int S = path_->cfg.dynamics == GRLCU_DYN_PENDULUM ? 3 : 5, OBS = path_->cfg.obs_dims;
+  const int S = path_->cfg.dynamics == GRLCU_DYN_PENDULUM ? 3 : path_->cfg.dynamics == GRLCU_DYN_CART_POLE ? 5 : 7;
+  const int OBS = path_->cfg.obs_dims;
   const double u = 0.5;                     // agent-0 view: centre draw; the batched path draws from Philox
   state_.assign(S, 0.);
   obs->assign(OBS, 0.);
@@ -166,8 +169,10 @@ void CudaLinearRepresentation::configure(Configuration &config)
   if (memory_ < 1) throw bad_param("representation/linear/cuda:memory");
   if (outputs_ != 1) throw bad_param("representation/linear/cuda:outputs");
   if (init_min_.size() != 1 || init_max_.size() != 1) throw bad_param("representation/linear/cuda:{init_min,init_max}");
-  // unset limits mean +-DBL_MAX (linear.cpp:88-98), the only case the kernels implement (clamp = identity)
-  if (!output_min_.empty() || !output_max_.empty()) throw bad_param("representation/linear/cuda:{output_min,output_max}");
+  // unset limits mean +-DBL_MAX (linear.cpp:88-98): the value tables.  Set limits are what the actor-critic
+  // policy's action representation carries (= the task's action_min/max); the experiment checks the role.
+  if (output_min_.size() != output_max_.size() || output_min_.size() > 1) throw bad_param("representation/linear/cuda:{output_min,output_max}");
+  if (!output_min_.empty() && limit_ != 1) throw bad_param("representation/linear/cuda:limit");
   if ((int)config["interval"] != 0) throw bad_param("representation/linear/cuda:interval");
 }
 
@@ -175,6 +180,7 @@ void CudaLinearRepresentation::contribute(CudaPath *p) const
 {
   if (p->have_projector && p->cfg.memory != memory_)
     throw bad_param("representation/linear/cuda:memory (or matching projector)");
+  if (!output_min_.empty()) throw bad_param("representation/linear/cuda:{output_min,output_max}");   // value table: unlimited
   p->cfg.init_min = init_min_[0]; p->cfg.init_max = init_max_[0];
   p->have_representation = true;
 }
@@ -184,7 +190,7 @@ double CudaLinearRepresentation::read(const ProjectionPtr &projection, Vector *r
   if (!path_) throw Exception(path() + ": not attached to an experiment");
   std::vector<uint64_t> idx(projection->indices.begin(), projection->indices.end());
   double v = 0;
-  CudaPath::check(grlcu_read(path_->context(), 0, (int)idx.size(), idx.data(), &v));
+  CudaPath::check((actor_ ? grlcu_read_actor : grlcu_read)(path_->context(), 0, (int)idx.size(), idx.data(), &v));
   result->assign(1, v);
   return v;
 }
@@ -194,7 +200,7 @@ void CudaLinearRepresentation::update(const ProjectionPtr projection, const Vect
   if (!path_) throw Exception(path() + ": not attached to an experiment");
   if (delta.size() != 1) throw Exception(path() + ": expected a 1-dimensional delta");
   std::vector<uint64_t> idx(projection->indices.begin(), projection->indices.end());
-  CudaPath::check(grlcu_update(path_->context(), 0, (int)idx.size(), idx.data(), delta[0]));
+  CudaPath::check((actor_ ? grlcu_update_actor : grlcu_update)(path_->context(), 0, (int)idx.size(), idx.data(), delta[0]));
 }
 
 void CudaLinearRepresentation::write(const ProjectionPtr projection, const Vector &target, const Vector &alpha)
@@ -211,7 +217,7 @@ void CudaLinearRepresentation::reconfigure(const Configuration &config)
   const std::string action = config["action"].str();
   if (action == "reset")
   {
-    if (path_->ctx) CudaPath::check(grlcu_reset(path_->ctx, GRLCU_RESET_TABLES));
+    if (path_->ctx && !actor_) CudaPath::check(grlcu_reset(path_->ctx, GRLCU_RESET_TABLES));   // resets both tables of an AC context
     return;
   }
   if (action != "save" && action != "load") return;
@@ -227,7 +233,7 @@ void CudaLinearRepresentation::reconfigure(const Configuration &config)
     const std::string file = base + cfg_path + (a ? "-agent" + std::to_string(a) : std::string()) + ".dat";
     if (action == "save")
     {
-      CudaPath::check(grlcu_get_table(path_->context(), a, p.data()));
+      CudaPath::check((actor_ ? grlcu_get_actor_table : grlcu_get_table)(path_->context(), a, p.data()));
       FILE *f = fopen(file.c_str(), "wb");
       if (!f) { WARNING("Could not open '" << file << "' for writing"); return; }
       fwrite(p.data(), sizeof(double), p.size(), f);
@@ -242,7 +248,7 @@ void CudaLinearRepresentation::reconfigure(const Configuration &config)
       fseek(f, 0, SEEK_SET);
       if (fread(p.data(), sizeof(double), p.size(), f) != p.size()) { WARNING("Could not read '" << file << "'"); fclose(f); return; }
       fclose(f);
-      CudaPath::check(grlcu_set_table(path_->context(), a, p.data()));
+      CudaPath::check((actor_ ? grlcu_set_actor_table : grlcu_set_table)(path_->context(), a, p.data()));
     }
   }
 }
@@ -276,6 +282,67 @@ void CudaSARSAPredictor::contribute(CudaPath *p) const
   p->cfg.alpha = alpha_; p->cfg.gamma = gamma_; p->cfg.lambda = lambda_;
   p->cfg.trace = trace_ ? trace_->kind : GRLCU_TRACE_NONE;
   p->cfg.algo = GRLCU_ALGO_SARSA;
+  p->have_predictor = true;
+}
+
+// ---- predictor/critic/td/cuda (predictors/td.cpp:35-66) ----------------------------------------------------
+void CudaTDPredictor::request(ConfigurationRequest *config)
+{
+  config->push_back(CRP("alpha", "Learning rate", alpha_));
+  config->push_back(CRP("gamma", "Discount rate", gamma_));
+  config->push_back(CRP("lambda", "Trace decay rate", lambda_));
+  config->push_back(CRP("projector", "projector.observation", "Projects observations onto representation space", projector_));
+  config->push_back(CRP("representation", "representation.value/state", "State value representation", representation_));
+  config->push_back(CRP("trace", "trace", "Trace of projections", trace_, true));
+}
+
+void CudaTDPredictor::configure(Configuration &config)
+{
+  projector_ = (Projector *)config["projector"].ptr();
+  representation_ = (Representation *)config["representation"].ptr();
+  trace_ = dynamic_cast<Trace *>(config["trace"].ptr());
+  alpha_ = config["alpha"]; gamma_ = config["gamma"]; lambda_ = config["lambda"];
+  if (!dynamic_cast<CudaTileCodingProjector *>(projector_)) throw Exception(path() + ": projector must be a projector/tile_coding/cuda");
+  if (!dynamic_cast<CudaLinearRepresentation *>(representation_)) throw Exception(path() + ": representation must be a representation/linear/cuda");
+  if (config["trace"].ptr() && !trace_) throw Exception(path() + ": trace must be trace/enumerated/replacing or trace/enumerated/accumulating");
+}
+
+void CudaTDPredictor::contribute(CudaPath *p) const
+{
+  p->cfg.alpha = alpha_; p->cfg.gamma = gamma_; p->cfg.lambda = lambda_;
+  p->cfg.trace = trace_ ? trace_->kind : GRLCU_TRACE_NONE;
+}
+
+// ---- predictor/ac/action/cuda (predictors/ac.cpp:35-70) ------------------------------------------------------
+void CudaACPredictor::request(ConfigurationRequest *config)
+{
+  config->push_back(CRP("alpha", "Actor learning rate", alpha_));
+  config->push_back(CRP("update_method", "Actor update method", "proportional", CRP::Configuration));
+  config->push_back(CRP("step_limit", "Actor exploration step limit", Vector()));
+  config->push_back(CRP("projector", "projector.observation", "Projects observations onto actor representation space", projector_));
+  config->push_back(CRP("representation", "representation.action", "Action representation", representation_));
+  config->push_back(CRP("critic", "predictor/critic", "Critic predictor", critic_));
+}
+
+void CudaACPredictor::configure(Configuration &config)
+{
+  projector_ = (Projector *)config["projector"].ptr();
+  representation_ = (Representation *)config["representation"].ptr();
+  critic_ = dynamic_cast<CudaTDPredictor *>(config["critic"].ptr());
+  alpha_ = config["alpha"];
+  if (!critic_) throw Exception(path() + ": critic must be a predictor/critic/td/cuda");
+  if (!dynamic_cast<CudaTileCodingProjector *>(projector_)) throw Exception(path() + ": projector must be a projector/tile_coding/cuda");
+  if (!dynamic_cast<CudaLinearRepresentation *>(representation_)) throw Exception(path() + ": representation must be a representation/linear/cuda");
+  // ac.cpp:84-107: "proportional" is the update on the device; "cacla" and the step limit are not
+  if (config["update_method"].str() != "proportional") throw bad_param("predictor/ac/action/cuda:update_method");
+  if (!config["step_limit"].v().empty()) throw bad_param("predictor/ac/action/cuda:step_limit");
+}
+
+void CudaACPredictor::contribute(CudaPath *p) const
+{
+  critic_->contribute(p);
+  p->cfg.actor_alpha = alpha_;
+  p->cfg.algo = GRLCU_ALGO_AC;
   p->have_predictor = true;
 }
 

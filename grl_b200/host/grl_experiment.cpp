@@ -58,44 +58,98 @@ void OnlineLearningExperiment::reconfigure(const Configuration &config)
   if (config.has("identity")) identity = config["identity"].str();
 }
 
-// Collect the parameters of the four CUDA objects into one grlcu_config (no device needed).
+// Collect the parameters of the CUDA objects into one grlcu_config (no device needed).
 void OnlineLearningExperiment::assemble()
 {
   if (assembled_) return;
   CudaBatchedEnvironment *env = dynamic_cast<CudaBatchedEnvironment *>(environment_);
   TDAgent *td = dynamic_cast<TDAgent *>(agent_);
   if (!env) throw Exception(path() + ": environment must be an environment/model/cuda_batched");
-  if (!td || !td->policy) throw Exception(path() + ": agent must be an agent/td with a mapping/policy/discrete/value/q policy");
-  CudaSARSAPredictor *pred = dynamic_cast<CudaSARSAPredictor *>(td->predictor);
-  if (!pred) throw Exception(path() + ": agent predictor must be a predictor/sarsa/cuda");
-  QPolicy *pol = td->policy;
+  if (!td || !td->policy)
+    throw Exception(path() + ": agent must be an agent/td with a mapping/policy/discrete/value/q or mapping/policy/action policy");
+  Policy *pol = td->policy;
   CudaTileCodingProjector *proj = dynamic_cast<CudaTileCodingProjector *>(pol->projector);
   CudaLinearRepresentation *rep = dynamic_cast<CudaLinearRepresentation *>(pol->representation);
   if (!proj) throw Exception(path() + ": policy projector must be a projector/tile_coding/cuda");
   if (!rep) throw Exception(path() + ": policy representation must be a representation/linear/cuda");
-  if (pred->projector() != pol->projector || pred->representation() != pol->representation)
-    throw Exception(path() + ": predictor and policy must share one projector and one representation");
-  if (!pol->discretizer || !pol->sampler) throw Exception(path() + ": policy needs a discretizer and a sampler");
-  if (test_agent_ && test_agent_->policy)
-  {
-    QPolicy *tp = test_agent_->policy;
-    if (tp->projector != pol->projector || tp->representation != pol->representation || tp->discretizer != pol->discretizer)
-      throw Exception(path() + ": test_agent must evaluate the learning agent's discretizer, projector and representation");
-    if (!dynamic_cast<GreedySampler *>(tp->sampler)) throw Exception(path() + ": test_agent sampler must be sampler/greedy");
-  }
-  env->contribute(&path_);
-  proj->contribute(&path_);
-  rep->contribute(&path_);
-  pred->contribute(&path_);
   grlcu_config &c = path_.cfg;
-  c.n_actions = (int)pol->discretizer->values.size();
-  for (int i = 0; i < c.n_actions; ++i) c.actions[i] = pol->discretizer->values[i];
-  c.epsilon = pol->sampler->epsilon;
+
+  if (CudaSARSAPredictor *pred = dynamic_cast<CudaSARSAPredictor *>(td->predictor))
+  {
+    // SARSA(lambda): QPolicy and predictor share one (obs, action) projector and one Q table
+    QPolicy *qp = dynamic_cast<QPolicy *>(pol);
+    if (!qp) throw Exception(path() + ": predictor/sarsa/cuda needs a mapping/policy/discrete/value/q policy");
+    if (pred->projector() != pol->projector || pred->representation() != pol->representation)
+      throw Exception(path() + ": predictor and policy must share one projector and one representation");
+    if (!qp->discretizer || !qp->sampler) throw Exception(path() + ": policy needs a discretizer and a sampler");
+    if (test_agent_ && test_agent_->policy)
+    {
+      QPolicy *tp = dynamic_cast<QPolicy *>(test_agent_->policy);
+      if (!tp || tp->projector != pol->projector || tp->representation != pol->representation || tp->discretizer != qp->discretizer)
+        throw Exception(path() + ": test_agent must evaluate the learning agent's discretizer, projector and representation");
+      if (!dynamic_cast<GreedySampler *>(tp->sampler)) throw Exception(path() + ": test_agent sampler must be sampler/greedy");
+    }
+    env->contribute(&path_);
+    proj->contribute(&path_);
+    rep->contribute(&path_);
+    pred->contribute(&path_);
+    c.n_actions = (int)qp->discretizer->values.size();
+    for (int i = 0; i < c.n_actions; ++i) c.actions[i] = qp->discretizer->values[i];
+    c.epsilon = qp->sampler->epsilon;
+    env->attach(&path_); proj->attach(&path_); rep->attach(&path_);
+    checkpoint_reps_ = {rep};
+  }
+  else if (CudaACPredictor *ac = dynamic_cast<CudaACPredictor *>(td->predictor))
+  {
+    // Actor-critic (cfg/cart_double_pole/ac.yaml): ActionPolicy + predictor/ac/action{critic: predictor/critic/td}.
+    // The actor's and the critic's projectors must be configured identically: the tile hash has no per-object
+    // seed, so one index set addresses both per-agent tables (grlcu_ac.cuh).
+    ActionPolicy *ap = dynamic_cast<ActionPolicy *>(pol);
+    if (!ap) throw Exception(path() + ": predictor/ac/action/cuda needs a mapping/policy/action policy");
+    if (ac->projector() != pol->projector || ac->representation() != pol->representation)
+      throw Exception(path() + ": predictor/ac/action/cuda must update the policy's projector and representation");
+    CudaTileCodingProjector *cproj = dynamic_cast<CudaTileCodingProjector *>(ac->critic()->projector());
+    CudaLinearRepresentation *crep = dynamic_cast<CudaLinearRepresentation *>(ac->critic()->representation());
+    if (crep == rep) throw Exception(path() + ": actor and critic need separate representations");
+    if (cproj->tilings() != proj->tilings() || cproj->memory() != proj->memory() ||
+        cproj->resolution() != proj->resolution() || cproj->wrapping() != proj->wrapping())
+      throw Exception(path() + ": the critic's projector must have the actor projector's tilings, memory, resolution and wrapping");
+    if (rep->memory() != proj->memory() || crep->memory() != proj->memory())
+      throw bad_param("representation/linear/cuda:memory (or matching projector)");
+    if (rep->outputMin() != ap->min || rep->outputMax() != ap->max)
+      throw Exception(path() + ": the action representation's output_min/max must be the policy's (the task's action limits)");
+    if (rep->initMin() != crep->initMin() || rep->initMax() != crep->initMax())
+      throw Exception(path() + ": actor and critic representations must share init_min/init_max");
+    if (test_agent_ && test_agent_->policy)
+    {
+      ActionPolicy *tp = dynamic_cast<ActionPolicy *>(test_agent_->policy);
+      if (!tp || tp->projector != pol->projector || tp->representation != pol->representation)
+        throw Exception(path() + ": test_agent must evaluate the learning agent's projector and representation");
+      if (tp->sigma != 0.) throw Exception(path() + ": test_agent policy must not explore (sigma: [ ])");
+    }
+    env->contribute(&path_);
+    cproj->contribute(&path_);
+    crep->contribute(&path_);
+    ac->contribute(&path_);
+    c.n_actions = 0;
+    c.epsilon = 0;
+    c.sigma = ap->sigma;
+    c.action_min = ap->min[0]; c.action_max = ap->max[0];
+    for (size_t i = 0; i < proj->resolution().size(); ++i)
+    {
+      c.actor_resolution[i] = proj->resolution()[i];
+      c.actor_wrapping[i] = proj->wrapping()[i];
+    }
+    env->attach(&path_); proj->attach(&path_); cproj->attach(&path_);
+    rep->attach(&path_, true); crep->attach(&path_);
+    checkpoint_reps_ = {rep, crep};
+  }
+  else
+    throw Exception(path() + ": agent predictor must be a predictor/sarsa/cuda or a predictor/ac/action/cuda");
   c.test_interval = test_interval_;
   c.seed = seed;
   path_.agents = agents_;
   path_.device = device_;
-  env->attach(&path_); proj->attach(&path_); rep->attach(&path_);
   assembled_ = true;
 }
 
@@ -133,7 +187,7 @@ std::vector<double> OnlineLearningExperiment::run()
       loadconfig.set("action", "load");
       loadconfig.set("file", load_file_ + "-");
       loadconfig.set("agents", agents_);
-      if (agent_->policy && agent_->policy->representation) agent_->policy->representation->reconfigure(loadconfig);
+      for (Representation *r : checkpoint_reps_) r->reconfigure(loadconfig);
     }
     auto start = std::chrono::steady_clock::now();
     {
@@ -170,7 +224,7 @@ std::vector<double> OnlineLearningExperiment::run()
       saveconfig.set("action", "save");
       saveconfig.set("file", oss.str());
       saveconfig.set("agents", agents_);
-      agent_->policy->representation->reconfigure(saveconfig);
+      for (Representation *r : checkpoint_reps_) r->reconfigure(saveconfig);
     }
     if (ofs.is_open())
     {

@@ -15,12 +15,14 @@ REGISTER_CONFIGURABLE(CartDoublePoleDynamics)
 REGISTER_CONFIGURABLE(DynamicalModel)
 REGISTER_CONFIGURABLE(PendulumSwingupTask)
 REGISTER_CONFIGURABLE(CartPoleSwingupTask)
+REGISTER_CONFIGURABLE(CartDoublePoleBalancingTask)
 REGISTER_CONFIGURABLE(UniformDiscretizer)
 REGISTER_CONFIGURABLE(GreedySampler)
 REGISTER_CONFIGURABLE(EpsilonGreedySampler)
 REGISTER_CONFIGURABLE(ReplacingEnumeratedTrace)
 REGISTER_CONFIGURABLE(AccumulatingEnumeratedTrace)
 REGISTER_CONFIGURABLE(QPolicy)
+REGISTER_CONFIGURABLE(ActionPolicy)
 REGISTER_CONFIGURABLE(TDAgent)
 REGISTER_CONFIGURABLE(FixedAgent)
 
@@ -117,6 +119,23 @@ void CartPoleSwingupTask::configure(Configuration &config)
   provide_limits(config, *this, 4, -2 * pow(2.4, 2) - 0.1 * pow(10, 2) - pow(M_PI, 2) - 0.1 * pow(5 * M_PI, 2) - 10000, 0);
 }
 
+void CartDoublePoleBalancingTask::request(ConfigurationRequest *config)
+{
+  request_limits(config);
+  config->push_back(CRP("timeout", "Episode timeout", 4.99, CRP::Configuration, 0., DBL_MAX));
+}
+void CartDoublePoleBalancingTask::configure(Configuration &config)
+{
+  // cart_double_pole.cpp:225-246; start() always draws theta1 = 0.01 U - 0.005 (no randomization parameter)
+  dynamics_id = GRLCU_DYN_CART_DOUBLE_POLE;
+  timeout = config["timeout"];
+  randomization = 0;
+  if (timeout < 0) throw bad_param("task/cart_double_pole/balancing:timeout");
+  observation_min = {-2.4, -0.7, -0.7, -5.0, -5.0, -5.0}; observation_max = {2.4, 0.7, 0.7, 5.0, 5.0, 5.0};
+  action_min = {-20.}; action_max = {20.};
+  provide_limits(config, *this, 6, 0, 6.2);
+}
+
 void UniformDiscretizer::request(const std::string &role, ConfigurationRequest *config)
 {
   const std::string suffix = role == "action" ? "action" : role == "observation" ? "observation" : "";
@@ -172,6 +191,38 @@ void QPolicy::configure(Configuration &config)
   sampler = (Sampler *)config["sampler"].ptr();
 }
 
+void ActionPolicy::request(ConfigurationRequest *config)
+{
+  // policies/action.cpp:39-55
+  config->push_back(CRP("sigma", "Standard deviation of Gaussian exploration distribution", Vector(), CRP::Configuration));
+  config->push_back(CRP("theta", "Ornstein-Uhlenbeck friction term (1=pure Gaussian noise)", Vector(), CRP::Configuration));
+  config->push_back(CRP("decay_rate", "Multiplicative decay factor per episode", 1., CRP::Configuration));
+  config->push_back(CRP("decay_min", "Minimum decay (sigma_min = sigma*decay_min)", 0., CRP::Configuration));
+  config->push_back(CRP("renormalize", "Renormalize representation output from [-1, 1] to [min, max]", 0, CRP::Configuration, 0, 1));
+  config->push_back(CRP("output_min", "vector.action_min", "Lower limit on outputs", Vector(), CRP::System));
+  config->push_back(CRP("output_max", "vector.action_max", "Upper limit on outputs", Vector(), CRP::System));
+  config->push_back(CRP("projector", "projector.observation", "Projects observations onto representation space", projector));
+  config->push_back(CRP("representation", "representation.action", "Action representation", representation));
+}
+void ActionPolicy::configure(Configuration &config)
+{
+  // policies/action.cpp:57-97
+  projector = (Projector *)config["projector"].ptr();
+  representation = (Representation *)config["representation"].ptr();
+  min = config["output_min"].v(); max = config["output_max"].v();
+  if (min.size() != max.size() || min.empty()) throw bad_param("policy/action:{output_min,output_max}");
+  if (min.size() != 1) throw Exception(path() + ": the batched CUDA path supports one action dimension");
+  Vector s = config["sigma"].v(), th = config["theta"].v();
+  if (s.empty()) s = Vector{0.};
+  if (s.size() != 1) throw bad_param("policy/action:sigma");
+  if (th.empty()) th = Vector{1.};
+  if (th.size() != 1) throw bad_param("policy/action:theta");
+  if (th[0] != 1.) throw bad_param("policy/action:theta");                 // Ornstein-Uhlenbeck noise: not on the device
+  if ((double)config["decay_rate"] != 1.) throw bad_param("policy/action:decay_rate");
+  if ((int)config["renormalize"] != 0) throw bad_param("policy/action:renormalize");
+  sigma = s[0];
+}
+
 void TDAgent::request(ConfigurationRequest *config)
 {
   config->push_back(CRP("policy", "mapping/policy", "Control policy", policy));
@@ -179,14 +230,14 @@ void TDAgent::request(ConfigurationRequest *config)
 }
 void TDAgent::configure(Configuration &config)
 {
-  policy = (QPolicy *)config["policy"].ptr();
+  policy = dynamic_cast<Policy *>(config["policy"].ptr());
   predictor = (Predictor *)config["predictor"].ptr();
 }
 void FixedAgent::request(ConfigurationRequest *config)
 {
   config->push_back(CRP("policy", "mapping/policy", "Control policy", policy));
 }
-void FixedAgent::configure(Configuration &config) { policy = (QPolicy *)config["policy"].ptr(); }
+void FixedAgent::configure(Configuration &config) { policy = dynamic_cast<Policy *>(config["policy"].ptr()); }
 
 // ---- shared device context ------------------------------------------------------------------------------
 CudaPath::CudaPath() { memset(&cfg, 0, sizeof(cfg)); cfg.test_interval = -1; cfg.seed = 1; }

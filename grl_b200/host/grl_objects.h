@@ -90,6 +90,12 @@ struct CartPoleSwingupTask : Task
   void request(ConfigurationRequest *config) override;
   void configure(Configuration &config) override;
 };
+struct CartDoublePoleBalancingTask : Task
+{
+  TYPEINFO("task/cart_double_pole/balancing", "Cart-double-pole balancing task")
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
 
 struct UniformDiscretizer : Configurable
 {
@@ -121,16 +127,25 @@ class CudaTileCodingProjector;
 class CudaLinearRepresentation;
 class CudaSARSAPredictor;
 
-struct QPolicy : Configurable
+struct Policy : Configurable { Projector *projector = nullptr; Representation *representation = nullptr; };
+struct QPolicy : Policy
 {
   TYPEINFO("mapping/policy/discrete/value/q", "Q-value based policy")
-  UniformDiscretizer *discretizer = nullptr; Projector *projector = nullptr;
-  Representation *representation = nullptr; Sampler *sampler = nullptr;
+  UniformDiscretizer *discretizer = nullptr; Sampler *sampler = nullptr;
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+/// ActionPolicy (policies/action.cpp:39-97): a = clamp(pi(s) + N(0, sigma)); only theta = 1 (pure Gaussian
+/// noise), no decay and no renormalisation run on the device.
+struct ActionPolicy : Policy
+{
+  TYPEINFO("mapping/policy/action", "Policy based on a direct action representation")
+  double sigma = 0; Vector min, max;
   void request(ConfigurationRequest *config) override;
   void configure(Configuration &config) override;
 };
 
-struct Agent : Configurable { QPolicy *policy = nullptr; };
+struct Agent : Configurable { Policy *policy = nullptr; };
 struct TDAgent : Agent
 {
   TYPEINFO("agent/td", "Agent that learns from observed state transitions")
@@ -189,6 +204,8 @@ class CudaTileCodingProjector : public Projector
     void attach(CudaPath *path) { path_ = path; }
     int tilings() const { return tilings_; }
     int memory() const { return memory_; }
+    const Vector &resolution() const { return resolution_; }
+    const Vector &wrapping() const { return wrapping_; }
   private:
     int tilings_ = 16, memory_ = 8 * 1024 * 1024, safe_ = 0; Vector resolution_, wrapping_;
     CudaPath *path_ = nullptr;
@@ -205,11 +222,16 @@ class CudaLinearRepresentation : public Representation
     void write(const ProjectionPtr projection, const Vector &target, const Vector &alpha) override;
     void update(const ProjectionPtr projection, const Vector &delta) override;
     void contribute(CudaPath *path) const;
-    void attach(CudaPath *path) { path_ = path; }
+    /// actor: this object is the actor-critic policy's action representation (second table of the context)
+    void attach(CudaPath *path, bool actor = false) { path_ = path; actor_ = actor; }
     int memory() const { return memory_; }
+    const Vector &outputMin() const { return output_min_; }
+    const Vector &outputMax() const { return output_max_; }
+    double initMin() const { return init_min_[0]; }
+    double initMax() const { return init_max_[0]; }
   private:
     Vector init_min_, init_max_, output_min_, output_max_; int memory_ = 8 * 1024 * 1024, outputs_ = 1, limit_ = 1;
-    CudaPath *path_ = nullptr;
+    CudaPath *path_ = nullptr; bool actor_ = false;
 };
 
 class CudaSARSAPredictor : public Predictor
@@ -225,6 +247,39 @@ class CudaSARSAPredictor : public Predictor
   private:
     double alpha_ = 0.2, gamma_ = 0.97, lambda_ = 0.65;
     Projector *projector_ = nullptr; Representation *representation_ = nullptr; Trace *trace_ = nullptr;
+};
+
+/// predictor/critic/td/cuda (stands in for predictor/critic/td, predictors/td.cpp:35-66): TD(lambda) on V(s);
+/// its type starts with `predictor/critic`, which is what predictor/ac/action asks for (ac.cpp:47).
+class CudaTDPredictor : public Predictor
+{
+  public:
+    TYPEINFO("predictor/critic/td/cuda", "TD(lambda) state-value critic fused with the environment step on a B200")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void contribute(CudaPath *path) const;
+    Projector *projector() const { return projector_; }
+    Representation *representation() const { return representation_; }
+  private:
+    double alpha_ = 0.2, gamma_ = 0.97, lambda_ = 0.65;
+    Projector *projector_ = nullptr; Representation *representation_ = nullptr; Trace *trace_ = nullptr;
+};
+
+/// predictor/ac/action/cuda (stands in for predictor/ac/action, predictors/ac.cpp:35-70): proportional actor
+/// update driven by the critic's TD error.
+class CudaACPredictor : public Predictor
+{
+  public:
+    TYPEINFO("predictor/ac/action/cuda", "Actor-critic predictor for direct action policies on a B200")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void contribute(CudaPath *path) const;
+    Projector *projector() const { return projector_; }
+    Representation *representation() const { return representation_; }
+    CudaTDPredictor *critic() const { return critic_; }
+  private:
+    double alpha_ = 0.01;
+    Projector *projector_ = nullptr; Representation *representation_ = nullptr; CudaTDPredictor *critic_ = nullptr;
 };
 
 class OnlineLearningExperiment : public Experiment
@@ -248,6 +303,7 @@ class OnlineLearningExperiment : public Experiment
     std::string output_, load_file_, save_every_ = "never";
     Environment *environment_ = nullptr; Agent *agent_ = nullptr, *test_agent_ = nullptr;
     CudaPath path_;
+    std::vector<Representation *> checkpoint_reps_;     // tables written by save_every / read by load_file
     bool assembled_ = false;
 };
 

@@ -164,6 +164,11 @@ int grlcu_task_start(grlcu_ctx *ctx, int64_t n, int32_t test, const double *u, d
  * every idx[i] != (uint64_t)-1, sequentially (duplicates accumulate). */
 int grlcu_read(grlcu_ctx *ctx, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value);
 int grlcu_update(grlcu_ctx *ctx, int32_t agent, int32_t n_idx, const uint64_t *idx, double delta);
+/* The same views of the ACTOR table of an actor-critic context (ActionPolicy's representation,
+ * policies/action.cpp:99-113): the read is clamped to [action_min, action_max] (linear.cpp:179-180) and so is
+ * every updated weight (limit = 1, linear.cpp:207-211). */
+int grlcu_read_actor(grlcu_ctx *ctx, int32_t agent, int32_t n_idx, const uint64_t *idx, double *value);
+int grlcu_update_actor(grlcu_ctx *ctx, int32_t agent, int32_t n_idx, const uint64_t *idx, double delta);
 
 /* Fused K1-K4: n_steps iterations of online_learning.cpp:186-221 for every agent
  * (episode start/end handled on device).  Asynchronous on the context's stream.

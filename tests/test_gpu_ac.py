@@ -139,3 +139,39 @@ def test_ac_free_running_statistics(G, orc):
     # episodes finished within 3000 steps and last returns: same population on both sides
     assert abs(np.mean(r["episodes"]) - np.mean(eps)) < 4 * (np.std(eps) / np.sqrt(64) + np.std(r["episodes"]) / np.sqrt(n)) + 1
     assert abs(np.mean(r["last_return"]) - np.mean(rets)) < 4 * (np.std(rets) / np.sqrt(64) + np.std(r["last_return"]) / np.sqrt(n)) + 1
+
+
+def test_actor_table_views(G, orc):
+    """grlcu_read_actor / grlcu_update_actor: ActionPolicy's representation (limits = action_min/max, limit = 1)."""
+    cfg = G.cart_double_pole_ac_config(memory=2048)
+    b = G.Batch(cfg, 2)
+    try:
+        idx = np.array([5, 17, 5, 900, 2047, 33, 1, 0, 12, 13, 14, 15, 16, 18, 19, 20], dtype=np.uint64)
+        t = b.get_actor_table(1)
+        want = 0.0
+        for i in idx:
+            want += t[int(i)]
+        assert b.read(1, idx, actor=True) == min(max(want / 16, -20.0), 20.0)
+        # update: sequential += delta, every written weight clamped (linear.cpp:207-211); duplicates accumulate
+        b.update(1, idx, 15.0, actor=True)
+        t2 = t.copy()
+        for i in idx:
+            t2[int(i)] = min(max(t2[int(i)] + 15.0, -20.0), 20.0)
+        assert np.array_equal(b.get_actor_table(1), t2)
+        assert t2[5] == 20.0                                   # 0..1 + 15 + 15 saturates
+        assert b.read(1, idx, actor=True) <= 20.0
+        assert np.array_equal(b.get_actor_table(0), b.get_actor_table(0)) and not np.array_equal(b.get_actor_table(0), t2)
+        # the critic views are not limited
+        c = b.get_table(1)
+        b.update(1, idx[:4], 1e6)
+        assert b.get_table(1)[17] == c[17] + 1e6
+        with pytest.raises(G.GrlcuError):
+            b.read(1, np.array([2048], dtype=np.uint64), actor=True)
+    finally:
+        b.close()
+    s = G.Batch(G.pendulum_config(memory=2048), 1)
+    try:
+        with pytest.raises(G.GrlcuError):
+            s.read(0, idx, actor=True)                         # no actor table on a SARSA context
+    finally:
+        s.close()

@@ -46,12 +46,33 @@ def test_shipped_configs_resolve_to_the_harness_configs(grld):
         assert got["actions"] == list(want.actions)[:3]
 
 
+def test_actor_critic_config_resolves_to_the_harness_config(grld):
+    import grl_b200
+    rc, out, err = check(grld, os.path.join(ROOT, "cfg/cart_double_pole/ac_tc_cuda.yaml"))
+    assert rc == 0, err
+    got = json.loads(out)
+    want = grl_b200.cart_double_pole_ac_config(memory=got["memory"], test_interval=10)
+    assert got["agents"] == 4096 and got["algo"] == grl_b200.capi.ALGO_AC
+    for k in ("dynamics", "integration_steps", "control_step", "timeout", "randomization", "tilings", "memory", "obs_dims",
+              "n_actions", "alpha", "gamma", "epsilon", "trace", "init_min", "init_max", "seed", "algo",
+              "sigma", "actor_alpha", "action_min", "action_max"):
+        assert got[k] == getattr(want, k), k
+    assert got["lambda"] == want.lambda_
+    assert got["resolution"][:6] == list(want.resolution)[:6] == got["actor_resolution"] == list(want.actor_resolution)[:6]
+    assert got["actor_wrapping"] == [0.0] * 6
+
+
 def swap_types(text):
     """The only edit a GRL user makes to an existing YAML: the four type names (+ a table size that fits)."""
     text = text.replace("type: environment/modeled", "type: environment/model/cuda_batched")
     text = re.sub(r"type: projector/tile_coding\b", "type: projector/tile_coding/cuda", text)
     text = text.replace("type: representation/parameterized/linear", "type: representation/linear/cuda")
     text = text.replace("type: predictor/critic/sarsa", "type: predictor/sarsa/cuda")
+    # actor-critic (cfg/cart_double_pole/ac.yaml): the two predictors; the policy's type name in that file is stale
+    # in the reference itself (TYPEINFO is mapping/policy/action, policies/action.h:44)
+    text = text.replace("type: predictor/ac/action", "type: predictor/ac/action/cuda")
+    text = text.replace("type: predictor/critic/td", "type: predictor/critic/td/cuda")
+    text = text.replace("type: policy/parameterized/action", "type: mapping/policy/action")
     return text
 
 
@@ -67,6 +88,37 @@ def test_reference_yaml_loads_with_only_the_type_names_swapped(grld, tmp_path, n
     assert got["dynamics"] == dyn and got["memory"] == mem and got["seed"] == 7
     assert got["test_interval"] == 10 and got["trace"] == 1 and got["agents"] == 1
     assert got["actions"] == ([-3.0, 0.0, 3.0] if dyn == 0 else [-15.0, 0.0, 15.0])   # discretizer via task/action_min,max
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_CFG), reason="reference tree not present (GPU box)")
+def test_reference_actor_critic_yaml_loads_with_the_type_names_swapped(grld, tmp_path):
+    src = open(os.path.join(REF_CFG, "cart_double_pole/ac.yaml")).read()
+    dst = tmp_path / "swapped.yaml"
+    dst.write_text(swap_types(src))
+    rc, out, err = check(grld, str(dst))
+    assert rc == 0, err
+    got = json.loads(out)
+    assert got["dynamics"] == 2 and got["algo"] == 1 and got["memory"] == 67108864 and got["obs_dims"] == 6
+    assert (got["sigma"], got["actor_alpha"], got["alpha"], got["lambda"]) == (5.0, 0.01, 0.2, 0.65)
+    assert (got["action_min"], got["action_max"], got["timeout"], got["test_interval"]) == (-20.0, 20.0, 4.99, 10)
+
+
+def test_actor_critic_error_behaviour(grld, tmp_path):
+    base = open(os.path.join(ROOT, "cfg/cart_double_pole/ac_tc_cuda.yaml")).read()
+    cases = [
+        # the critic's projector must be the actor's (one index set addresses both tables)
+        ("          resolution: experiment/agent/policy/projector/resolution", "          resolution: [ 2.5, 0.1, 0.1, 2.5, 1, 1 ]", "critic's projector"),
+        ("      update_method: proportional", "      update_method: cacla", "predictor/ac/action/cuda:update_method"),
+        ("      sigma: [  ]", "      sigma: [ 1 ]", "must not explore"),
+        ("        type: predictor/critic/td/cuda", "        type: predictor/sarsa/cuda", "critic"),
+        ("        output_min: experiment/environment/task/action_min\n", "        output_min: [ -1 ]\n", "output_min/max"),
+    ]
+    for old, new, msg in cases:
+        assert old in base, old
+        p = tmp_path / "bad.yaml"
+        p.write_text(base.replace(old, new, 1))
+        rc, out, err = check(grld, str(p))
+        assert rc == 1 and msg in err, (old, err)
 
 
 def test_error_behaviour(grld, tmp_path):
@@ -134,3 +186,40 @@ def test_grld_matches_ctypes_harness(grld, tmp_path):
     ck = np.fromfile(str(tmp_path / "out") + "-run0-experiment_agent_policy_representation.dat", dtype=np.float64)
     assert np.array_equal(ck, b.get_table(0))
     b.close()
+
+
+@pytest.mark.gpu
+def test_grld_actor_critic_matches_ctypes_harness(grld, tmp_path):
+    """cfg 4 from YAML: same per-agent results as the ctypes harness, and both tables checkpointed in the reference's format."""
+    import grl_b200
+    base = open(os.path.join(ROOT, "cfg/cart_double_pole/ac_tc_cuda.yaml")).read()
+    y = base.replace("agents: 4096", "agents: 64").replace("steps: 5000", "steps: 600") \
+            .replace("steps_per_launch: 500", "steps_per_launch: 100").replace("memory: 131072", "memory: 8192") \
+            .replace("test_interval: 10", "test_interval: 3") \
+            .replace("  save_every: never", "  output: %s\n  save_every: run" % (tmp_path / "ac"))
+    p = tmp_path / "small.yaml"
+    p.write_text(y)
+    out = subprocess.run([grld, "-s", "5", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    rows = [l.split() for l in open(str(tmp_path / "ac") + "-0.txt") if l.startswith("# ") and l[2].isdigit()]
+    assert len(rows) == 64
+    cfg = grl_b200.cart_double_pole_ac_config(memory=8192, test_interval=3, seed=5)
+    b = grl_b200.Batch(cfg, 64)
+    try:
+        while True:
+            b.run(100)
+            r = b.results()
+            if r["steps"].min() >= 600:
+                break
+        for a, row in enumerate(rows):
+            assert int(row[2]) == r["steps"][a] and int(row[3]) == r["episodes"][a]
+            assert float(row[4]) == r["last_return"][a] and float(row[5]) == r["last_test_return"][a]
+        stem = str(tmp_path / "ac") + "-run0-experiment_agent_"
+        actor = np.fromfile(stem + "policy_representation.dat", dtype=np.float64)
+        critic = np.fromfile(stem + "predictor_critic_representation.dat", dtype=np.float64)
+        assert np.array_equal(actor, b.get_actor_table(0)) and np.array_equal(critic, b.get_table(0))
+        assert np.abs(actor).max() <= 20.0 and not np.array_equal(actor, critic)
+        a7 = np.fromfile(stem + "policy_representation-agent7.dat", dtype=np.float64)
+        assert np.array_equal(a7, b.get_actor_table(7))
+    finally:
+        b.close()
