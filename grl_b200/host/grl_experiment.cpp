@@ -33,6 +33,12 @@ void OnlineLearningExperiment::request(ConfigurationRequest *config)
   config->push_back(CRP("agents", "Independent agents learning side by side on the GPU (per run)", agents_, CRP::Configuration, 1));
   config->push_back(CRP("steps_per_launch", "Agent-steps per agent between two reports", steps_per_launch_, CRP::Configuration, 1));
   config->push_back(CRP("device", "CUDA device ordinal", device_, CRP::Configuration, 0));
+  // Hyper-parameter grid on the agents axis: what MultiExperiment `instances` (experiments/multi.cpp:38-60) and a
+  // grlo `parameters` list (bin/optimize.yaml) do with one process per setting.  Agent with global id g runs grid
+  // cell g mod (|alpha| |lambda| |epsilon|), alpha fastest; the other agents of a cell are its repetitions.
+  config->push_back(CRP("sweep_alpha", "Learning rates of the grid (empty: the predictor's alpha)", Vector(), CRP::Configuration));
+  config->push_back(CRP("sweep_lambda", "Trace decay rates of the grid (empty: the predictor's lambda)", Vector(), CRP::Configuration));
+  config->push_back(CRP("sweep_epsilon", "Exploration rates of the grid (empty: the sampler's epsilon)", Vector(), CRP::Configuration));
 }
 
 void OnlineLearningExperiment::configure(Configuration &config)
@@ -44,6 +50,10 @@ void OnlineLearningExperiment::configure(Configuration &config)
   rate_ = config["rate"]; test_interval_ = config["test_interval"]; test_trials_ = config["test_trials"];
   output_ = config["output"].str(); load_file_ = config["load_file"].str(); save_every_ = config["save_every"].str();
   agents_ = config["agents"]; steps_per_launch_ = config["steps_per_launch"]; device_ = config["device"];
+  sweep_alpha_ = config["sweep_alpha"].v(); sweep_lambda_ = config["sweep_lambda"].v(); sweep_epsilon_ = config["sweep_epsilon"].v();
+  for (double v : sweep_alpha_) if (!(v > 0)) throw bad_param("experiment/online_learning:sweep_alpha");
+  for (double v : sweep_lambda_) if (!(v >= 0 && v <= 1)) throw bad_param("experiment/online_learning:sweep_lambda");
+  for (double v : sweep_epsilon_) if (!(v >= 0 && v <= 1)) throw bad_param("experiment/online_learning:sweep_epsilon");
   if (runs_ < 1) throw bad_param("experiment/online_learning:runs");
   if (agents_ < 1) throw bad_param("experiment/online_learning:agents");
   if (steps_per_launch_ < 1) throw bad_param("experiment/online_learning:steps_per_launch");
@@ -146,6 +156,9 @@ void OnlineLearningExperiment::assemble()
   }
   else
     throw Exception(path() + ": agent predictor must be a predictor/sarsa/cuda or a predictor/ac/action/cuda");
+  // the trace ring is sized for the largest lambda of the grid (grlcu_set_hyper checks it)
+  for (double v : sweep_lambda_) c.lambda = std::max(c.lambda, v);
+  if (!sweep_epsilon_.empty() && c.algo == GRLCU_ALGO_AC) throw bad_param("experiment/online_learning:sweep_epsilon");
   c.test_interval = test_interval_;
   c.seed = seed;
   path_.agents = agents_;
@@ -174,13 +187,39 @@ std::vector<double> OnlineLearningExperiment::run()
     path_.release();
     path_.first_agent_id = (long long)rr * agents_;
     grlcu_ctx *ctx = path_.context();
-    std::ofstream ofs;
+    const size_t na = std::max<size_t>(sweep_alpha_.size(), 1), nl = std::max<size_t>(sweep_lambda_.size(), 1),
+                 ne = std::max<size_t>(sweep_epsilon_.size(), 1), cells = na * nl * ne;
+    const bool sweeping = !sweep_alpha_.empty() || !sweep_lambda_.empty() || !sweep_epsilon_.empty();
+    std::vector<size_t> cell_of(n, 0);
+    if (sweeping)
+    {
+      std::vector<double> al(n), la(n), ep(n);
+      for (size_t a = 0; a < n; ++a)
+      {
+        const size_t cell = (size_t)((unsigned long long)path_.first_agent_id + a) % cells;
+        cell_of[a] = cell;
+        al[a] = sweep_alpha_.empty() ? path_.cfg.alpha : sweep_alpha_[cell % na];
+        la[a] = sweep_lambda_.empty() ? path_.cfg.lambda : sweep_lambda_[(cell / na) % nl];
+        ep[a] = sweep_epsilon_.empty() ? path_.cfg.epsilon : sweep_epsilon_[cell / (na * nl)];
+      }
+      CudaPath::check(grlcu_set_hyper(ctx, al.data(), la.data(), ep.data()));
+    }
+    std::ofstream ofs, cfs;
     if (!output_.empty())
     {
       std::ostringstream oss;
       oss << output_ << "-" << rr << identity << ".txt";
       ofs.open(oss.str().c_str());
+      if (sweeping)
+      {
+        std::ostringstream css;
+        css << output_ << "-" << rr << identity << "-cells.txt";
+        cfs.open(css.str().c_str());
+        cfs << "# report cell alpha lambda epsilon agents mean p10 p50 p90   (of the last "
+            << (test_interval_ >= 0 ? "test" : "learning") << " return of the cell's agents)" << std::endl;
+      }
     }
+    size_t report = 0;
     if (!load_file_.empty())
     {
       Configuration loadconfig;
@@ -214,6 +253,25 @@ std::vector<double> OnlineLearningExperiment::run()
       INFO(oss.str());
       if (ofs.is_open()) ofs << oss.str() << std::endl;
       curve.push_back(mean);
+      if (cfs.is_open())
+      {
+        // learning curve per grid cell: mean and percentiles over the cell's repetitions
+        std::vector<std::vector<double>> by_cell(cells);
+        for (size_t a = 0; a < n; ++a) by_cell[cell_of[a]].push_back(r[a]);
+        for (size_t cell = 0; cell < cells; ++cell)
+        {
+          std::vector<double> &v = by_cell[cell];
+          if (v.empty()) continue;
+          std::sort(v.begin(), v.end());
+          auto pct = [&](double q) { return v[std::min(v.size() - 1, (size_t)(q * v.size()))]; };
+          cfs << report << " " << cell << " " << (sweep_alpha_.empty() ? path_.cfg.alpha : sweep_alpha_[cell % na]) << " "
+              << (sweep_lambda_.empty() ? path_.cfg.lambda : sweep_lambda_[(cell / na) % nl]) << " "
+              << (sweep_epsilon_.empty() ? path_.cfg.epsilon : sweep_epsilon_[cell / (na * nl)]) << " " << v.size() << " "
+              << std::setprecision(9) << std::accumulate(v.begin(), v.end(), 0.) / v.size() << " " << pct(0.1) << " " << pct(0.5) << " "
+              << pct(0.9) << std::endl;
+        }
+      }
+      ++report;
       if ((steps_ && min_ss >= (uint64_t)steps_) || (trials_ && min_tt >= (uint32_t)trials_)) break;
     }
     if (save_every_ == "run" && !output_.empty())

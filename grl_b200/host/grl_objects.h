@@ -303,6 +303,7 @@ class OnlineLearningExperiment : public Experiment
     std::string output_, load_file_, save_every_ = "never";
     Environment *environment_ = nullptr; Agent *agent_ = nullptr, *test_agent_ = nullptr;
     CudaPath path_;
+    Vector sweep_alpha_, sweep_lambda_, sweep_epsilon_;   // hyper-parameter grid over the agents axis (MultiExperiment / grlo)
     std::vector<Representation *> checkpoint_reps_;     // tables written by save_every / read by load_file
     bool assembled_ = false;
 };

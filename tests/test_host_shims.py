@@ -144,6 +144,23 @@ def test_error_behaviour(grld, tmp_path):
     assert rc == 0 and json.loads(out)["trace"] == 2
 
 
+def test_sweep_grid_parameters(grld, tmp_path):
+    """sweep_alpha / sweep_lambda / sweep_epsilon: the trace ring is sized for the grid's largest lambda."""
+    rc, out, err = check(grld, os.path.join(ROOT, "cfg/pendulum/sarsa_tc_sweep_cuda.yaml"))
+    assert rc == 0, err
+    got = json.loads(out)
+    assert (got["agents"], got["memory"], got["lambda"], got["alpha"], got["epsilon"]) == (131072, 32768, 0.9, 0.2, 0.05)
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_sweep_cuda.yaml")).read()
+    for old, new, msg in (("sweep_lambda: [0.0, 0.2,", "sweep_lambda: [1.5, 0.2,", "experiment/online_learning:sweep_lambda"),
+                          ("sweep_alpha: [0.05,", "sweep_alpha: [0.0,", "experiment/online_learning:sweep_alpha"),
+                          ("sweep_epsilon: [0.01,", "sweep_epsilon: [-0.01,", "experiment/online_learning:sweep_epsilon")):
+        assert old in base
+        p = tmp_path / "bad.yaml"
+        p.write_text(base.replace(old, new, 1))
+        rc, out, err = check(grld, str(p))
+        assert rc == 1 and msg in err, err
+
+
 def test_run_without_gpu_fails_loudly(grld):
     import torch
     if torch.cuda.is_available():
@@ -223,3 +240,49 @@ def test_grld_actor_critic_matches_ctypes_harness(grld, tmp_path):
         assert np.array_equal(a7, b.get_actor_table(7))
     finally:
         b.close()
+
+
+@pytest.mark.gpu
+def test_grld_sweep_matches_ctypes_harness(grld, tmp_path):
+    """The grid on the agents axis: agent g runs cell g mod cells (alpha fastest); per-cell curves are written."""
+    import grl_b200
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_sweep_cuda.yaml")).read()
+    y = base.replace("agents: 131072", "agents: 160").replace("steps: 10000", "steps: 400") \
+            .replace("memory: 32768", "memory: 4096") \
+            .replace("sweep_alpha: [0.05, 0.1, 0.2, 0.4]", "sweep_alpha: [0.1, 0.4]") \
+            .replace("sweep_lambda: [0.0, 0.2, 0.4, 0.5, 0.65, 0.75, 0.85, 0.9]", "sweep_lambda: [0.0, 0.65, 0.9]") \
+            .replace("sweep_epsilon: [0.01, 0.02, 0.05, 0.1]", "sweep_epsilon: [0.02, 0.3]") \
+            .replace("  runs: 1", "  runs: 1\n  output: %s" % (tmp_path / "sw"))
+    p = tmp_path / "sweep.yaml"
+    p.write_text(y)
+    out = subprocess.run([grld, "-s", "9", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    rows = [l.split() for l in open(str(tmp_path / "sw") + "-0.txt") if l.startswith("# ") and l[2].isdigit()]
+    assert len(rows) == 160
+    n, cells = 160, 12
+    g = np.arange(n) % cells
+    al, la, ep = np.array([0.1, 0.4])[g % 2], np.array([0.0, 0.65, 0.9])[(g // 2) % 3], np.array([0.02, 0.3])[g // 6]
+    cfg = grl_b200.pendulum_config(memory=4096, randomization=1.0, test_interval=-1, seed=9, lambda_=0.9)
+    b = grl_b200.Batch(cfg, n)
+    try:
+        b.set_hyper(al, la, ep)
+        reports = 0
+        while True:
+            b.run(100)
+            reports += 1
+            r = b.results()
+            if r["steps"].min() >= 400:
+                break
+        for a, row in enumerate(rows):
+            assert int(row[2]) == r["steps"][a] and int(row[3]) == r["episodes"][a] and float(row[4]) == r["last_return"][a]
+    finally:
+        b.close()
+    cell_rows = [l.split() for l in open(str(tmp_path / "sw") + "-0-cells.txt") if not l.startswith("#")]
+    assert len(cell_rows) == reports * cells
+    last = [c for c in cell_rows if int(c[0]) == reports - 1]
+    for c in last:
+        cell = int(c[1])
+        members = r["last_return"][g == cell]
+        assert (float(c[2]), float(c[3]), float(c[4])) == (al[cell], la[cell], ep[cell]) and int(c[5]) == members.size
+        assert abs(float(c[6]) - members.mean()) <= 1e-6 * abs(members.mean())
+        assert members.min() <= float(c[7]) <= float(c[8]) <= float(c[9]) <= members.max()
