@@ -10,7 +10,7 @@ from . import build as _build
 MAX_DIMS, MAX_ACTIONS, MAX_STATE = 8, 8, 7
 DYN_PENDULUM, DYN_CART_POLE, DYN_CART_DOUBLE_POLE = 0, 1, 2
 TRACE_NONE, TRACE_REPLACING, TRACE_ACCUMULATING = 0, 1, 2
-ALGO_SARSA, ALGO_AC = 0, 1
+ALGO_SARSA, ALGO_AC, ALGO_Q, ALGO_EXPECTED_SARSA = 0, 1, 2, 3
 RESET_TABLES, RESET_AGENTS, RESET_STATS = 1, 2, 4
 INVALID = 0xFFFFFFFF
 
@@ -34,6 +34,7 @@ class Config(C.Structure):
         ("sigma", C.c_double), ("actor_alpha", C.c_double),
         ("action_min", C.c_double), ("action_max", C.c_double),
         ("actor_resolution", C.c_double * MAX_DIMS), ("actor_wrapping", C.c_double * MAX_DIMS),
+        ("target_epsilon", C.c_double),
     ]
 
 

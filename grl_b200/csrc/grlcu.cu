@@ -94,7 +94,9 @@ static int supported(const grlcu_config *cfg)
     if (cfg->sigma < 0) return fail(GRLCU_ERR_ARG, "sigma must be >= 0");
     return 0;
   }
-  if (cfg->algo != GRLCU_ALGO_SARSA) return fail(GRLCU_ERR_UNSUPPORTED, "unknown algo %d", cfg->algo);
+  if (cfg->algo != GRLCU_ALGO_SARSA && cfg->algo != GRLCU_ALGO_Q && cfg->algo != GRLCU_ALGO_EXPECTED_SARSA)
+    return fail(GRLCU_ERR_UNSUPPORTED, "unknown algo %d", cfg->algo);
+  if (cfg->algo == GRLCU_ALGO_EXPECTED_SARSA && cfg->target_epsilon > 1) return fail(GRLCU_ERR_ARG, "target_epsilon > 1");
   if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE)
     return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for SARSA", cfg->dynamics);
   if (cfg->n_actions != 3) return fail(GRLCU_ERR_UNSUPPORTED, "n_actions %d: kernels are instantiated for 3", cfg->n_actions);
@@ -199,6 +201,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   p.trace_kind = cfg->trace;
   p.force_slow = getenv("GRLCU_FORCE_SLOW") ? atoi(getenv("GRLCU_FORCE_SLOW")) : 0;
   p.mode = getenv("GRLCU_MODE") ? atoi(getenv("GRLCU_MODE")) : 0;
+  p.target_kind = cfg->algo == GRLCU_ALGO_Q ? 1 : cfg->algo == GRLCU_ALGO_EXPECTED_SARSA ? 2 : 0;
+  p.target_epsilon = cfg->target_epsilon;
   p.trace_cap = trace_capacity_for(cfg->gamma * cfg->lambda, cfg->trace);
   if (p.trace_cap < 0 || p.trace_cap > 160)
   {

@@ -11,6 +11,7 @@
 //   counters / returns [n]
 // Citations: /root/reference/base.
 #pragma once
+#include <math_constants.h>
 #include "grlcu_device.cuh"
 
 namespace grlcu {
@@ -40,6 +41,8 @@ struct Params
   uint64_t *dupmask;          // bit k: trace entry of age k holds duplicate indices (fast paths: cap <= 64)
   int32_t  force_slow;        // 1: always take the sequential update path (A/B testing)
   int32_t  mode;              // 0: trace value cache where eligible, 1: uncached
+  int32_t  target_kind;       // bootstrap value: 0 Q(s',a') (SARSA), 1 max_a Q(s',a) (Q-learning), 2 policy value (expected SARSA)
+  double   target_epsilon;    // expected SARSA: target policy's epsilon (< 0: greedy sampler)
   double   *cache_val;        // [cap*T][n] cached trace weights (grlcu_cached.cuh)
   uint32_t *cache_mask;       // [cap][n] valid bits per trace entry
   uint64_t *act_ctr, *test_act_ctr, *episode_ctr, *tt, *ss, *swept;
@@ -65,6 +68,54 @@ struct ReplayIO
 };
 
 struct Draws { double u; uint32_t r_explore, r_tie; };
+
+// What the predictor bootstraps from at s' (the policy's Q(s', .) re-used: no table write lies in between):
+//   SARSAPredictor (sarsa.cpp:103-104): Q(s', a');
+//   QPredictor (advantage.cpp:84-90): v = -inf; v = fmax(v, Q(s', a_k)) over the discretizer's options, in order;
+//   ExpectedSARSAPredictor (sarsa.cpp:172-173) -> QPolicy::value (q.cpp:56-68): sum_k q_k * dist_k, dist from
+//   GreedySampler::distribution (greedy.cpp:88-98: 1/man on the maxima) or EpsilonGreedySampler::distribution
+//   (greedy.cpp:220-238, one epsilon, decay_ = 1: a 1 becomes 1 - eps, then every entry += eps / A).
+template <int A>
+__device__ __forceinline__ double bootstrap_value(const double (&q)[A], int ai, int kind, double target_epsilon)
+{
+  if (kind == 1)
+  {
+    double v = -CUDART_INF;
+#pragma unroll
+    for (int kk = 0; kk < A; ++kk) v = fmax(v, q[kk]);
+    return v;
+  }
+  if (kind == 2)
+  {
+    int mai = 0, man = 1;
+#pragma unroll
+    for (int ii = 1; ii < A; ++ii)
+    {
+      if (q[ii] > q[mai]) { mai = ii; man = 1; }
+      else if (q[ii] == q[mai]) man++;
+    }
+    double qm = q[0];
+#pragma unroll
+    for (int ii = 1; ii < A; ++ii) if (ii == mai) qm = q[ii];
+    double v = 0;
+#pragma unroll
+    for (int ii = 0; ii < A; ++ii)
+    {
+      double d = (q[ii] == qm) ? 1. / man : 0.;
+      if (target_epsilon >= 0)
+      {
+        if (d == 1) d = 1 - 1. * target_epsilon;
+        d += 1. * target_epsilon / A;
+      }
+      v += q[ii] * d;
+    }
+    return v;
+  }
+  double qn = q[0];
+#pragma unroll
+  for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
+  return qn;
+}
 
 // greedy.cpp:47-61 findmax + 63-86 / 151-218 sample (epsilon_.size() == 1, decay_ = 1)
 template <int A>

@@ -136,9 +136,7 @@ __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, co
 #pragma unroll
       for (int aa = 0; aa < A; ++aa) o_q[(size_t)aa * p.n + a] = q[aa];
     }
-    qn = q[0];
-#pragma unroll
-    for (int aa = 1; aa < A; ++aa) if (aa == ai) qn = q[aa];
+    qn = bootstrap_value<A>(q, ai, p.target_kind, p.target_epsilon);
   }
   else if (learn)
   {

@@ -13,6 +13,8 @@ REGISTER_CONFIGURABLE(CudaBatchedEnvironment)
 REGISTER_CONFIGURABLE(CudaTileCodingProjector)
 REGISTER_CONFIGURABLE(CudaLinearRepresentation)
 REGISTER_CONFIGURABLE(CudaSARSAPredictor)
+REGISTER_CONFIGURABLE(CudaQPredictor)
+REGISTER_CONFIGURABLE(CudaExpectedSARSAPredictor)
 REGISTER_CONFIGURABLE(CudaTDPredictor)
 REGISTER_CONFIGURABLE(CudaACPredictor)
 
@@ -283,6 +285,47 @@ void CudaSARSAPredictor::contribute(CudaPath *p) const
   p->cfg.trace = trace_ ? trace_->kind : GRLCU_TRACE_NONE;
   p->cfg.algo = GRLCU_ALGO_SARSA;
   p->have_predictor = true;
+}
+
+// ---- predictor/q/cuda (advantage.cpp:35-69), predictor/expected_sarsa/cuda (sarsa.cpp:134-165) ------------------
+void CudaQPredictor::request(ConfigurationRequest *config)
+{
+  CudaSARSAPredictor::request(config);
+  config->push_back(CRP("discretizer", "discretizer.action", "Action discretizer", discretizer_));
+}
+
+void CudaQPredictor::configure(Configuration &config)
+{
+  CudaSARSAPredictor::configure(config);
+  discretizer_ = dynamic_cast<UniformDiscretizer *>(config["discretizer"].ptr());
+  if (!discretizer_) throw Exception(path() + ": discretizer must be a discretizer/uniform");
+}
+
+void CudaQPredictor::contribute(CudaPath *p) const
+{
+  CudaSARSAPredictor::contribute(p);
+  p->cfg.algo = GRLCU_ALGO_Q;
+}
+
+void CudaExpectedSARSAPredictor::request(ConfigurationRequest *config)
+{
+  CudaSARSAPredictor::request(config);
+  config->push_back(CRP("policy", "mapping/policy/discrete/value", "Value based target policy", policy_));
+}
+
+void CudaExpectedSARSAPredictor::configure(Configuration &config)
+{
+  CudaSARSAPredictor::configure(config);
+  policy_ = dynamic_cast<QPolicy *>(config["policy"].ptr());
+  if (!policy_ || !policy_->sampler) throw Exception(path() + ": policy must be a mapping/policy/discrete/value/q with a sampler");
+}
+
+void CudaExpectedSARSAPredictor::contribute(CudaPath *p) const
+{
+  CudaSARSAPredictor::contribute(p);
+  p->cfg.algo = GRLCU_ALGO_EXPECTED_SARSA;
+  // GreedySampler::distribution (greedy.cpp:88-98) or EpsilonGreedySampler::distribution (greedy.cpp:220-238)
+  p->cfg.target_epsilon = dynamic_cast<EpsilonGreedySampler *>(policy_->sampler) ? policy_->sampler->epsilon : -1.;
 }
 
 // ---- predictor/critic/td/cuda (predictors/td.cpp:35-66) ----------------------------------------------------

@@ -92,6 +92,16 @@ void OnlineLearningExperiment::assemble()
     if (pred->projector() != pol->projector || pred->representation() != pol->representation)
       throw Exception(path() + ": predictor and policy must share one projector and one representation");
     if (!qp->discretizer || !qp->sampler) throw Exception(path() + ": policy needs a discretizer and a sampler");
+    if (CudaQPredictor *q = dynamic_cast<CudaQPredictor *>(pred))
+      if (q->discretizer() != qp->discretizer) throw Exception(path() + ": predictor/q/cuda must maximise over the policy's discretizer");
+    if (CudaExpectedSARSAPredictor *es = dynamic_cast<CudaExpectedSARSAPredictor *>(pred))
+    {
+      QPolicy *tp = es->targetPolicy();
+      if (tp->projector != pol->projector || tp->representation != pol->representation || tp->discretizer != qp->discretizer)
+        throw Exception(path() + ": the expected-SARSA target policy must evaluate the learning agent's discretizer, projector and representation");
+      if (!sweep_epsilon_.empty() && tp->sampler == qp->sampler)
+        throw Exception(path() + ": sweep_epsilon with an on-policy expected-SARSA target is not supported (one target epsilon per context)");
+    }
     if (test_agent_ && test_agent_->policy)
     {
       QPolicy *tp = dynamic_cast<QPolicy *>(test_agent_->policy);

@@ -241,12 +241,40 @@ class CudaSARSAPredictor : public Predictor
     void request(ConfigurationRequest *config) override;
     void configure(Configuration &config) override;
     void reconfigure(const Configuration &config) override;
-    void contribute(CudaPath *path) const;
+    virtual void contribute(CudaPath *path) const;
     Projector *projector() const { return projector_; }
     Representation *representation() const { return representation_; }
-  private:
+  protected:
     double alpha_ = 0.2, gamma_ = 0.97, lambda_ = 0.65;
     Projector *projector_ = nullptr; Representation *representation_ = nullptr; Trace *trace_ = nullptr;
+};
+
+/// predictor/q/cuda (stands in for predictor/critic/q, predictors/advantage.cpp:35-110): Q-learning; the SARSA
+/// kernels with the target bootstrapping from max_a Q(s', a).
+class CudaQPredictor : public CudaSARSAPredictor
+{
+  public:
+    TYPEINFO("predictor/q/cuda", "Q-learning off-policy value function predictor fused with the environment step on a B200")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void contribute(CudaPath *path) const override;
+    UniformDiscretizer *discretizer() const { return discretizer_; }
+  private:
+    UniformDiscretizer *discretizer_ = nullptr;
+};
+
+/// predictor/expected_sarsa/cuda (stands in for predictor/critic/expected_sarsa, predictors/sarsa.cpp:134-194):
+/// the target bootstraps from the value of s' under the target policy (greedy or epsilon-greedy sampler).
+class CudaExpectedSARSAPredictor : public CudaSARSAPredictor
+{
+  public:
+    TYPEINFO("predictor/expected_sarsa/cuda", "Expected SARSA value function predictor fused with the environment step on a B200")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    void contribute(CudaPath *path) const override;
+    QPolicy *targetPolicy() const { return policy_; }
+  private:
+    QPolicy *policy_ = nullptr;
 };
 
 /// predictor/critic/td/cuda (stands in for predictor/critic/td, predictors/td.cpp:35-66): TD(lambda) on V(s);

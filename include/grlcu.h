@@ -33,7 +33,9 @@ extern "C" {
 
 enum { GRLCU_DYN_PENDULUM = 0, GRLCU_DYN_CART_POLE = 1, GRLCU_DYN_CART_DOUBLE_POLE = 2 };
 enum { GRLCU_TRACE_NONE = 0, GRLCU_TRACE_REPLACING = 1, GRLCU_TRACE_ACCUMULATING = 2 };
-enum { GRLCU_ALGO_SARSA = 0, GRLCU_ALGO_AC = 1 };
+/* predictor: predictor/critic/sarsa (sarsa.cpp:98-124) | predictor/ac/action + predictor/critic/td (ac.cpp, td.cpp) |
+ * predictor/critic/q (advantage.cpp:71-110) | predictor/critic/expected_sarsa (sarsa.cpp:167-194) */
+enum { GRLCU_ALGO_SARSA = 0, GRLCU_ALGO_AC = 1, GRLCU_ALGO_Q = 2, GRLCU_ALGO_EXPECTED_SARSA = 3 };
 enum { GRLCU_OK = 0, GRLCU_ERR_ARG = 1, GRLCU_ERR_CUDA = 2, GRLCU_ERR_UNSUPPORTED = 3,
        GRLCU_ERR_NOMEM = 4 };
 enum { GRLCU_RESET_TABLES = 1, GRLCU_RESET_AGENTS = 2, GRLCU_RESET_STATS = 4 };
@@ -65,6 +67,8 @@ typedef struct grlcu_config
   double  action_min, action_max;       /* task action_min/max = actor output_min/max (AC) */
   double  actor_resolution[GRLCU_MAX_DIMS];  /* AC: the actor's projector; must equal resolution/wrapping, */
   double  actor_wrapping[GRLCU_MAX_DIMS];    /* which describe the critic's (obs dims only, no action)     */
+  double  target_epsilon;     /* GRLCU_ALGO_EXPECTED_SARSA: the target policy's sampler (predictor `policy`,
+                                 sarsa.cpp:145): < 0 sampler/greedy, else sampler/epsilon_greedy's epsilon */
 } grlcu_config;
 
 typedef struct grlcu_ctx grlcu_ctx;

@@ -56,7 +56,7 @@ extern "C" {
 
 enum { ORC_DYN_PENDULUM = 0, ORC_DYN_CART_POLE = 1, ORC_DYN_CART_DOUBLE_POLE = 2 };
 enum { ORC_TRACE_NONE = 0, ORC_TRACE_REPLACING = 1, ORC_TRACE_ACCUMULATING = 2 };
-enum { ORC_ALGO_SARSA = 0, ORC_ALGO_AC = 1 };
+enum { ORC_ALGO_SARSA = 0, ORC_ALGO_AC = 1, ORC_ALGO_Q = 2, ORC_ALGO_EXPECTED_SARSA = 3 };
 enum { ORC_RNG_PHILOX = 0, ORC_RNG_GLIBC = 1 };
 
 /* Same field order as grlcu_config (include/grlcu.h) so one ctypes Structure
@@ -88,6 +88,8 @@ typedef struct orc_config
   double  action_min, action_max;
   double  actor_resolution[ORC_MAX_DIMS];
   double  actor_wrapping[ORC_MAX_DIMS];
+  /* predictor/critic/expected_sarsa: the target policy's sampler; < 0: sampler/greedy, else epsilon-greedy */
+  double  target_epsilon;
 } orc_config;
 
 /* Everything observable about one agent-step (one iteration of

@@ -302,15 +302,50 @@ static double task_start(orc_agent *a, int test, double *state)
   return r;
 }
 
-/* ---- SARSAPredictor::criticize (sarsa.cpp:98-124), tau = 1 --------------- */
+/* QPolicy::value (q.cpp:56-68) with GreedySampler::distribution (greedy.cpp:88-98) or
+ * EpsilonGreedySampler::distribution (greedy.cpp:220-238, one epsilon, decay_ = 1): sum of q * dist in order. */
+static double policy_value(const double *q, int A, double target_epsilon)
+{
+  int mai, man;
+  double v = 0;
+  findmax(q, A, &mai, &man);
+  for (int ii = 0; ii < A; ++ii)
+  {
+    double d = (q[ii] == q[mai]) ? 1. / man : 0.;
+    if (target_epsilon >= 0)
+    {
+      if (d == 1) d = 1 - 1. * target_epsilon;
+      d += 1. * target_epsilon / A;
+    }
+    v += q[ii] * d;
+  }
+  return v;
+}
+
+/* ---- SARSAPredictor::criticize (sarsa.cpp:98-124), tau = 1; with algo = Q: QPredictor::criticize
+ * (advantage.cpp:71-110, target = r + gamma max_a Q(s',a) by an fmax chain from -inf); with algo =
+ * EXPECTED_SARSA: ExpectedSARSAPredictor::criticize (sarsa.cpp:167-194, target = r + gamma policy->value(s')).
+ * q_next: Q(s', .) for every action (the predictor re-reads what the policy just read: no write in between). */
 static void sarsa_update(orc_agent *a, double reward, const uint32_t *next_idx /* NULL if absorbing */,
-                         orc_record *rec)
+                         const double *q_next, orc_record *rec)
 {
   const orc_config *c = &a->c;
   const int T = c->tilings;
   double target = reward;
   if (next_idx)
-    target += c->gamma * table_read(a->table, next_idx, T, -DBL_MAX, DBL_MAX);  /* pow(gamma,1) */
+  {
+    double v;
+    if (c->algo == ORC_ALGO_Q)
+    {
+      v = -INFINITY;
+      for (int kk = 0; kk < c->n_actions; ++kk) v = fmax(v, q_next[kk]);
+    }
+    else if (c->algo == ORC_ALGO_EXPECTED_SARSA)
+      v = policy_value(q_next, c->n_actions, c->target_epsilon);
+    else
+      v = table_read(a->table, next_idx, T, -DBL_MAX, DBL_MAX);
+    target += c->gamma * v;                                                     /* pow(gamma,1) */
+  }
   double qp = table_read(a->table, a->prev_idx, T, -DBL_MAX, DBL_MAX);
   double delta = target - qp;
   int swept = 0, entries = 0;
@@ -478,7 +513,7 @@ int orc_step(orc_agent *a, orc_record *rec)
   if (terminal == 2)
   {
     /* TDAgent::end (td.cpp:76-81): update without bootstrap; FixedAgent::end: nothing */
-    if (!a->test) sarsa_update(a, reward, NULL, rec);
+    if (!a->test) sarsa_update(a, reward, NULL, NULL, rec);
   }
   else
   {
@@ -497,7 +532,7 @@ int orc_step(orc_agent *a, orc_record *rec)
       }
       rec->action_index = ai;
     }
-    if (!a->test) sarsa_update(a, reward, idx + ai * T, rec);
+    if (!a->test) sarsa_update(a, reward, idx + ai * T, q, rec);
     memcpy(a->prev_obs, obs, sizeof(obs));
     a->prev_action = action;
     memcpy(a->prev_idx, idx + ai * T, (size_t)T * sizeof(uint32_t));

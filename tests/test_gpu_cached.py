@@ -46,6 +46,9 @@ def _run(G, mk, mode, n, launches, sweep=False, **kw):
     # trace capacity 35 (> 32 entries: the duplicate mask is 64 bits wide) with per-agent hyperparameters
     dict(which="pendulum", n=128, memory=65536, launches=[120, 260], test_interval=5, lambda_=0.9, sweep=True),
     dict(which="pendulum", n=64, memory=521, launches=[300], test_interval=-1, lambda_=0.9, sweep=True),
+    # Q-learning / expected SARSA targets through the cache
+    dict(which="pendulum", n=64, memory=16384, launches=[150, 150], test_interval=3, algo=2),
+    dict(which="cart_pole", n=32, memory=65536, launches=[300], test_interval=-1, algo=3, target_epsilon=0.1),
     # actor-critic (BASELINE configs[3]): the critic's trace goes through the cache, the actor table does not
     dict(which="ac", n=64, memory=131072, launches=[90, 1, 310], test_interval=3),
     dict(which="ac", n=32, memory=509, launches=[350], test_interval=-1, actor_alpha=0.5, sigma=15.0),

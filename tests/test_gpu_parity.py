@@ -180,6 +180,19 @@ def test_replay_per_agent_hyperparameters(G, orc):
             randomization=1.0, test_interval=-1, lambda_=0.9)
 
 
+def test_replay_q_learning_and_expected_sarsa(G, orc):
+    """Sibling predictors on the same kernels: predictor/critic/q and predictor/critic/expected_sarsa
+    (greedy and epsilon-greedy target policy) differ from SARSA only in what the target bootstraps from."""
+    for algo, eps in ((O.ALGO_Q, 0.0), (O.ALGO_EXPECTED_SARSA, -1.0), (O.ALGO_EXPECTED_SARSA, 0.05)):
+        _replay(G, G.pendulum_config, O.pendulum_config, n=32, steps=260, mem=16384,
+                randomization=1.0, test_interval=3, algo=algo, target_epsilon=eps)
+    _replay(G, G.cart_pole_config, O.cart_pole_config, n=16, steps=300, mem=262144,
+            randomization=1.0, test_interval=-1, epsilon=0.2, algo=O.ALGO_Q)
+    # small table: equal Q-values (ties) and duplicate indices
+    _replay(G, G.pendulum_config, O.pendulum_config, n=32, steps=200, mem=67,
+            randomization=1.0, test_interval=-1, algo=O.ALGO_EXPECTED_SARSA, target_epsilon=0.3)
+
+
 def test_replay_accumulating_and_no_trace(G, orc):
     _replay(G, G.pendulum_config, O.pendulum_config, n=16, steps=150, mem=8192,
             randomization=1.0, test_interval=-1, trace=2)

@@ -68,6 +68,8 @@ def swap_types(text):
     text = re.sub(r"type: projector/tile_coding\b", "type: projector/tile_coding/cuda", text)
     text = text.replace("type: representation/parameterized/linear", "type: representation/linear/cuda")
     text = text.replace("type: predictor/critic/sarsa", "type: predictor/sarsa/cuda")
+    text = text.replace("type: predictor/critic/q", "type: predictor/q/cuda")
+    text = text.replace("type: predictor/critic/expected_sarsa", "type: predictor/expected_sarsa/cuda")
     # actor-critic (cfg/cart_double_pole/ac.yaml): the two predictors; the policy's type name in that file is stale
     # in the reference itself (TYPEINFO is mapping/policy/action, policies/action.h:44)
     text = text.replace("type: predictor/ac/action", "type: predictor/ac/action/cuda")
@@ -119,6 +121,36 @@ def test_actor_critic_error_behaviour(grld, tmp_path):
         p.write_text(base.replace(old, new, 1))
         rc, out, err = check(grld, str(p))
         assert rc == 1 and msg in err, (old, err)
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_CFG), reason="reference tree not present (GPU box)")
+def test_reference_q_learning_yaml_and_expected_sarsa(grld, tmp_path):
+    """cfg/pendulum/q_tc.yaml with the types swapped -> GRLCU_ALGO_Q; the same tree with an expected-SARSA predictor
+    whose target policy is the greedy test policy / the epsilon-greedy learning policy."""
+    src = swap_types(open(os.path.join(REF_CFG, "pendulum/q_tc.yaml")).read())
+    dst = tmp_path / "q.yaml"
+    dst.write_text(src)
+    rc, out, err = check(grld, str(dst))
+    assert rc == 0, err
+    got = json.loads(out)
+    assert (got["algo"], got["dynamics"], got["memory"], got["trace"], got["epsilon"]) == (2, 0, 8388608, 1, 0.05)
+    es = src.replace("type: predictor/q/cuda", "type: predictor/expected_sarsa/cuda") \
+            .replace("      discretizer: experiment/agent/policy/discretizer\n      projector: experiment/agent/policy/projector",
+                     "      policy:\n        type: mapping/policy/discrete/value/q\n"
+                     "        discretizer: experiment/agent/policy/discretizer\n        projector: experiment/agent/policy/projector\n"
+                     "        representation: experiment/agent/policy/representation\n        sampler:\n          type: sampler/greedy\n"
+                     "      projector: experiment/agent/policy/projector", 1)
+    assert "type: sampler/greedy\n      projector" in es
+    dst.write_text(es)
+    rc, out, err = check(grld, str(dst))
+    assert rc == 0, err
+    assert (json.loads(out)["algo"], json.loads(out)["target_epsilon"]) == (3, -1.0)
+    a = es.index("      policy:\n        type: mapping/policy/discrete/value/q\n        discretizer: experiment/agent")
+    b = es.index("      projector: experiment/agent/policy/projector", a)
+    dst.write_text(es[:a] + "      policy: experiment/agent/policy\n" + es[b:])
+    rc, out, err = check(grld, str(dst))
+    assert rc == 0, err
+    assert (json.loads(out)["algo"], json.loads(out)["target_epsilon"]) == (3, 0.05)
 
 
 def test_error_behaviour(grld, tmp_path):

@@ -116,3 +116,58 @@ def test_actor_critic_oracle_learns_and_respects_limits(orc):
         assert np.mean(tests[-15:]) > 1.5 * np.mean(tests[:15])      # 6.2 per balanced step: longer episodes
     finally:
         orc.orc_destroy(a)
+
+
+def test_q_learning_and_expected_sarsa_targets(orc):
+    """predictor/critic/q (advantage.cpp:84-90) and predictor/critic/expected_sarsa (sarsa.cpp:172-173 ->
+    q.cpp:56-68, greedy.cpp:88-98,220-238): the oracle's targets against a direct restatement on its own
+    recorded Q(s', .), and Q-learning still learns the pendulum swing-up."""
+    import ctypes as C
+    import numpy as np
+    import _oracle as O
+
+    def value(q, eps):
+        mx = max(q)
+        man = sum(1 for x in q if x == mx)
+        v = 0.0
+        for x in q:
+            d = 1.0 / man if x == mx else 0.0
+            if eps >= 0:
+                if d == 1:
+                    d = 1 - 1.0 * eps
+                d += 1.0 * eps / len(q)
+            v += x * d
+        return v
+
+    for algo, eps in ((O.ALGO_Q, 0.0), (O.ALGO_EXPECTED_SARSA, -1.0), (O.ALGO_EXPECTED_SARSA, 0.05), (O.ALGO_SARSA, 0.0)):
+        c = O.pendulum_config(memory=4096, randomization=1.0, test_interval=-1, algo=algo, target_epsilon=eps)
+        a = orc.orc_create(C.byref(c), 11)
+        rec = O.Record()
+        checked = 0
+        try:
+            for _ in range(400):
+                orc.orc_step(a, C.byref(rec))
+                if rec.terminal == 2 or rec.test:
+                    continue
+                q = [rec.q[i] for i in range(3)]
+                if algo == O.ALGO_Q:
+                    want = rec.reward + c.gamma * max(q)
+                elif algo == O.ALGO_EXPECTED_SARSA:
+                    want = rec.reward + c.gamma * value(q, eps)
+                else:
+                    want = rec.reward + c.gamma * q[rec.action_index]
+                assert rec.target == want
+                checked += 1
+        finally:
+            orc.orc_destroy(a)
+        assert checked > 300
+    # learning: Q-learning reaches the same return band as SARSA on the swing-up
+    c = O.pendulum_config(memory=65536, randomization=0.0, test_interval=-1, algo=O.ALGO_Q)
+    a = orc.orc_create(C.byref(c), 2)
+    try:
+        orc.orc_run(a, 100 * 300)
+        lr = C.c_double()
+        orc.orc_stats(a, None, None, None, C.byref(lr), None)
+        assert lr.value > -2500
+    finally:
+        orc.orc_destroy(a)
