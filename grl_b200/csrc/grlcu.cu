@@ -3,6 +3,7 @@
 #include "../../include/grlcu.h"
 #include "grlcu_kernels.cuh"
 #include "grlcu_ac.cuh"
+#include "grlcu_coop.cuh"
 
 #include <cuda_runtime.h>
 #include <cfloat>
@@ -46,6 +47,8 @@ struct grlcu_ctx
   double *d_alpha, *d_lambda, *d_epsilon, *d_start;
   int64_t launches;
   int sm_count;
+  CoopArrays coop;            // agent-major cache of one cohort (grlcu_coop.cuh), allocated on first use
+  int coop_cohort, coop_lanes;
   bool cache_live;            // the trace value cache of the fused kernel is live (tables hold directory sentinels)
   // run-kernel timing (events recorded around every k_run launch)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending;
@@ -148,6 +151,11 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   c->cache_live = false;
   c->block = 64;
   c->sm_count = 148;
+  memset(&c->coop, 0, sizeof(c->coop));
+  c->coop_cohort = 4096;
+  if (const char *b = getenv("GRLCU_COOP_COHORT")) { int v = atoi(b); if (v >= 4) c->coop_cohort = v; }
+  c->coop_lanes = 4;
+  if (const char *b = getenv("GRLCU_COOP_LANES")) { int v = atoi(b); if (v == 2 || v == 4 || v == 8 || v == 16) c->coop_lanes = v; }
   cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
   if (const char *b = getenv("GRLCU_BLOCK")) { int v = atoi(b); if (v >= 32 && v <= kMaxBlock && v % 32 == 0) c->block = v; }
 
@@ -589,6 +597,43 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
   if (cohort <= 0 || cohort > n) cohort = n;
   // the cache stays live between launches (values return to the tables lazily, see ensure_plain) unless the
   // agents run in cohorts or GRLCU_EAGER_CLOSE is set
+  // GRLCU_MODE=2: sixteen lanes per agent, L2-sized cohorts (grlcu_coop.cuh); same eligibility as the value cache
+  if (c->p.mode == 2 && c->cfg.algo != GRLCU_ALGO_AC && c->cfg.tilings == kLanes && !c->p.force_slow &&
+      c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64 && c->cfg.n_actions == 3)
+  {
+    if (int r = ensure_plain(c)) return r;
+    int cc = c->coop_cohort < n ? c->coop_cohort : n;
+    if (cohort < cc) cc = cohort;
+    if (!c->coop.cv)
+    {
+      const size_t slots = (size_t)c->coop_cohort * c->p.trace_cap * kLanes;
+      if (int r = dalloc(c, &c->coop.cv, slots)) return r;
+      if (int r = dalloc(c, &c->coop.ring, slots)) return r;
+      if (int r = dalloc(c, &c->coop.vmask, (size_t)c->coop_cohort * c->p.trace_cap)) return r;
+    }
+    for (int begin = 0; begin < n; begin += cc)
+    {
+      const int end = begin + cc < n ? begin + cc : n;
+      cudaEvent_t e0 = get_event(c), e1 = get_event(c);
+      CU(cudaEventRecord(e0, c->stream));
+#define COOP(D, L, MB) k_run_coop<D, 3, L, MB><<<((end - begin) * L + kMaxBlock - 1) / kMaxBlock, kMaxBlock, 0, c->stream>>>(c->p, c->coop, begin, end, n_steps)
+      const bool pend = c->cfg.dynamics == GRLCU_DYN_PENDULUM;
+      const bool roomy = getenv("GRLCU_COOP_ROOMY") != nullptr;     // 255 registers, half the resident warps
+      switch (c->coop_lanes)
+      {
+        case 16: if (pend) COOP(0, 16, 8); else COOP(1, 16, 8); break;
+        case 8:  if (pend) COOP(0, 8, 8); else COOP(1, 8, 8); break;
+        case 2:  if (roomy) { if (pend) COOP(0, 2, 4); else COOP(1, 2, 4); } else { if (pend) COOP(0, 2, 8); else COOP(1, 2, 8); } break;
+        default: if (roomy) { if (pend) COOP(0, 4, 4); else COOP(1, 4, 4); } else { if (pend) COOP(0, 4, 8); else COOP(1, 4, 8); } break;
+      }
+#undef COOP
+      CU(cudaEventRecord(e1, c->stream));
+      c->ev_pending.push_back({e0, e1});
+      c->launches++;
+    }
+    CU(cudaGetLastError());
+    return 0;
+  }
   const bool lazy = cohort == n && !getenv("GRLCU_EAGER_CLOSE");
   if (!lazy) if (int r = ensure_plain(c)) return r;
   for (int begin = 0; begin < n; begin += cohort)

@@ -10,12 +10,18 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _run(G, mk, mode, n, launches, sweep=False, **kw):
+def _run(G, mk, mode, n, launches, sweep=False, coop_cohort=None, coop_lanes=None, **kw):
     os.environ["GRLCU_MODE"] = str(mode)
+    if coop_cohort:
+        os.environ["GRLCU_COOP_COHORT"] = str(coop_cohort)
+    if coop_lanes:
+        os.environ["GRLCU_COOP_LANES"] = str(coop_lanes)
     try:
         b = G.Batch(mk(**kw), n)
     finally:
         os.environ.pop("GRLCU_MODE", None)
+        os.environ.pop("GRLCU_COOP_COHORT", None)
+        os.environ.pop("GRLCU_COOP_LANES", None)
     try:
         if sweep:
             # per-agent hyperparameters (MultiExperiment / grlo sweeps): trace lengths differ inside a warp
@@ -62,12 +68,19 @@ def test_cached_equals_uncached(case):
     if which != "ac":
         case["randomization"] = 1.0
     r1, t1, s1 = _run(G, mk, 1, n, launches, **case)
-    r0, t0, s0 = _run(G, mk, 0, n, launches, **case)
-    assert not np.isnan(t0).any()                      # no directory sentinel left in a table
-    assert np.array_equal(t0, t1)
-    for k in r0:
-        if k != "table_writes":               # roofline accounting: differs between the two paths by design
-            assert np.array_equal(r0[k], r1[k]), k
-    for a, b in zip(s0, s1):
-        assert np.array_equal(a[0], b[0]) and a[1:] == b[1:]
-    assert int(r0["steps"].sum()) > 0 and int(r0["swept"].sum()) >= 0
+    # mode 0: one thread per agent with the value cache; mode 2: sixteen lanes per agent in L2-sized cohorts
+    # (grlcu_coop.cuh; SARSA family only), once as a single cohort and once as several ragged ones
+    variants = [dict(mode=0)]
+    if which != "ac":
+        variants += [dict(mode=2, coop_lanes=4), dict(mode=2, coop_lanes=4, coop_cohort=20), dict(mode=2, coop_lanes=16),
+                     dict(mode=2, coop_lanes=8, coop_cohort=28), dict(mode=2, coop_lanes=2)]
+    for v in variants:
+        r0, t0, s0 = _run(G, mk, v["mode"], n, launches, coop_cohort=v.get("coop_cohort"), coop_lanes=v.get("coop_lanes"), **case)
+        assert not np.isnan(t0).any(), v                   # no directory sentinel left in a table
+        assert np.array_equal(t0, t1), v
+        for k in r0:
+            if k != "table_writes":               # roofline accounting: differs between the paths by design
+                assert np.array_equal(r0[k], r1[k]), (v, k)
+        for a, b in zip(s0, s1):
+            assert np.array_equal(a[0], b[0]) and a[1:] == b[1:], v
+        assert int(r0["steps"].sum()) > 0 and int(r0["swept"].sum()) >= 0
