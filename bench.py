@@ -59,13 +59,18 @@ def make_config(mod, args):
 
 
 def sweep_hyper(first_id, n):
-    """Per-agent (alpha, lambda, epsilon): grid cell = global agent id mod 128, seeds fill the rest."""
+    """Per-agent (alpha, lambda, epsilon) of the 4 x 8 x 4 grid, keyed by the global agent id.  lambda is constant
+    over each block of 32 consecutive agents (a warp sweeps as long as its longest trace): block b = g // 32 runs
+    lambda[b % 8]; alpha and epsilon cycle through the agents that share a lambda.  Every cell gets the same number
+    of agents.  The same rule as experiment/online_learning's sweep_* parameters (grl_b200/host/grl_experiment.cpp)."""
     import numpy as np
     gid = np.arange(first_id, first_id + n)
-    cell = gid % (len(SWEEP_ALPHA) * len(SWEEP_LAMBDA) * len(SWEEP_EPSILON))
-    a = np.array(SWEEP_ALPHA)[cell % len(SWEEP_ALPHA)]
-    l = np.array(SWEEP_LAMBDA)[(cell // len(SWEEP_ALPHA)) % len(SWEEP_LAMBDA)]
-    e = np.array(SWEEP_EPSILON)[cell // (len(SWEEP_ALPHA) * len(SWEEP_LAMBDA))]
+    na, nl = len(SWEEP_ALPHA), len(SWEEP_LAMBDA)
+    blk, r = gid // 32, gid % 32
+    k = (blk // nl) * 32 + r
+    a = np.array(SWEEP_ALPHA)[k % na]
+    l = np.array(SWEEP_LAMBDA)[blk % nl]
+    e = np.array(SWEEP_EPSILON)[(k // na) % len(SWEEP_EPSILON)]
     return a, l, e
 
 

@@ -34,8 +34,11 @@ void OnlineLearningExperiment::request(ConfigurationRequest *config)
   config->push_back(CRP("steps_per_launch", "Agent-steps per agent between two reports", steps_per_launch_, CRP::Configuration, 1));
   config->push_back(CRP("device", "CUDA device ordinal", device_, CRP::Configuration, 0));
   // Hyper-parameter grid on the agents axis: what MultiExperiment `instances` (experiments/multi.cpp:38-60) and a
-  // grlo `parameters` list (bin/optimize.yaml) do with one process per setting.  Agent with global id g runs grid
-  // cell g mod (|alpha| |lambda| |epsilon|), alpha fastest; the other agents of a cell are its repetitions.
+  // grlo `parameters` list (bin/optimize.yaml) do with one process per setting.  For the agent with global id g:
+  // lambda is constant over blocks of 32 consecutive agents (a warp sweeps as long as its longest trace), block
+  // b = g / 32 runs lambda[b mod |lambda|]; alpha and epsilon cycle through the agents that share a lambda
+  // (k = (b / |lambda|) * 32 + g mod 32: alpha[k mod |alpha|], epsilon[(k / |alpha|) mod |epsilon|]).  Agents with the
+  // same setting are its repetitions; cell id = alpha index + |alpha| (lambda index + |lambda| epsilon index).
   config->push_back(CRP("sweep_alpha", "Learning rates of the grid (empty: the predictor's alpha)", Vector(), CRP::Configuration));
   config->push_back(CRP("sweep_lambda", "Trace decay rates of the grid (empty: the predictor's lambda)", Vector(), CRP::Configuration));
   config->push_back(CRP("sweep_epsilon", "Exploration rates of the grid (empty: the sampler's epsilon)", Vector(), CRP::Configuration));
@@ -206,11 +209,13 @@ std::vector<double> OnlineLearningExperiment::run()
       std::vector<double> al(n), la(n), ep(n);
       for (size_t a = 0; a < n; ++a)
       {
-        const size_t cell = (size_t)((unsigned long long)path_.first_agent_id + a) % cells;
-        cell_of[a] = cell;
-        al[a] = sweep_alpha_.empty() ? path_.cfg.alpha : sweep_alpha_[cell % na];
-        la[a] = sweep_lambda_.empty() ? path_.cfg.lambda : sweep_lambda_[(cell / na) % nl];
-        ep[a] = sweep_epsilon_.empty() ? path_.cfg.epsilon : sweep_epsilon_[cell / (na * nl)];
+        const unsigned long long g = (unsigned long long)path_.first_agent_id + a;
+        const unsigned long long blk = g / 32, k = (blk / nl) * 32 + g % 32;
+        const size_t ia = (size_t)(k % na), il = (size_t)(blk % nl), ie = (size_t)((k / na) % ne);
+        cell_of[a] = ia + na * (il + nl * ie);
+        al[a] = sweep_alpha_.empty() ? path_.cfg.alpha : sweep_alpha_[ia];
+        la[a] = sweep_lambda_.empty() ? path_.cfg.lambda : sweep_lambda_[il];
+        ep[a] = sweep_epsilon_.empty() ? path_.cfg.epsilon : sweep_epsilon_[ie];
       }
       CudaPath::check(grlcu_set_hyper(ctx, al.data(), la.data(), ep.data()));
     }
