@@ -1,20 +1,21 @@
 #!/bin/bash
-# evidence pass for the compacted kernels (v7): parity, bench lines of every workload, reference arm,
+# evidence pass for the compacted kernels ($TAG): parity, bench lines of every workload, reference arm,
+TAG=${TAG:-v8}
 # ncu launch list of the default bench command and one --set full capture of the run kernel per workload
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu_v7.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu_v7.log
-tail -2 gpurun_out/pytest_gpu_v7.log
-python bench.py > gpurun_out/bench_v7.json 2> gpurun_out/bench_v7.err; echo "bench exit $?"
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_v7.json 2> gpurun_out/bench_ref_v7.err; echo "ref exit $?"
+python -m pytest tests -m gpu -q -rs > gpurun_out/pytest_gpu_${TAG}.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu_${TAG}.log
+tail -2 gpurun_out/pytest_gpu_${TAG}.log
+python bench.py > gpurun_out/bench_${TAG}.json 2> gpurun_out/bench_${TAG}.err; echo "bench exit $?"
+python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_${TAG}.json 2> gpurun_out/bench_ref_${TAG}.err; echo "ref exit $?"
 for w in cart_pole cart_double_pole_ac sweep; do
-  python bench.py --workload $w --no-cpu > gpurun_out/bench_${w}_v7.json 2> gpurun_out/bench_${w}_v7.err; echo "$w exit $?"
+  python bench.py --workload $w --no-cpu > gpurun_out/bench_${w}_${TAG}.json 2> gpurun_out/bench_${w}_${TAG}.err; echo "$w exit $?"
 done
 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_v7.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_${TAG}.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launches.log 2>&1
 for w in pendulum cart_pole cart_double_pole_ac; do
   python bench.py --workload $w --steps 2 --warmup 3 --no-cpu > gpurun_out/plain_$w.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k regex:k_run -s 3 -c 1 -o gpurun_out/prof_v7_$w \
+  ncu --set full --clock-control none --import-source on -k regex:k_run -s 3 -c 1 -o gpurun_out/prof_${TAG}_$w \
       python bench.py --workload $w --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full_$w.log 2>&1
 done
 ls -la gpurun_out
