@@ -136,8 +136,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
                 e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
   if (device < 0 || device >= ndev) return fail(GRLCU_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
   CU(cudaSetDevice(device));
-  // hashed 8-byte gathers use one 32-byte sector per access: ask L2 not to fetch the neighbour sector
-  cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, getenv("GRLCU_L2_FETCH") ? (size_t)atoi(getenv("GRLCU_L2_FETCH")) : 32);
+  // (cudaLimitMaxL2FetchGranularity was measured to change nothing for the hashed gathers and is left alone: a
+  // library has no business changing device-wide limits; ld_tbl() asks for 64-byte fetches per instruction instead)
 
   grlcu_ctx *c = new (std::nothrow) grlcu_ctx();
   if (!c) return fail(GRLCU_ERR_NOMEM, "out of host memory");
