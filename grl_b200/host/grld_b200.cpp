@@ -27,25 +27,64 @@ static void print_config_json(const grlcu_config &c, int agents)
          vec(c.actor_wrapping, c.algo == GRLCU_ALGO_AC ? c.obs_dims : 0).c_str(), c.target_epsilon);
 }
 
+// -i: drive the one-agent role interfaces of the CUDA objects (Environment::start/step, Projector::project,
+// Representation::read/write/update: the signatures of environment.h:48-54, projector.h:52-69,
+// representation.h:51-92) the way a GRL agent would, and print what they returned as one JSON line.
+static void print_vec(const char *name, const Vector &v, bool last = false)
+{
+  printf("\"%s\": [", name);
+  for (size_t i = 0; i < v.size(); ++i) printf("%s%.17g", i ? ", " : "", v[i]);
+  printf("]%s", last ? "" : ", ");
+}
+
+static int exercise_interfaces(Configurator &configurator, OnlineLearningExperiment *experiment)
+{
+  experiment->resolved();                                     // attaches the objects to the experiment's device context
+  Environment *env = dynamic_cast<Environment *>(configurator.object("experiment/environment"));
+  Projector *proj = dynamic_cast<Projector *>(configurator.object("experiment/agent/policy/projector"));
+  Representation *rep = dynamic_cast<Representation *>(configurator.object("experiment/agent/policy/representation"));
+  if (!env || !proj || !rep) { ERROR("-i needs experiment/environment and experiment/agent/policy/{projector,representation}"); return 1; }
+  const grlcu_config &cfg = experiment->resolved();
+  Observation obs, obs2;
+  env->start(0, &obs);
+  Vector in = obs;
+  if (cfg.algo != GRLCU_ALGO_AC) in.push_back(cfg.actions[cfg.n_actions - 1]);   // extend(obs, action) (q.cpp:94-107)
+  ProjectionPtr p = proj->project(in);
+  Vector idx(p->indices.begin(), p->indices.end());
+  Vector q0, q1, q2;
+  rep->read(p, &q0);
+  rep->write(p, Vector{q0[0] + 1.}, Vector{0.5});             // linear.cpp:186-196: every weight += 0.5 * 1
+  rep->read(p, &q1);
+  rep->update(p, Vector{-0.25});
+  rep->read(p, &q2);
+  double reward = 0; int terminal = 0;
+  const double tau = env->step(Vector{cfg.algo == GRLCU_ALGO_AC ? 1.5 : cfg.actions[cfg.n_actions - 1]}, &obs2, &reward, &terminal);
+  printf("{");
+  print_vec("obs", obs); print_vec("index", idx); print_vec("q", Vector{q0[0], q1[0], q2[0]}); print_vec("next_obs", obs2);
+  printf("\"reward\": %.17g, \"terminal\": %d, \"tau\": %.17g}\n", reward, terminal, tau);
+  return 0;
+}
+
 int main(int argc, char **argv)
 {
   unsigned long long seed = 1;
-  bool check = false;
+  bool check = false, interfaces = false;
   int c;
-  while ((c = getopt(argc, argv, "vcs:")) != -1)
+  while ((c = getopt(argc, argv, "vcis:")) != -1)
     switch (c)
     {
       case 'v': grl_log_verbosity__++; break;
       case 'c': check = true; break;
+      case 'i': interfaces = true; break;
       case 's': seed = strtoull(optarg, nullptr, 10); break;
       default: return 1;
     }
   if (optind > argc - 1)
   {
-    ERROR("Usage: " << std::endl << "  " << argv[0] << " [-v] [-c] [-s seed] <yaml file>");
+    ERROR("Usage: " << std::endl << "  " << argv[0] << " [-v] [-c] [-i] [-s seed] <yaml file>");
     return 1;
   }
-  if (check && grl_log_verbosity__ == 3) grl_log_verbosity__ = 1;     // keep stdout to the JSON line
+  if ((check || interfaces) && grl_log_verbosity__ == 3) grl_log_verbosity__ = 1;     // keep stdout to the JSON line
   try
   {
     NOTICE("Loading configuration from '" << argv[optind] << "'");
@@ -65,6 +104,7 @@ int main(int argc, char **argv)
       print_config_json(experiment->resolved(), experiment->agents());
       return 0;
     }
+    if (interfaces) return exercise_interfaces(configurator, experiment);
     NOTICE("Starting experiment");
     experiment->run();
     NOTICE("Exiting");

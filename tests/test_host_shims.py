@@ -323,3 +323,42 @@ def test_grld_sweep_matches_ctypes_harness(grld, tmp_path):
         assert abs(float(c[6]) - members.mean()) <= 1e-6 * abs(members.mean())
         tol = 1e-6 * np.abs(members).max()                      # the file holds 9 significant digits
         assert members.min() - tol <= float(c[7]) <= float(c[8]) <= float(c[9]) <= members.max() + tol
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("yaml,mk,kw", [
+    ("cfg/pendulum/sarsa_tc_cuda.yaml", "pendulum_config", dict(randomization=1.0, test_interval=-1)),
+    ("cfg/cart_pole/sarsa_tc_cuda.yaml", "cart_pole_config", dict(randomization=1.0)),
+    ("cfg/cart_double_pole/ac_tc_cuda.yaml", "cart_double_pole_ac_config", dict(test_interval=10)),
+])
+def test_role_interfaces_of_the_shims(grld, tmp_path, yaml, mk, kw):
+    """`grld_b200 -i`: Environment::start/step, Projector::project, Representation::read/write/update of the CUDA
+    objects (one-agent views, the reference's L2 signatures) against the same calls through the ctypes harness."""
+    import grl_b200
+    text = re.sub(r"agents: \d+", "agents: 4", open(os.path.join(ROOT, yaml)).read())
+    p = tmp_path / "iface.yaml"
+    p.write_text(text)
+    out = subprocess.run([grld, "-i", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    got = json.loads(out.stdout.strip().splitlines()[-1])
+    cfgj = json.loads(subprocess.run([grld, "-c", str(p)], capture_output=True, text=True).stdout)
+    cfg = getattr(grl_b200, mk)(memory=cfgj["memory"], **kw)
+    ac = cfg.algo == grl_b200.capi.ALGO_AC
+    b = grl_b200.Batch(cfg, 4)
+    try:
+        st, obs, _ = b.task_start(np.array([0.5]), test=0)
+        assert got["obs"] == list(obs[0])
+        act = 1.5 if ac else cfg.actions[cfg.n_actions - 1]
+        x = list(obs[0]) + ([] if ac else [act])
+        _, idx = b.project(np.array([x]))
+        assert got["index"] == [float(i) for i in idx[0]]
+        q0 = b.read(0, idx[0], actor=ac)
+        b.update(0, idx[0], 0.5 * ((q0 + 1.0) - q0), actor=ac)
+        q1 = b.read(0, idx[0], actor=ac)
+        b.update(0, idx[0], -0.25, actor=ac)
+        q2 = b.read(0, idx[0], actor=ac)
+        assert got["q"] == [q0, q1, q2] and q1 > q0 and q2 < q1
+        nxt, obs2, rew, term = b.model_step(st, np.array([act]))
+        assert got["next_obs"] == list(obs2[0]) and got["reward"] == rew[0] and got["terminal"] == term[0] and got["tau"] == 1.0
+    finally:
+        b.close()
