@@ -6,8 +6,10 @@
  * GRL itself has no C FFI: the path sits behind its C++ Configurable plugin API
  * (base/include/grl/configurable.h:704-826).  The callers of this ABI are the thin C++
  * Configurable shims in grl_b200/host/ (environment/model/cuda_batched,
- * projector/tile_coding/cuda, representation/linear/cuda, predictor/sarsa/cuda; see
- * INTEGRATION.md) and the Python ctypes harness used by tests/ and bench.py.
+ * projector/tile_coding/cuda, representation/linear/cuda, predictor/sarsa/cuda, and for the
+ * sibling algorithms predictor/q/cuda, predictor/expected_sarsa/cuda, predictor/ac/action/cuda,
+ * predictor/critic/td/cuda) and the Python ctypes harness used by tests/
+ * and bench.py.
  *
  * Conventions: plain pointers and sizes, caller-owned HOST buffers unless a name says
  * "_dev", int return codes (0 = ok, non-zero = error, text in grlcu_last_error()),
