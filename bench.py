@@ -304,8 +304,16 @@ def ours(args):
         # this GPU type (profiles/random_access_ceilings.json); accesses counted on the device.
         random_access = None
         try:
-            with open(os.path.join(ROOT, "profiles", "random_access_ceilings.json")) as f:
-                ceil = json.load(f)
+            # the ceilings of THIS device, measured now (grlcu_probe_random_access: independent random 8-byte reads /
+            # writes over an 8 GiB scratch buffer); the committed figures are the fallback
+            try:
+                r_s, w_s, _ = grl_b200.capi.probe_random_access(local, 1 << 33)
+                ceil = {"read_G_per_s": r_s / 1e9, "write_G_per_s": w_s / 1e9,
+                        "source": "measured on this device after the timed region (grlcu_probe_random_access, 8 GiB footprint)"}
+            except Exception:
+                with open(os.path.join(ROOT, "profiles", "random_access_ceilings.json")) as f:
+                    ceil = json.load(f)
+                ceil["source"] = "profiles/random_access_ceilings.json"
             ac = args.workload == "cart_double_pole_ac"
             cached = args.workload in ("pendulum", "cart_pole", "cart_double_pole_ac", "sweep") and os.environ.get("GRLCU_MODE", "0") == "0"
             W = writes_all / max(steps_all, 1)
@@ -316,6 +324,7 @@ def ours(args):
                              "read_ceiling_G_per_s": ceil["read_G_per_s"], "write_ceiling_G_per_s": ceil["write_G_per_s"],
                              "ns_per_agent_step_at_ceiling": floor_ns, "ns_per_agent_step": got_ns,
                              "frac": floor_ns / got_ns if got_ns > 0 else None,
+                             "ceiling_source": ceil.get("source"),
                              "note": "time the measured counts of random 8-byte table reads and writes would take at "
                                      "the measured B200 ceilings, over the kernel's measured time"}
         except Exception:

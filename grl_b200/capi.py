@@ -114,7 +114,7 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_run_host", "grlcu_replay_step", "grlcu_get_results", "grlcu_get_table",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
            "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update",
-           "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor"]
+           "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor", "grlcu_probe_random_access"]
 
 _lib = None
 
@@ -154,6 +154,7 @@ def load(build=True):
     L.grlcu_task_start.argtypes = [vp, C.c_int64, C.c_int32, _dp, _dp, _dp, _i32p]
     L.grlcu_read.argtypes = [vp, C.c_int32, C.c_int32, _u64p, _dp]
     L.grlcu_update.argtypes = [vp, C.c_int32, C.c_int32, _u64p, C.c_double]
+    L.grlcu_probe_random_access.argtypes = [C.c_int32, C.c_uint64, _dp, _dp, _dp]
     L.grlcu_read_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, _dp]
     L.grlcu_update_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, C.c_double]
     _lib = L
@@ -162,6 +163,16 @@ def load(build=True):
 
 def _ptr(a, ty):
     return None if a is None else a.ctypes.data_as(ty)
+
+
+def probe_random_access(device=0, footprint_bytes=1 << 33):
+    """(reads/s, writes/s, rmws/s) of independent random 8-byte accesses on this device (grlcu_probe_random_access)."""
+    L = load()
+    r, w, m = C.c_double(), C.c_double(), C.c_double()
+    rc = L.grlcu_probe_random_access(device, footprint_bytes, C.byref(r), C.byref(w), C.byref(m))
+    if rc != 0:
+        raise GrlcuError("grlcu error %d: %s" % (rc, L.grlcu_last_error().decode()))
+    return r.value, w.value, m.value
 
 
 class Batch:

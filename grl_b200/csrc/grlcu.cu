@@ -59,6 +59,75 @@ struct grlcu_ctx
 extern "C" const char *grlcu_last_error(void) { return g_err; }
 extern "C" int grlcu_version(void) { return 1; }
 
+// ---- random-access probe (include/grlcu.h): what this device does for the path's access pattern ---------------
+template <int MODE>   // 0 read, 1 write, 2 read-modify-write
+__global__ void k_probe(double *buf, uint64_t mask, int iters, double *sink)
+{
+  constexpr int K = 16;
+  uint64_t s = (uint64_t)(blockIdx.x * blockDim.x + threadIdx.x) * 0x9E3779B97F4A7C15ull + 12345;
+  double acc = 0;
+  for (int it = 0; it < iters; ++it)
+  {
+    uint64_t ix[K];
+    double v[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { s = s * 6364136223846793005ull + 1442695040888963407ull; ix[k] = (s >> 17) & mask; }
+    if (MODE != 1)
+    {
+#pragma unroll
+      for (int k = 0; k < K; ++k) v[k] = ld_tbl(buf + ix[k]);
+    }
+    if (MODE == 0)
+    {
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc += v[k];
+    }
+    else
+    {
+#pragma unroll
+      for (int k = 0; k < K; ++k) buf[ix[k]] = MODE == 1 ? (double)it : v[k] + 1.0;
+    }
+  }
+  if (acc == 123.456) *sink = acc;
+}
+
+extern "C" int grlcu_probe_random_access(int32_t device, uint64_t footprint_bytes, double *reads_per_s, double *writes_per_s,
+                                         double *rmws_per_s)
+{
+  if (footprint_bytes < (64ull << 20) || (footprint_bytes & (footprint_bytes - 1)))
+    return fail(GRLCU_ERR_ARG, "grlcu_probe_random_access: footprint must be a power of two >= 64 MiB");
+  CU(cudaSetDevice(device));
+  double *buf = nullptr, *sink = nullptr;
+  if (cudaMalloc(&buf, footprint_bytes) != cudaSuccess) { cudaGetLastError(); return fail(GRLCU_ERR_NOMEM, "grlcu_probe_random_access: no room for the scratch buffer"); }
+  if (cudaMalloc(&sink, 8) != cudaSuccess) { cudaFree(buf); cudaGetLastError(); return fail(GRLCU_ERR_NOMEM, "grlcu_probe_random_access: out of device memory"); }
+  cudaMemset(buf, 0, footprint_bytes);
+  const uint64_t mask = footprint_bytes / 8 - 1;
+  const int threads = 65536, iters = 64;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  double *outs[3] = {reads_per_s, writes_per_s, rmws_per_s};
+  for (int mode = 0; mode < 3; ++mode)
+  {
+    if (!outs[mode]) continue;
+    for (int rep = 0; rep < 2; ++rep)      // first pass warms up
+    {
+      cudaEventRecord(e0);
+      if (mode == 0) k_probe<0><<<threads / 64, 64>>>(buf, mask, rep ? iters : 2, sink);
+      else if (mode == 1) k_probe<1><<<threads / 64, 64>>>(buf, mask, rep ? iters : 2, sink);
+      else k_probe<2><<<threads / 64, 64>>>(buf, mask, rep ? iters : 2, sink);
+      cudaEventRecord(e1);
+      cudaEventSynchronize(e1);
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    *outs[mode] = ms > 0 ? (double)threads * iters * 16 / (ms * 1e-3) : 0.;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(buf); cudaFree(sink);
+  CU(cudaGetLastError());
+  return 0;
+}
+
 template <typename Tp>
 static int dalloc(grlcu_ctx *c, Tp **ptr, size_t count)
 {

@@ -129,6 +129,14 @@ typedef struct grlcu_results
 const char *grlcu_last_error(void);
 int grlcu_version(void);
 
+/* Measurement aid (replaces nothing in the reference): the rates, in accesses per second, at which THIS device
+ * serves independent random 8-byte reads (ld.global.L2::64B, what the table gathers use), writes and
+ * read-modify-writes over a scratch buffer of `footprint_bytes` (a power of two >= 64 MiB, well beyond L2).
+ * Every table access of the path is such an access, so these are the denominators of bench.py's
+ * `roofline.random_access`.  Any output pointer may be NULL.  Takes ~50 ms. */
+int grlcu_probe_random_access(int32_t device, uint64_t footprint_bytes, double *reads_per_s, double *writes_per_s,
+                              double *rmws_per_s);
+
 /* Creates the device-resident state of n_agents agents with global ids
  * [first_agent_id, first_agent_id + n_agents) on CUDA device `device`, launching on
  * `stream` (a cudaStream_t, NULL = default stream).  Tables are initialised like

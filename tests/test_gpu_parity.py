@@ -276,3 +276,11 @@ def test_one_agent_views(G, orc):
                 b.read(1, np.array([4096], np.uint64))
         finally:
             b.close()
+
+
+def test_random_access_probe(G):
+    """grlcu_probe_random_access: the live denominators of bench.py's random-access roofline."""
+    r, w, m = G.capi.probe_random_access(0, 1 << 31)
+    assert 1e10 < m < w < r < 1e12            # B200: about 37 G reads/s, 20 G writes/s, 13.5 G read-modify-writes/s
+    with pytest.raises(G.GrlcuError):
+        G.capi.probe_random_access(0, 3 << 20)
