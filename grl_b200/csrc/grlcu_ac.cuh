@@ -64,26 +64,36 @@ __device__ __forceinline__ void ac_update(const Params &p, const ACParams &ac, A
 #pragma unroll
   for (int j = 0; j < T; ++j) u += ua[j];
   u = clampd(u / T, ac.action_min, ac.action_max);
-  // critique = critic_->criticize(transition, u)
-  if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, critic, reward, bootstrap, vnext, vp, qp, target, delta, swept);
-  else sarsa_update<DYN, T>(p, ag, critic, a, reward, bootstrap, vnext, vp, qp, target, delta, swept);
-  // delta = critique * (prev_action - u); target_u = u + delta; representation_->write(ap, target_u, alpha)
-  const double du = delta * (ag.action - u);
-  const double target_u = u + du;
-  const double dw = ac.actor_alpha * (target_u - u);      // write() reads the same, unchanged, actor value again
-  if (!(ag.flags & 8))
+  // delta = critique * (prev_action - u); target_u = u + delta; representation_->write(ap, target_u, alpha):
+  // the reference does this after critic_->criticize() returns; the actor table is not touched by the critic, so
+  // the stores are issued as soon as the critique is known (cached path: before the critic's trace sweep, while the
+  // sectors fetched with ua are still in L2)
+  auto actor_write = [&](double critique)
   {
+    const double du = critique * (ag.action - u);
+    const double target_u = u + du;
+    const double dw = ac.actor_alpha * (target_u - u);    // write() reads the same, unchanged, actor value again
+    if (!(ag.flags & 8))
+    {
 #pragma unroll
-    for (int j = 0; j < T; ++j) actor[ag.pidx[j]] = clampd(ua[j] + dw, ac.action_min, ac.action_max);
-  }
+      for (int j = 0; j < T; ++j) actor[ag.pidx[j]] = clampd(ua[j] + dw, ac.action_min, ac.action_max);
+    }
+    else
+    {
+      uint32_t lp[T];
+#pragma unroll
+      for (int j = 0; j < T; ++j) lp[j] = ag.pidx[j];
+#pragma unroll 1
+      for (int j = 0; j < T; ++j)                          // duplicate indices: sequential, clamped each time
+        actor[lp[j]] = clampd(ld_tbl(actor + lp[j]) + dw, ac.action_min, ac.action_max);
+    }
+  };
+  // critique = critic_->criticize(transition, u)
+  if (CACHED) sarsa_update_cached<DYN, T>(p, ag, c, critic, reward, bootstrap, vnext, vp, qp, target, delta, swept, actor_write);
   else
   {
-    uint32_t lp[T];
-#pragma unroll
-    for (int j = 0; j < T; ++j) lp[j] = ag.pidx[j];
-#pragma unroll 1
-    for (int j = 0; j < T; ++j)                            // duplicate indices: sequential, clamped each time
-      actor[lp[j]] = clampd(ld_tbl(actor + lp[j]) + dw, ac.action_min, ac.action_max);
+    sarsa_update<DYN, T>(p, ag, critic, a, reward, bootstrap, vnext, vp, qp, target, delta, swept);
+    actor_write(delta);
   }
   ag.dtblw += (uint32_t)T;                                  // actor stores (the critic's are counted by sarsa_update)
   u_out = u;

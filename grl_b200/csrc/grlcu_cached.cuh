@@ -180,11 +180,16 @@ __device__ __forceinline__ void cache_clear(const Params &p, Agent<DYN, T> &ag, 
 
 // SARSAPredictor::criticize (sarsa.cpp:98-124), replacing trace, through the value cache.
 //   rawp[j]: table[pidx[j]] as read before any store of this step (value or sentinel).
-template <int DYN, int T>
+struct NoEarlyStores { __device__ __forceinline__ void operator()(double) const { } };
+
+//   early(delta): called as soon as the TD error is known, before the sweep: lets a caller issue its own stores to
+//   table words it fetched together with rawp while they are still in L2 (the actor update of the actor-critic).
+template <int DYN, int T, typename Early = NoEarlyStores>
 __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                                     double reward, bool bootstrap, double q_next,
                                                     const double (&rawp)[T],
-                                                    double &o_qp, double &o_target, double &o_delta, int &o_swept)
+                                                    double &o_qp, double &o_target, double &o_delta, int &o_swept,
+                                                    Early early = Early())
 {
   const int cap = p.trace_cap;
   double target = reward;
@@ -228,6 +233,16 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
     for (int j = 0; j < T; ++j)
       for (int r = (int)((dups >> (4 * j)) & 15u); r > 0; --r) np[j] += dw;
   }
+  // The directory sentinels of p's new slots (ring position head + 1, where trace.add puts p below) are stored NOW,
+  // while the sectors that Q(p)'s gather fetched a moment ago are still in L2: after the sweep they are gone (an L2
+  // line lives ~40 us, a step of all agents takes ~200 us) and each store would pay a 32-byte fill from DRAM.
+  // Nothing between here and the push reads these table words: the update works on rawp / sp / the dense cache, and
+  // the flushes below only write indices that ssub has not invalidated, i.e. never one of p's.
+  early(delta);
+  const int nhead = ag.head + 1 == cap ? 0 : ag.head + 1;
+#pragma unroll
+  for (int j = 0; j < T; ++j)
+    if ((owner >> j) & 1u) tbl[ag.pidx[j]] = make_sentinel(nhead * T + j);
   // indices that an older entry holds: that slot receives p's write now and the sweep's increment below
 #pragma unroll
   for (int j = 0; j < T; ++j)
@@ -285,11 +300,7 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
     for (int j = 0; j < T; ++j)
     {
       const uint32_t x = ag.pidx[j];
-      if ((owner >> j) & 1u)
-      {
-        c.val(pos * T + j) = np[j];
-        tbl[x] = make_sentinel(pos * T + j);
-      }
+      if ((owner >> j) & 1u) c.val(pos * T + j) = np[j];      // (its sentinel went out before the sweep)
       c.idx(pos, j) = x;
     }
     if (pdup)

@@ -3,7 +3,9 @@
 rev=${1:-HEAD}
 d=$(mktemp -d)
 mkdir -p $d/grl_b200/csrc $d/include
-for f in grlcu.cu grlcu_device.cuh grlcu_agent.cuh grlcu_cached.cuh grlcu_kernels.cuh grlcu_ac.cuh; do git show $rev:grl_b200/csrc/$f > $d/grl_b200/csrc/$f; done
+for f in $(git ls-tree --name-only $rev grl_b200/csrc/ | grep -E "\.(cu|cuh)$"); do git show $rev:$f > $d/$f; done
 git show $rev:include/grlcu.h > $d/include/grlcu.h
 (cd $d/grl_b200/csrc && nvcc -gencode arch=compute_100a,code=sm_100a -O3 -fmad=false -lineinfo -std=c++17 -Xcompiler -fPIC -shared -o "$OLDPWD/tools/prev.bin" grlcu.cu)
+rc=$?
 rm -rf $d
+exit $rc
