@@ -39,9 +39,14 @@ WORKLOADS = {
                   "cart-pole swing-up SARSA(lambda) tile coding (cfg/cart_pole/sarsa.yaml), 4-D state, 3 actions"),
     "cart_double_pole_ac": ("cart_double_pole_ac_config", 65536, 131072,
                             "cart-double-pole actor-critic, two tile-coded tables per agent (cfg/cart_double_pole/ac.yaml)"),
+    "pendulum_ac": ("pendulum_ac_config", 65536, 65536,
+                    "pendulum swing-up actor-critic, two tile-coded tables per agent (cfg/pendulum/ac_tc.yaml)"),
+    "cart_pole_ac": ("cart_pole_ac_config", 32768, 262144,
+                     "cart-pole swing-up actor-critic, two tile-coded tables per agent (cfg/cart_pole/ac_tc.yaml)"),
     "sweep": ("pendulum_config", 131072, 32768,
               "pendulum SARSA-TC alpha x lambda x epsilon sweep (4 x 8 x 4 grid), per-agent hyper-parameters"),
 }
+AC_WORKLOADS = ("cart_double_pole_ac", "pendulum_ac", "cart_pole_ac")
 SWEEP_ALPHA = [0.05, 0.1, 0.2, 0.4]
 SWEEP_LAMBDA = [0.0, 0.2, 0.4, 0.5, 0.65, 0.75, 0.85, 0.9]
 SWEEP_EPSILON = [0.01, 0.02, 0.05, 0.1]
@@ -51,7 +56,7 @@ def make_config(mod, args):
     """The workload's config from `mod` (grl_b200 or the oracle harness: same maker names, same fields)."""
     maker = WORKLOADS[args.workload][0]
     kw = dict(memory=args.memory, test_interval=-1)
-    if args.workload != "cart_double_pole_ac":
+    if args.workload != "cart_double_pole_ac":       # (task/cart_double_pole/balancing has no randomization parameter)
         kw["randomization"] = 1.0
     if args.workload == "sweep":
         kw["lambda_"] = max(SWEEP_LAMBDA)          # trace ring sized for the largest lambda of the grid
@@ -77,7 +82,7 @@ def sweep_hyper(first_id, n):
 def table_bytes_per_step(workload, V):
     """algorithmic table bytes per agent-step (8-byte entries, each touched entry once per read and
     once per write): SARSA 8*A*T + 8*T + 8*T + 16*V = 640 + 16 V; AC 8*T + 16*T + 2*8*T + 8*T + 16*V = 768 + 16 V."""
-    return (768 if workload == "cart_double_pole_ac" else 640) + 16 * V
+    return (768 if workload in AC_WORKLOADS else 640) + 16 * V
 
 
 def peaks():
@@ -152,7 +157,7 @@ def reference_arm(args):
 
 
 def workload_config(args, n_gpus):
-    tables = 2 if args.workload == "cart_double_pole_ac" else 1
+    tables = 2 if args.workload in AC_WORKLOADS else 1
     cfg = {"workload": "%s, %d independent agents per GPU" % (WORKLOADS[args.workload][3], args.agents),
            "name": args.workload, "agents_per_gpu": args.agents, "agents_total": args.agents * n_gpus,
            "memory_per_agent": args.memory, "tables_per_agent": tables,
@@ -314,8 +319,8 @@ def ours(args):
                 with open(os.path.join(ROOT, "profiles", "random_access_ceilings.json")) as f:
                     ceil = json.load(f)
                 ceil["source"] = "profiles/random_access_ceilings.json"
-            ac = args.workload == "cart_double_pole_ac"
-            cached = args.workload in ("pendulum", "cart_pole", "cart_double_pole_ac", "sweep") and os.environ.get("GRLCU_MODE", "0") == "0"
+            ac = args.workload in AC_WORKLOADS
+            cached = os.environ.get("GRLCU_MODE", "0") == "0"
             W = writes_all / max(steps_all, 1)
             R = (4 * 16 if ac else 3 * 16 + 16) + (0 if cached else V)      # cached path: the sweep runs on the dense cache
             floor_ns = R / ceil["read_G_per_s"] + W / ceil["write_G_per_s"]
@@ -343,7 +348,7 @@ def ours(args):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src, "random_access": random_access,
                          "bytes_per_agent_step": B, "V_mean": V,
-                         "kernel": "grlcu::k_run_ac" if args.workload == "cart_double_pole_ac" else "grlcu::k_run",
+                         "kernel": "grlcu::k_run_ac" if args.workload in AC_WORKLOADS else "grlcu::k_run",
                          "kernel_ms_per_launch": kern_ms / max(kern_launches, 1),
                          "kernel_launches": int(kern_launches)},
             "mean_last_return": mean_return,

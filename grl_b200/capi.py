@@ -35,7 +35,13 @@ class Config(C.Structure):
         ("action_min", C.c_double), ("action_max", C.c_double),
         ("actor_resolution", C.c_double * MAX_DIMS), ("actor_wrapping", C.c_double * MAX_DIMS),
         ("target_epsilon", C.c_double),
+        ("end_stop_penalty", C.c_int32), ("reserved_", C.c_int32),
     ]
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        if "end_stop_penalty" not in kw:
+            self.end_stop_penalty = 1     # the reference's default (cart_pole.h:75)
 
 
 def _fill(c, **kw):
@@ -81,6 +87,33 @@ def cart_double_pole_ac_config(memory=131072, **kw):
           alpha=0.2, gamma=0.97, lambda_=0.65, epsilon=0.0, trace=TRACE_REPLACING, test_interval=10,
           init_min=0.0, init_max=1.0, seed=1, algo=ALGO_AC,
           sigma=5.0, actor_alpha=0.01, action_min=-20.0, action_max=20.0)
+    return _fill(c, **kw)
+
+
+def pendulum_ac_config(memory=65536, **kw):
+    """cfg/pendulum/ac_tc.yaml of the reference (actor-critic on the pendulum swing-up, sigma = 1, action +-3)."""
+    c = Config()
+    res, wrap = [0.31415, 3.1415], [6.283, 0]
+    _fill(c, dynamics=DYN_PENDULUM, integration_steps=5, control_step=0.03, timeout=2.99, randomization=0.0,
+          tilings=16, memory=memory, obs_dims=2, n_actions=0, resolution=res, wrapping=wrap,
+          actor_resolution=res, actor_wrapping=wrap,
+          alpha=0.2, gamma=0.97, lambda_=0.65, epsilon=0.0, trace=TRACE_REPLACING, test_interval=10,
+          init_min=0.0, init_max=1.0, seed=1, algo=ALGO_AC,
+          sigma=1.0, actor_alpha=0.01, action_min=-3.0, action_max=3.0)
+    return _fill(c, **kw)
+
+
+def cart_pole_ac_config(memory=262144, **kw):
+    """cfg/cart_pole/ac_tc.yaml of the reference (actor-critic on the cart-pole swing-up: sigma = 5, action +-15,
+    end_stop_penalty 0: the cart rides the end stop instead of ending the episode)."""
+    c = Config()
+    res, wrap = [2.5, 0.157075, 2.5, 1.57075], [0, 6.283, 0, 0]
+    _fill(c, dynamics=DYN_CART_POLE, integration_steps=5, control_step=0.05, timeout=9.99, randomization=0.0,
+          tilings=16, memory=memory, obs_dims=4, n_actions=0, resolution=res, wrapping=wrap,
+          actor_resolution=res, actor_wrapping=wrap,
+          alpha=0.2, gamma=0.97, lambda_=0.65, epsilon=0.0, trace=TRACE_REPLACING, test_interval=10,
+          init_min=0.0, init_max=1.0, seed=1, algo=ALGO_AC,
+          sigma=5.0, actor_alpha=0.01, action_min=-15.0, action_max=15.0, end_stop_penalty=0)
     return _fill(c, **kw)
 
 

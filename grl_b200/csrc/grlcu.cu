@@ -153,11 +153,14 @@ static int supported(const grlcu_config *cfg)
   if (cfg->tilings != 16) return fail(GRLCU_ERR_UNSUPPORTED, "tilings %d: kernels are instantiated for 16", cfg->tilings);
   if (cfg->memory < 1) return fail(GRLCU_ERR_ARG, "memory must be positive");
   if (cfg->integration_steps < 1) return fail(GRLCU_ERR_ARG, "integration_steps must be >= 1");
+  if (cfg->end_stop_penalty != 0 && cfg->end_stop_penalty != 1) return fail(GRLCU_ERR_ARG, "end_stop_penalty must be 0 or 1");
   if (cfg->algo == GRLCU_ALGO_AC)
   {
-    if (cfg->dynamics != GRLCU_DYN_CART_DOUBLE_POLE)
-      return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for actor-critic (cart_double_pole only)", cfg->dynamics);
-    if (cfg->obs_dims != 6) return fail(GRLCU_ERR_ARG, "obs_dims %d does not match dynamics (6)", cfg->obs_dims);
+    // cfg/cart_double_pole/ac.yaml, cfg/pendulum/ac_tc.yaml, cfg/cart_pole/ac_tc.yaml of the reference
+    if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE && cfg->dynamics != GRLCU_DYN_CART_DOUBLE_POLE)
+      return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for actor-critic", cfg->dynamics);
+    const int aobs = cfg->dynamics == GRLCU_DYN_PENDULUM ? 2 : cfg->dynamics == GRLCU_DYN_CART_POLE ? 4 : 6;
+    if (cfg->obs_dims != aobs) return fail(GRLCU_ERR_ARG, "obs_dims %d does not match dynamics (%d)", cfg->obs_dims, aobs);
     for (int i = 0; i < cfg->obs_dims; ++i)
       if (cfg->actor_resolution[i] != cfg->resolution[i] || cfg->actor_wrapping[i] != cfg->wrapping[i])
         return fail(GRLCU_ERR_UNSUPPORTED, "actor and critic projectors must have the same resolution and wrapping "
@@ -232,7 +235,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   memset(&p, 0, sizeof(p));
   p.n = n_agents; p.first_id = first_agent_id; p.seed = cfg->seed;
   p.tau = cfg->control_step; p.isteps = cfg->integration_steps;
-  p.timeout = cfg->timeout; p.randomization = cfg->randomization;
+  p.timeout = cfg->timeout; p.randomization = cfg->randomization; p.end_stop_penalty = cfg->end_stop_penalty;
   // TileCodingProjector::configure (tile_coding.cpp:66-79)
   const bool is_ac = cfg->algo == GRLCU_ALGO_AC;
   const int dims = is_ac ? cfg->obs_dims : cfg->obs_dims + 1;   // AC projects observations, SARSA (obs, action)
@@ -488,8 +491,10 @@ extern "C" int grlcu_project(grlcu_ctx *c, int64_t n, const double *in, uint32_t
   CU(cudaMemcpyAsync(d_in, in, sizeof(double) * n * dims, cudaMemcpyHostToDevice, c->stream));
   const int grd = grid_for(n, 128);
 #define CALL(D) k_project<Dyn<D>::OBS + 1, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i)
-  if (is_ac) k_project<6, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i);
+#define CALL_AC(D) k_project<Dyn<D>::OBS, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i)
+  if (is_ac) DISPATCH_DYN(c, CALL_AC);
   else DISPATCH_SARSA(c, CALL);
+#undef CALL_AC
 #undef CALL
   c->launches++;
   CU(cudaGetLastError());
@@ -515,7 +520,7 @@ extern "C" int grlcu_model_step(grlcu_ctx *c, int64_t n, const double *state, co
   CU(cudaMemcpyAsync(d_s, state, sizeof(double) * n * S, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemcpyAsync(d_a, action, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
   const int grd = grid_for(n, 128);
-#define CALL(D) k_model_step<D><<<grd, 128, 0, c->stream>>>(n, c->p.tau, c->p.isteps, c->p.timeout, d_s, d_a, d_n, d_o, d_r, d_t)
+#define CALL(D) k_model_step<D><<<grd, 128, 0, c->stream>>>(n, c->p.tau, c->p.isteps, c->p.timeout, c->p.end_stop_penalty, d_s, d_a, d_n, d_o, d_r, d_t)
   DISPATCH_DYN(c, CALL);
 #undef CALL
   c->launches++;
@@ -530,7 +535,7 @@ extern "C" int grlcu_model_step(grlcu_ctx *c, int64_t n, const double *state, co
 
 // ---- one-agent views (L2-signature shims) --------------------------------------------------------
 template <int DYN>
-__global__ void k_task_start(int64_t n, int test, double randomization, double timeout, const double *u,
+__global__ void k_task_start(int64_t n, int test, double randomization, double timeout, int end_stop_penalty, const double *u,
                              double *state, double *obs, int32_t *terminal)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
@@ -539,7 +544,7 @@ __global__ void k_task_start(int64_t n, int test, double randomization, double t
     double x[S], o[OBS];
     int term;
     task_start<DYN>(u[t], randomization, test, x);
-    observe<DYN>(x, timeout, o, term);
+    observe<DYN>(x, timeout, o, term, end_stop_penalty);
 #pragma unroll
     for (int i = 0; i < S; ++i) state[t * S + i] = x[i];
 #pragma unroll
@@ -561,7 +566,7 @@ extern "C" int grlcu_task_start(grlcu_ctx *c, int64_t n, int32_t test, const dou
   if (!d_u || !d_s || !d_o || !d_t) return fail(GRLCU_ERR_NOMEM, "grlcu_task_start: out of device memory");
   CU(cudaMemcpyAsync(d_u, u, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
   const int grd = grid_for(n, 128);
-#define CALL(D) k_task_start<D><<<grd, 128, 0, c->stream>>>(n, test, c->p.randomization, c->p.timeout, d_u, d_s, d_o, d_t)
+#define CALL(D) k_task_start<D><<<grd, 128, 0, c->stream>>>(n, test, c->p.randomization, c->p.timeout, c->p.end_stop_penalty, d_u, d_s, d_o, d_t)
   DISPATCH_DYN(c, CALL);
 #undef CALL
   c->launches++;
@@ -723,14 +728,16 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
       else if (roomy) k_run<D, 16, 3, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0); \
       else k_run<D, 16, 3, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0);      \
     } while (0)
-    if (c->cfg.algo == GRLCU_ALGO_AC)
-    {
-      if (cached && roomy) k_run_ac<2, 16, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1);
-      else if (cached) k_run_ac<2, 16, true, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1);
-      else if (roomy) k_run_ac<2, 16, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0);
-      else k_run_ac<2, 16, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0);
-    }
+#define CALL_AC(D)                                                                                 \
+    do {                                                                                           \
+      if (cached && roomy) k_run_ac<D, 16, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
+      else if (cached) k_run_ac<D, 16, true, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
+      else if (roomy) k_run_ac<D, 16, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0); \
+      else k_run_ac<D, 16, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0);      \
+    } while (0)
+    if (c->cfg.algo == GRLCU_ALGO_AC) DISPATCH_DYN(c, CALL_AC);
     else DISPATCH_SARSA(c, CALL);
+#undef CALL_AC
 #undef CALL
     if (cached && lazy && begin + cohort >= n) c->cache_live = true;
     CU(cudaEventRecord(e1, c->stream));
@@ -944,8 +951,10 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
   if (oom) return fail(GRLCU_ERR_NOMEM, "grlcu_replay_step: device scratch allocation/copy failed");
   const int blk = 64, grd = ((int)n + blk - 1) / blk;
 #define CALL(D) k_replay<D, 16, 3><<<grd, blk, 0, c->stream>>>(c->p, io)
-  if (is_ac) k_replay_ac<2, 16><<<grd, blk, 0, c->stream>>>(c->p, c->ac, io);
+#define CALL_AC(D) k_replay_ac<D, 16><<<grd, blk, 0, c->stream>>>(c->p, c->ac, io)
+  if (is_ac) DISPATCH_DYN(c, CALL_AC);
   else DISPATCH_SARSA(c, CALL);
+#undef CALL_AC
 #undef CALL
   c->launches++;
   CU(cudaGetLastError());

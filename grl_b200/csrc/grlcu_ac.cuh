@@ -213,7 +213,7 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
         task_start<DYN>(u53(w.w[0], w.w[1]), p.randomization, test ? 1 : 0, ag.x);
       }
       int term0;
-      observe<DYN>(ag.x, p.timeout, obs, term0);
+      observe<DYN>(ag.x, p.timeout, obs, term0, p.end_stop_penalty);
       if (!test)
       {
         // TDAgent::start -> finalize -> trace clear
@@ -230,8 +230,8 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
 #pragma unroll
       for (int i = 0; i < S; ++i) next[i] = ag.x[i];
       rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(ag.action), next);
-      observe<DYN>(next, p.timeout, obs, terminal);
-      reward = evaluate<DYN>(ag.x, ag.action, next);
+      observe<DYN>(next, p.timeout, obs, terminal, p.end_stop_penalty);
+      reward = evaluate<DYN>(ag.x, ag.action, next, p.end_stop_penalty);
       ag.total_reward += reward;
 #pragma unroll
       for (int i = 0; i < S; ++i) ag.x[i] = next[i];
@@ -279,7 +279,7 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
     for (int i = 0; i < S; ++i) ag.x[i] = io.start_state[(size_t)i * n + a];
     double obs0[OBS];
     int term0;
-    observe<DYN>(ag.x, p.timeout, obs0, term0);
+    observe<DYN>(ag.x, p.timeout, obs0, term0, p.end_stop_penalty);
     if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
     ag.total_reward = 0;
     ag.flags = 1 | (test ? 2 : 0);
@@ -295,8 +295,8 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
   for (int i = 0; i < S; ++i) x0[i] = next[i] = io.state[(size_t)i * n + a];
   const double act = io.action[a];
   rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(act), next);
-  observe<DYN>(next, p.timeout, obs, terminal);
-  const double r_own = evaluate<DYN>(x0, act, next);
+  observe<DYN>(next, p.timeout, obs, terminal, p.end_stop_penalty);
+  const double r_own = evaluate<DYN>(x0, act, next, p.end_stop_penalty);
   if (io.o_next) for (int i = 0; i < S; ++i) io.o_next[(size_t)i * n + a] = next[i];
   if (io.o_obs) for (int i = 0; i < OBS; ++i) io.o_obs[(size_t)i * n + a] = obs[i];
   if (io.o_reward) io.o_reward[a] = r_own;

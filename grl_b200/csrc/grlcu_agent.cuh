@@ -22,6 +22,7 @@ struct Params
   int64_t  first_id;          // global id of agent 0 (Philox stream)
   uint64_t seed;
   double   tau; int32_t isteps; double timeout, randomization;
+  int32_t  end_stop_penalty;  // task/cart_pole/swingup end_stop_penalty (cart_pole.cpp:177,196)
   Projector proj;
   uint32_t kact[8][16];      // pre-mixed MurmurHash2 word of the action coordinate, per (action, tiling)
   uint32_t kj[16];           // pre-mixed word of the tiling number

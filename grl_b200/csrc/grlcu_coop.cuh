@@ -339,7 +339,7 @@ k_run_coop(Params p, CoopArrays ca, int agent_begin, int agent_end, int64_t n_st
         task_start<DYN>(u53(w.w[0], w.w[1]), p.randomization, test ? 1 : 0, ag.x);
       }
       int term0;
-      observe<DYN>(ag.x, p.timeout, obs, term0);
+      observe<DYN>(ag.x, p.timeout, obs, term0, p.end_stop_penalty);
       if (!test) coop_clear<DYN, L>(p, ag, c1, tbl, lane);    // predictor finalize -> trace clear
       ag.total_reward = 0;
       ag.flags = 1 | (test ? 2 : 0);
@@ -352,8 +352,8 @@ k_run_coop(Params p, CoopArrays ca, int agent_begin, int agent_end, int64_t n_st
 #pragma unroll
       for (int i = 0; i < S; ++i) next[i] = ag.x[i];
       rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(ag.action), next);
-      observe<DYN>(next, p.timeout, obs, terminal);
-      reward = evaluate<DYN>(ag.x, ag.action, next);
+      observe<DYN>(next, p.timeout, obs, terminal, p.end_stop_penalty);
+      reward = evaluate<DYN>(ag.x, ag.action, next, p.end_stop_penalty);
       ag.total_reward += reward;
 #pragma unroll
       for (int i = 0; i < S; ++i) ag.x[i] = next[i];

@@ -267,7 +267,7 @@ __device__ __forceinline__ void rk4(double tau, int steps, double u, double (&x)
 
 template <int DYN>
 __device__ __forceinline__ void observe(const double (&x)[Dyn<DYN>::S], double timeout,
-                                        double (&obs)[Dyn<DYN>::OBS], int &terminal)
+                                        double (&obs)[Dyn<DYN>::OBS], int &terminal, int end_stop_penalty = 1)
 {
   if (DYN == 0)
   {
@@ -283,7 +283,7 @@ __device__ __forceinline__ void observe(const double (&x)[Dyn<DYN>::S], double t
     double a = fmod(x[1] + GRLCU_PI, 2 * GRLCU_PI);
     if (a < 0) a += 2 * GRLCU_PI;
     obs[0] = x[0]; obs[1] = a; obs[2] = x[2]; obs[3] = x[3];
-    if (fabs(x[0]) > 2.4) terminal = 2;
+    if (end_stop_penalty && fabs(x[0]) > 2.4) terminal = 2;
     else if (x[4] > timeout) terminal = 1;
     else terminal = 0;
   }
@@ -300,7 +300,7 @@ __device__ __forceinline__ void observe(const double (&x)[Dyn<DYN>::S], double t
 
 template <int DYN>
 __device__ __forceinline__ double evaluate(const double (&state)[Dyn<DYN>::S], double action,
-                                           const double (&next)[Dyn<DYN>::S])
+                                           const double (&next)[Dyn<DYN>::S], int end_stop_penalty = 1)
 {
   if (DYN == 0)
   {
@@ -314,12 +314,13 @@ __device__ __forceinline__ double evaluate(const double (&state)[Dyn<DYN>::S], d
   }
   else if (DYN == 1)
   {
-    // cart_pole.cpp:188-197,229-235 (shaping 0, action_penalty 0, end_stop_penalty 1)
+    // cart_pole.cpp:188-197,229-235 (shaping 0, action_penalty 0; end_stop_penalty 1 by default, 0 in
+    // cfg/cart_pole/ac_tc.yaml: the cart then rides the end stop of the dynamics without ending the episode)
     double a = fmod(fabs(next[1]), 2 * GRLCU_PI);
     if (a > GRLCU_PI) a -= 2 * GRLCU_PI;
     double potential = -2 * (next[0] * next[0]) - 0.1 * (next[2] * next[2]) - (a * a) - 0.1 * (next[3] * next[3]);
     double failed = fabs(next[0]) > 2.4 ? 1. : 0.;
-    return potential - 0. - failed * 10000;
+    return potential - 0. - end_stop_penalty * failed * 10000;
   }
   else
   {

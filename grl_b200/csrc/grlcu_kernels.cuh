@@ -54,8 +54,8 @@ __global__ void k_project(Projector proj, int64_t n, const double *in, uint32_t 
 
 // K1: ModeledEnvironment::step body for n independent (state, action) pairs (row-major).
 template <int DYN>
-__global__ void k_model_step(int64_t n, double tau, int isteps, double timeout, const double *state,
-                             const double *action, double *next, double *obs, double *reward, int32_t *terminal)
+__global__ void k_model_step(int64_t n, double tau, int isteps, double timeout, int end_stop_penalty,
+                             const double *state, const double *action, double *next, double *obs, double *reward, int32_t *terminal)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (int64_t)gridDim.x * blockDim.x)
@@ -66,8 +66,8 @@ __global__ void k_model_step(int64_t n, double tau, int isteps, double timeout, 
     for (int i = 0; i < S; ++i) x0[i] = x[i] = state[t * S + i];
     const double act = action[t];
     rk4<DYN>(tau, isteps, Dyn<DYN>::actuate(act), x);
-    observe<DYN>(x, timeout, o, term);
-    double r = evaluate<DYN>(x0, act, x);
+    observe<DYN>(x, timeout, o, term, end_stop_penalty);
+    double r = evaluate<DYN>(x0, act, x, end_stop_penalty);
 #pragma unroll
     for (int i = 0; i < S; ++i) next[t * S + i] = x[i];
 #pragma unroll
@@ -165,7 +165,7 @@ __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag
   constexpr int OBS = Dyn<DYN>::OBS;
   double obs[OBS];
   int term;
-  observe<DYN>(ag.x, p.timeout, obs, term);
+  observe<DYN>(ag.x, p.timeout, obs, term, p.end_stop_penalty);
   if (!test)
   {
     // predictor finalize -> trace clear
@@ -242,7 +242,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
         task_start<DYN>(u53(w.w[0], w.w[1]), p.randomization, test ? 1 : 0, ag.x);
       }
       int term0;
-      observe<DYN>(ag.x, p.timeout, obs, term0);
+      observe<DYN>(ag.x, p.timeout, obs, term0, p.end_stop_penalty);
       if (!test)
       {
         // predictor finalize -> trace clear
@@ -260,8 +260,8 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
 #pragma unroll
       for (int i = 0; i < S; ++i) next[i] = ag.x[i];
       rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(ag.action), next);
-      observe<DYN>(next, p.timeout, obs, terminal);
-      reward = evaluate<DYN>(ag.x, ag.action, next);
+      observe<DYN>(next, p.timeout, obs, terminal, p.end_stop_penalty);
+      reward = evaluate<DYN>(ag.x, ag.action, next, p.end_stop_penalty);
       ag.total_reward += reward;
 #pragma unroll
       for (int i = 0; i < S; ++i) ag.x[i] = next[i];
@@ -333,8 +333,8 @@ k_replay(Params p, ReplayIO io)
   for (int i = 0; i < S; ++i) x0[i] = next[i] = io.state[(size_t)i * n + a];
   const double act = io.action[a];
   rk4<DYN>(p.tau, p.isteps, Dyn<DYN>::actuate(act), next);
-  observe<DYN>(next, p.timeout, obs, terminal);
-  const double r_own = evaluate<DYN>(x0, act, next);
+  observe<DYN>(next, p.timeout, obs, terminal, p.end_stop_penalty);
+  const double r_own = evaluate<DYN>(x0, act, next, p.end_stop_penalty);
   if (io.o_next) for (int i = 0; i < S; ++i) io.o_next[(size_t)i * n + a] = next[i];
   if (io.o_obs) for (int i = 0; i < OBS; ++i) io.o_obs[(size_t)i * n + a] = obs[i];
   if (io.o_reward) io.o_reward[a] = r_own;

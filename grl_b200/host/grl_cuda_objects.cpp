@@ -66,6 +66,7 @@ void CudaBatchedEnvironment::contribute(CudaPath *p) const
   p->cfg.control_step = model_->tau;
   p->cfg.timeout = task_->timeout;
   p->cfg.randomization = task_->randomization;
+  p->cfg.end_stop_penalty = task_->end_stop_penalty;
   p->cfg.obs_dims = (int)task_->observation_min.size();
   p->have_env = true;
 }

@@ -201,9 +201,16 @@ Configurable *Configurator::object(const std::string &path) const
 bool Configurator::value(const std::string &path, std::string *out) const
 {
   auto it = values_.find(path);
-  if (it == values_.end()) return false;
-  *out = it->second;
-  return true;
+  if (it != values_.end()) { *out = it->second; return true; }
+  // a path through a parameter that was itself given as a reference ("…/critic/projector/memory" where
+  // critic/projector names the policy's projector, cfg/pendulum/ac_tc.yaml): follow it like the reference's
+  // ReferenceConfigurator does (configurable.cpp:318-346)
+  for (size_t cut = path.rfind('/'); cut != std::string::npos && cut > 0; cut = path.rfind('/', cut - 1))
+  {
+    auto at = aliases_.find(path.substr(0, cut));
+    if (at != aliases_.end()) return value(at->second + path.substr(cut), out);
+  }
+  return false;
 }
 
 static std::string base_type(const std::string &t)
@@ -240,6 +247,7 @@ Configurable *Configurator::build(const YamlNode &node, const std::string &path,
       {
         child = object(pn->scalar);         // reference to an earlier object
         if (!child) throw Exception(ppath + ": '" + pn->scalar + "' does not name an object defined earlier");
+        aliases_[ppath] = child->path();
       }
       if (child)
       {

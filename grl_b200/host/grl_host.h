@@ -195,6 +195,7 @@ class Configurator
     std::map<std::string, Configurable *> by_path_;
     std::map<std::string, std::string> values_;                     // path/param -> literal (incl. provided)
     std::map<std::string, Configurable *> value_objects_;           // path/param -> referenced object
+    std::map<std::string, std::string> aliases_;                    // path/param given as a reference -> path of the object it names
 };
 
 }  // namespace grl

@@ -107,16 +107,17 @@ void CartPoleSwingupTask::request(ConfigurationRequest *config)
 }
 void CartPoleSwingupTask::configure(Configuration &config)
 {
-  // cart_pole.cpp:122-147; the device code implements the defaults of cart_pole.h:75
+  // cart_pole.cpp:122-147; the device code implements shaping = 0, action_penalty = 0 (the defaults of
+  // cart_pole.h:75) and both values of end_stop_penalty (cfg/cart_pole/ac_tc.yaml switches it off)
   dynamics_id = GRLCU_DYN_CART_POLE;
   timeout = config["timeout"];
   randomization = config["randomization"];
   if ((int)config["shaping"] != 0) throw bad_param("task/cart_pole/swingup:shaping");
-  if ((int)config["end_stop_penalty"] != 1) throw bad_param("task/cart_pole/swingup:end_stop_penalty");
+  end_stop_penalty = config["end_stop_penalty"];
   if ((int)config["action_penalty"] != 0) throw bad_param("task/cart_pole/swingup:action_penalty");
   observation_min = {-2.4, 0., -10.0, -5 * M_PI}; observation_max = {2.4, 2 * M_PI, 10.0, 5 * M_PI};
   action_min = {-15.}; action_max = {15.};
-  provide_limits(config, *this, 4, -2 * pow(2.4, 2) - 0.1 * pow(10, 2) - pow(M_PI, 2) - 0.1 * pow(5 * M_PI, 2) - 10000, 0);
+  provide_limits(config, *this, 4, -2 * pow(2.4, 2) - 0.1 * pow(10, 2) - pow(M_PI, 2) - 0.1 * pow(5 * M_PI, 2) - end_stop_penalty * 10000, 0);
 }
 
 void CartDoublePoleBalancingTask::request(ConfigurationRequest *config)
@@ -240,7 +241,7 @@ void FixedAgent::request(ConfigurationRequest *config)
 void FixedAgent::configure(Configuration &config) { policy = dynamic_cast<Policy *>(config["policy"].ptr()); }
 
 // ---- shared device context ------------------------------------------------------------------------------
-CudaPath::CudaPath() { memset(&cfg, 0, sizeof(cfg)); cfg.test_interval = -1; cfg.seed = 1; }
+CudaPath::CudaPath() { memset(&cfg, 0, sizeof(cfg)); cfg.test_interval = -1; cfg.seed = 1; cfg.end_stop_penalty = 1; }
 CudaPath::~CudaPath() { release(); }
 
 void CudaPath::check(int rc)

@@ -76,6 +76,7 @@ struct DynamicalModel : Configurable
 struct Task : Configurable
 {
   int dynamics_id = -1; double timeout = 0, randomization = 0;
+  int end_stop_penalty = 1;      // task/cart_pole/swingup only (cart_pole.h:75)
   Vector observation_min, observation_max, action_min, action_max;
 };
 struct PendulumSwingupTask : Task

@@ -71,6 +71,9 @@ typedef struct grlcu_config
   double  actor_wrapping[GRLCU_MAX_DIMS];    /* which describe the critic's (obs dims only, no action)     */
   double  target_epsilon;     /* GRLCU_ALGO_EXPECTED_SARSA: the target policy's sampler (predictor `policy`,
                                  sarsa.cpp:145): < 0 sampler/greedy, else sampler/epsilon_greedy's epsilon */
+  int32_t end_stop_penalty;   /* task/cart_pole/swingup end_stop_penalty (cart_pole.cpp:177,196; the reference's default
+                                 is 1, cfg/cart_pole/ac_tc.yaml uses 0); ignored by the other tasks */
+  int32_t reserved_;          /* padding, must be 0 */
 } grlcu_config;
 
 typedef struct grlcu_ctx grlcu_ctx;

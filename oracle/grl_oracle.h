@@ -90,6 +90,8 @@ typedef struct orc_config
   double  actor_wrapping[ORC_MAX_DIMS];
   /* predictor/critic/expected_sarsa: the target policy's sampler; < 0: sampler/greedy, else epsilon-greedy */
   double  target_epsilon;
+  int32_t end_stop_penalty;   /* task/cart_pole/swingup: end_stop_penalty (cart_pole.h:75 default 1) */
+  int32_t reserved_;
 } orc_config;
 
 /* Everything observable about one agent-step (one iteration of

@@ -294,7 +294,7 @@ void orc_observe(const orc_config *c, const double *x, double *obs, int32_t *ter
     double a = fmod(x[1] + M_PI, 2 * M_PI);
     if (a < 0) a += 2 * M_PI;
     obs[0] = x[0]; obs[1] = a; obs[2] = x[2]; obs[3] = x[3];
-    if (cp_failed(x)) *terminal = 2;          /* end_stop_penalty_ = 1 (cart_pole.h:75) */
+    if (c->end_stop_penalty && cp_failed(x)) *terminal = 2;   /* cart_pole.cpp:177; default 1 (cart_pole.h:75) */
     else if (x[4] > c->timeout) *terminal = 1;
     else *terminal = 0;
   }
@@ -329,9 +329,9 @@ double orc_evaluate(const orc_config *c, const double *state, double action, con
   }
   else if (c->dynamics == ORC_DYN_CART_POLE)
   {
-    /* shaping_ = 0, action_penalty_ = 0, end_stop_penalty_ = 1:
-     * potential(next) - 0*pow(action/15,2)*2 - 1*failed(next)*10000 */
-    reward = cp_potential(next) - 0 * pow(action / 15, 2) * 2 - 1 * cp_failed(next) * 10000;
+    /* shaping_ = 0, action_penalty_ = 0:
+     * potential(next) - 0*pow(action/15,2)*2 - end_stop_penalty_*failed(next)*10000 (int product, cart_pole.cpp:196) */
+    reward = cp_potential(next) - 0 * pow(action / 15, 2) * 2 - c->end_stop_penalty * cp_failed(next) * 10000;
   }
   else
   {

@@ -35,7 +35,13 @@ class Config(C.Structure):
         ("action_min", C.c_double), ("action_max", C.c_double),
         ("actor_resolution", C.c_double * MAX_DIMS), ("actor_wrapping", C.c_double * MAX_DIMS),
         ("target_epsilon", C.c_double),
+        ("end_stop_penalty", C.c_int32), ("reserved_", C.c_int32),
     ]
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        if "end_stop_penalty" not in kw:
+            self.end_stop_penalty = 1     # the reference's default (cart_pole.h:75)
 
 
 class Record(C.Structure):
@@ -116,6 +122,35 @@ def cart_double_pole_ac_config(memory=131072, **kw):
     for k, v in kw.items():
         setattr(c, k, v)
     return c
+
+
+def _ac_config(dynamics, control_step, timeout_, memory, res, wrap, sigma_, amax, **kw):
+    c = Config()
+    c.dynamics, c.integration_steps, c.control_step = dynamics, 5, control_step
+    c.timeout, c.randomization = timeout_, 0.0
+    c.tilings, c.memory, c.obs_dims, c.n_actions = 16, memory, len(res), 0
+    for i, (r, w) in enumerate(zip(res, wrap)):
+        c.resolution[i] = c.actor_resolution[i] = r
+        c.wrapping[i] = c.actor_wrapping[i] = w
+    c.alpha, c.gamma, c.lambda_, c.epsilon = 0.2, 0.97, 0.65, 0.0
+    c.trace, c.test_interval = TRACE_REPLACING, 10
+    c.init_min, c.init_max, c.seed = 0.0, 1.0, 1
+    c.rng, c.algo = RNG_PHILOX, ALGO_AC
+    c.sigma, c.actor_alpha, c.action_min, c.action_max = sigma_, 0.01, -amax, amax
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+def pendulum_ac_config(memory=65536, **kw):
+    """cfg/pendulum/ac_tc.yaml (reference)."""
+    return _ac_config(DYN_PENDULUM, 0.03, 2.99, memory, [0.31415, 3.1415], [6.283, 0], 1.0, 3.0, **kw)
+
+
+def cart_pole_ac_config(memory=262144, **kw):
+    """cfg/cart_pole/ac_tc.yaml (reference): end_stop_penalty 0."""
+    kw.setdefault("end_stop_penalty", 0)
+    return _ac_config(DYN_CART_POLE, 0.05, 9.99, memory, [2.5, 0.157075, 2.5, 1.57075], [0, 6.283, 0, 0], 5.0, 15.0, **kw)
 
 
 _lib = None

@@ -63,8 +63,8 @@ def test_double_pole_projection_and_dynamics(G, orc):
         b.close()
 
 
-def _replay_ac(G, n, steps, mem, **kw):
-    cfg, oc = G.cart_double_pole_ac_config(memory=mem, **kw), O.cart_double_pole_ac_config(memory=mem, **kw)
+def _replay_ac(G, n, steps, mem, which="cart_double_pole", **kw):
+    cfg, oc = getattr(G, which + "_ac_config")(memory=mem, **kw), getattr(O, which + "_ac_config")(memory=mem, **kw)
     b = G.Batch(cfg, n)
     ob = O.OracleBatch(oc, n)
     try:
@@ -113,6 +113,56 @@ def test_replay_ac(G, orc):
 def test_replay_ac_small_table_and_saturating_actor(G, orc):
     # memory 509: duplicate indices inside projections; a large actor step drives weights into the +-20 clamp
     _replay_ac(G, n=32, steps=300, mem=509, test_interval=-1, actor_alpha=0.5, sigma=15.0)
+
+
+def test_replay_ac_pendulum(G, orc):
+    # the reference's cfg/pendulum/ac_tc.yaml: same agent on the pendulum swing-up (2-D observations, wrapping angle)
+    _replay_ac(G, n=48, steps=330, mem=65536, which="pendulum", test_interval=2, randomization=1.0)
+    _replay_ac(G, n=16, steps=250, mem=251, which="pendulum", test_interval=-1, actor_alpha=0.3, sigma=4.0)
+
+
+def test_replay_ac_cart_pole(G, orc):
+    # the reference's cfg/cart_pole/ac_tc.yaml: end_stop_penalty 0 (the cart rides the end stop, episodes end by
+    # timeout only); and the task's default end_stop_penalty 1 (absorbing end, reward -10000) with the same agent
+    _replay_ac(G, n=32, steps=450, mem=262144, which="cart_pole", test_interval=1, randomization=1.0)
+    _replay_ac(G, n=32, steps=300, mem=4099, which="cart_pole", test_interval=3, end_stop_penalty=1, sigma=15.0)
+
+
+def test_end_stop_penalty_off(G, orc):
+    """task/cart_pole/swingup end_stop_penalty = 0 (cart_pole.cpp:177,196): beyond the end stop the episode goes on and
+    the reward is the plain potential; with 1 the observation is absorbing and the reward carries -10000."""
+    rng = np.random.default_rng(5)
+    m = 2000
+    st = np.zeros((m, 5))
+    st[:, 0] = rng.uniform(-2.6, 2.6, m)
+    st[:, 1] = rng.uniform(-7, 7, m)
+    st[:, 2:4] = rng.uniform(-3, 3, (m, 2))
+    st[:, 4] = rng.uniform(0, 10.2, m)
+    act = rng.uniform(-15, 15, m)
+    dp = C.POINTER(C.c_double)
+    seen = set()
+    for esp in (0, 1):
+        cfg, oc = G.cart_pole_ac_config(memory=1024, end_stop_penalty=esp), O.cart_pole_ac_config(memory=1024, end_stop_penalty=esp)
+        b = G.Batch(cfg, 1)
+        try:
+            nxt, obs, rew, term = b.model_step(st, act)
+        finally:
+            b.close()
+        for k in range(m):
+            on, oo, orw, ot = np.empty(7), np.empty(8), C.c_double(), C.c_int32()
+            s = np.ascontiguousarray(st[k])
+            orc.orc_env_step(C.byref(oc), s.ctypes.data_as(dp), C.c_double(act[k]), on.ctypes.data_as(dp),
+                             oo.ctypes.data_as(dp), C.byref(orw), C.byref(ot))
+            assert _rel(nxt[k], on[:5]) <= RTOL and term[k] == ot.value, (esp, k)
+            assert abs(rew[k] - orw.value) <= RTOL * max(abs(orw.value), 1e-300), (esp, k)
+            seen.add((esp, int(term[k])))
+        out = np.abs(nxt[:, 0]) > 2.4
+        assert out.any()
+        assert np.all(term[out] == 2) if esp else np.all(term[out] != 2)
+        assert np.all(rew[out] < -9000) if esp else np.all(rew[out] > -1000)
+    assert seen == {(0, 0), (0, 1), (1, 0), (1, 1), (1, 2)}
+    with pytest.raises(G.GrlcuError):
+        G.Batch(G.cart_pole_ac_config(memory=1024, end_stop_penalty=2), 1)
 
 
 def test_ac_free_running_statistics(G, orc):

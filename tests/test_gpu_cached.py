@@ -33,7 +33,7 @@ def _run(G, mk, mode, n, launches, sweep=False, coop_cohort=None, coop_lanes=Non
             b.run(k)
         res = b.results()
         tables = np.stack([b.get_table(i) for i in range(n)])
-        if mk is G.cart_double_pole_ac_config:
+        if b.cfg.algo == G.capi.ALGO_AC:
             tables = np.concatenate([tables, np.stack([b.get_actor_table(i) for i in range(n)])], axis=1)
         states = [b.get_state(i) for i in range(n)]
     finally:
@@ -58,20 +58,26 @@ def _run(G, mk, mode, n, launches, sweep=False, coop_cohort=None, coop_lanes=Non
     # actor-critic (BASELINE configs[3]): the critic's trace goes through the cache, the actor table does not
     dict(which="ac", n=64, memory=131072, launches=[90, 1, 310], test_interval=3),
     dict(which="ac", n=32, memory=509, launches=[350], test_interval=-1, actor_alpha=0.5, sigma=15.0),
+    # the same agent on the pendulum and on the cart-pole (cfg/pendulum/ac_tc.yaml, cfg/cart_pole/ac_tc.yaml)
+    dict(which="pendulum_ac", n=64, memory=65536, launches=[120, 230], test_interval=2, randomization=1.0),
+    dict(which="pendulum_ac", n=32, memory=263, launches=[300], test_interval=-1, randomization=1.0, sigma=3.0, actor_alpha=0.3),
+    dict(which="cart_pole_ac", n=64, memory=262144, launches=[250, 200], test_interval=1, randomization=1.0),
+    dict(which="cart_pole_ac", n=32, memory=2053, launches=[420], test_interval=-1, end_stop_penalty=1, sigma=15.0),
 ])
 def test_cached_equals_uncached(case):
     import grl_b200 as G
     case = dict(case)
     which = case.pop("which")
-    mk = {"pendulum": G.pendulum_config, "cart_pole": G.cart_pole_config, "ac": G.cart_double_pole_ac_config}[which]
+    mk = {"pendulum": G.pendulum_config, "cart_pole": G.cart_pole_config, "ac": G.cart_double_pole_ac_config,
+          "pendulum_ac": G.pendulum_ac_config, "cart_pole_ac": G.cart_pole_ac_config}[which]
     n, launches = case.pop("n"), case.pop("launches")
-    if which != "ac":
+    if which in ("pendulum", "cart_pole"):
         case["randomization"] = 1.0
     r1, t1, s1 = _run(G, mk, 1, n, launches, **case)
     # mode 0: one thread per agent with the value cache; mode 2: sixteen lanes per agent in L2-sized cohorts
     # (grlcu_coop.cuh; SARSA family only), once as a single cohort and once as several ragged ones
     variants = [dict(mode=0)]
-    if which != "ac":
+    if which in ("pendulum", "cart_pole"):
         variants += [dict(mode=2, coop_lanes=4), dict(mode=2, coop_lanes=4, coop_cohort=20), dict(mode=2, coop_lanes=16),
                      dict(mode=2, coop_lanes=8, coop_cohort=28), dict(mode=2, coop_lanes=2)]
     for v in variants:

@@ -62,6 +62,25 @@ def test_actor_critic_config_resolves_to_the_harness_config(grld):
     assert got["actor_wrapping"] == [0.0] * 6
 
 
+@pytest.mark.parametrize("yaml,mk", [("cfg/pendulum/ac_tc_cuda.yaml", "pendulum_ac_config"),
+                                     ("cfg/cart_pole/ac_tc_cuda.yaml", "cart_pole_ac_config")])
+def test_sibling_actor_critic_configs_resolve_to_the_harness_configs(grld, yaml, mk):
+    """The reference's other tile-coded actor-critic configs (cfg/pendulum/ac_tc.yaml, cfg/cart_pole/ac_tc.yaml)."""
+    import grl_b200
+    rc, out, err = check(grld, os.path.join(ROOT, yaml))
+    assert rc == 0, err
+    got = json.loads(out)
+    want = getattr(grl_b200, mk)(memory=got["memory"], test_interval=10, randomization=got["randomization"])
+    n = want.obs_dims
+    for k in ("dynamics", "integration_steps", "control_step", "timeout", "tilings", "memory", "obs_dims", "n_actions",
+              "alpha", "gamma", "epsilon", "trace", "init_min", "init_max", "seed", "algo", "sigma", "actor_alpha",
+              "action_min", "action_max", "end_stop_penalty"):
+        assert got[k] == getattr(want, k), k
+    assert got["resolution"][:n] == list(want.resolution)[:n] == got["actor_resolution"]
+    assert got["wrapping"][:n] == list(want.wrapping)[:n] == got["actor_wrapping"]
+    assert got["end_stop_penalty"] == (0 if "cart_pole" in yaml else 1)
+
+
 def swap_types(text):
     """The only edit a GRL user makes to an existing YAML: the four type names (+ a table size that fits)."""
     text = text.replace("type: environment/modeled", "type: environment/model/cuda_batched")
@@ -103,6 +122,23 @@ def test_reference_actor_critic_yaml_loads_with_the_type_names_swapped(grld, tmp
     assert got["dynamics"] == 2 and got["algo"] == 1 and got["memory"] == 67108864 and got["obs_dims"] == 6
     assert (got["sigma"], got["actor_alpha"], got["alpha"], got["lambda"]) == (5.0, 0.01, 0.2, 0.65)
     assert (got["action_min"], got["action_max"], got["timeout"], got["test_interval"]) == (-20.0, 20.0, 4.99, 10)
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_CFG), reason="reference tree not present (GPU box)")
+@pytest.mark.parametrize("name,dyn,obs,sigma,amax,esp", [("pendulum/ac_tc.yaml", 0, 2, 1.0, 3.0, 1),
+                                                         ("cart_pole/ac_tc.yaml", 1, 4, 5.0, 15.0, 0)])
+def test_reference_sibling_actor_critic_yamls_load_with_the_type_names_swapped(grld, tmp_path, name, dyn, obs, sigma, amax, esp):
+    """pendulum/ac_tc.yaml reaches the critic's memory through a parameter that is itself a reference
+    (critic/projector names the policy's projector); cart_pole/ac_tc.yaml switches the end-stop penalty off."""
+    dst = tmp_path / "swapped.yaml"
+    dst.write_text(swap_types(open(os.path.join(REF_CFG, name)).read()))
+    rc, out, err = check(grld, str(dst))
+    assert rc == 0, err
+    got = json.loads(out)
+    assert (got["dynamics"], got["algo"], got["memory"], got["obs_dims"]) == (dyn, 1, 8388608, obs)
+    assert (got["sigma"], got["actor_alpha"], got["alpha"], got["lambda"]) == (sigma, 0.01, 0.2, 0.65)
+    assert (got["action_min"], got["action_max"], got["end_stop_penalty"]) == (-amax, amax, esp)
+    assert got["actor_resolution"] == got["resolution"][:obs] and got["actor_wrapping"] == got["wrapping"][:obs]
 
 
 def test_actor_critic_error_behaviour(grld, tmp_path):
@@ -238,21 +274,28 @@ def test_grld_matches_ctypes_harness(grld, tmp_path):
 
 
 @pytest.mark.gpu
-def test_grld_actor_critic_matches_ctypes_harness(grld, tmp_path):
-    """cfg 4 from YAML: same per-agent results as the ctypes harness, and both tables checkpointed in the reference's format."""
+@pytest.mark.parametrize("yaml,mk,amax,kw", [
+    ("cfg/cart_double_pole/ac_tc_cuda.yaml", "cart_double_pole_ac_config", 20.0, {}),
+    ("cfg/pendulum/ac_tc_cuda.yaml", "pendulum_ac_config", 3.0, dict(randomization=1.0)),
+    ("cfg/cart_pole/ac_tc_cuda.yaml", "cart_pole_ac_config", 15.0, {}),
+])
+def test_grld_actor_critic_matches_ctypes_harness(grld, tmp_path, yaml, mk, amax, kw):
+    """cfg 4 (and its pendulum / cart-pole siblings) from YAML: same per-agent results as the ctypes harness, and both
+    tables checkpointed in the reference's format."""
     import grl_b200
-    base = open(os.path.join(ROOT, "cfg/cart_double_pole/ac_tc_cuda.yaml")).read()
+    base = open(os.path.join(ROOT, yaml)).read()
     y = base.replace("agents: 4096", "agents: 64").replace("steps: 5000", "steps: 600") \
-            .replace("steps_per_launch: 500", "steps_per_launch: 100").replace("memory: 131072", "memory: 8192") \
+            .replace("steps_per_launch: 500", "steps_per_launch: 100") \
             .replace("test_interval: 10", "test_interval: 3") \
             .replace("  save_every: never", "  output: %s\n  save_every: run" % (tmp_path / "ac"))
+    y = re.sub(r"        memory: \d+\n", "        memory: 8192\n", y)
     p = tmp_path / "small.yaml"
     p.write_text(y)
     out = subprocess.run([grld, "-s", "5", str(p)], capture_output=True, text=True)
     assert out.returncode == 0, out.stderr + out.stdout
     rows = [l.split() for l in open(str(tmp_path / "ac") + "-0.txt") if l.startswith("# ") and l[2].isdigit()]
     assert len(rows) == 64
-    cfg = grl_b200.cart_double_pole_ac_config(memory=8192, test_interval=3, seed=5)
+    cfg = getattr(grl_b200, mk)(memory=8192, test_interval=3, seed=5, **kw)
     b = grl_b200.Batch(cfg, 64)
     try:
         while True:
@@ -267,7 +310,7 @@ def test_grld_actor_critic_matches_ctypes_harness(grld, tmp_path):
         actor = np.fromfile(stem + "policy_representation.dat", dtype=np.float64)
         critic = np.fromfile(stem + "predictor_critic_representation.dat", dtype=np.float64)
         assert np.array_equal(actor, b.get_actor_table(0)) and np.array_equal(critic, b.get_table(0))
-        assert np.abs(actor).max() <= 20.0 and not np.array_equal(actor, critic)
+        assert np.abs(actor).max() <= amax and not np.array_equal(actor, critic)
         a7 = np.fromfile(stem + "policy_representation-agent7.dat", dtype=np.float64)
         assert np.array_equal(a7, b.get_actor_table(7))
     finally:
@@ -330,6 +373,8 @@ def test_grld_sweep_matches_ctypes_harness(grld, tmp_path):
     ("cfg/pendulum/sarsa_tc_cuda.yaml", "pendulum_config", dict(randomization=1.0, test_interval=-1)),
     ("cfg/cart_pole/sarsa_tc_cuda.yaml", "cart_pole_config", dict(randomization=1.0)),
     ("cfg/cart_double_pole/ac_tc_cuda.yaml", "cart_double_pole_ac_config", dict(test_interval=10)),
+    ("cfg/pendulum/ac_tc_cuda.yaml", "pendulum_ac_config", dict(randomization=1.0)),
+    ("cfg/cart_pole/ac_tc_cuda.yaml", "cart_pole_ac_config", dict()),
 ])
 def test_role_interfaces_of_the_shims(grld, tmp_path, yaml, mk, kw):
     """`grld_b200 -i`: Environment::start/step, Projector::project, Representation::read/write/update of the CUDA

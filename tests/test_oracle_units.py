@@ -118,6 +118,48 @@ def test_actor_critic_oracle_learns_and_respects_limits(orc):
         orc.orc_destroy(a)
 
 
+def test_sibling_actor_critic_configs_in_the_oracle(orc):
+    """cfg/pendulum/ac_tc.yaml and cfg/cart_pole/ac_tc.yaml: actions stay in the task's range; with end_stop_penalty 0
+    (cart_pole.cpp:177,196) no episode is absorbing, every episode runs to the timeout (200 steps) and no reward carries
+    the -10000 penalty even when the cart sits beyond the end stop; with 1 the same agent sees absorbing ends."""
+    import ctypes as C
+    import _oracle as O
+    rec = O.Record()
+    c = O.pendulum_ac_config(memory=1 << 16, test_interval=3)
+    a = orc.orc_create(C.byref(c), 1)
+    try:
+        n_done = 0
+        for t in range(1000):
+            orc.orc_step(a, C.byref(rec))
+            assert -3.0 <= rec.action <= 3.0 and rec.terminal in (0, 1)
+            n_done += rec.episode_done
+        assert n_done == 10                          # 100 steps per episode (timeout 2.99 at 0.03)
+    finally:
+        orc.orc_destroy(a)
+    seen = {}
+    for esp in (0, 1):
+        c = O.cart_pole_ac_config(memory=1 << 16, test_interval=-1, end_stop_penalty=esp, sigma=15.0)
+        a = orc.orc_create(C.byref(c), 2)
+        lens, cur, beyond, terms, rmin = [], 0, 0, set(), 0.0
+        try:
+            for t in range(4000):
+                orc.orc_step(a, C.byref(rec))
+                cur += 1
+                assert -15.0 <= rec.action <= 15.0
+                beyond += abs(rec.next[0]) > 2.4
+                terms.add(rec.terminal)
+                rmin = min(rmin, rec.reward)
+                if rec.episode_done:
+                    lens.append(cur); cur = 0
+        finally:
+            orc.orc_destroy(a)
+        seen[esp] = (lens, beyond, terms, rmin)
+    lens, beyond, terms, rmin = seen[0]
+    assert set(lens) == {200} and beyond > 0 and terms == {0, 1} and rmin > -1000
+    lens, beyond, terms, rmin = seen[1]
+    assert 2 in terms and min(lens) < 200 and rmin < -9000
+
+
 def test_q_learning_and_expected_sarsa_targets(orc):
     """predictor/critic/q (advantage.cpp:84-90) and predictor/critic/expected_sarsa (sarsa.cpp:172-173 ->
     q.cpp:56-68, greedy.cpp:88-98,220-238): the oracle's targets against a direct restatement on its own
