@@ -39,6 +39,9 @@ WORKLOADS = {
                   "cart-pole swing-up SARSA(lambda) tile coding (cfg/cart_pole/sarsa.yaml), 4-D state, 3 actions"),
     "cart_double_pole_ac": ("cart_double_pole_ac_config", 65536, 131072,
                             "cart-double-pole actor-critic, two tile-coded tables per agent (cfg/cart_double_pole/ac.yaml)"),
+    "cart_double_pole": ("cart_double_pole_config", 65536, 131072,
+                         "cart-double-pole balancing SARSA(lambda) tile coding (cfg/cart_double_pole/sarsa.yaml), 6-D state, "
+                         "lambda 0.92: 51-entry trace"),
     "pendulum_ac": ("pendulum_ac_config", 65536, 65536,
                     "pendulum swing-up actor-critic, two tile-coded tables per agent (cfg/pendulum/ac_tc.yaml)"),
     "cart_pole_ac": ("cart_pole_ac_config", 32768, 262144,
@@ -56,7 +59,7 @@ def make_config(mod, args):
     """The workload's config from `mod` (grl_b200 or the oracle harness: same maker names, same fields)."""
     maker = WORKLOADS[args.workload][0]
     kw = dict(memory=args.memory, test_interval=-1)
-    if args.workload != "cart_double_pole_ac":       # (task/cart_double_pole/balancing has no randomization parameter)
+    if args.workload not in ("cart_double_pole_ac", "cart_double_pole"):       # (task/cart_double_pole/balancing has no randomization parameter)
         kw["randomization"] = 1.0
     if args.workload == "sweep":
         kw["lambda_"] = max(SWEEP_LAMBDA)          # trace ring sized for the largest lambda of the grid

@@ -78,6 +78,19 @@ def cart_pole_config(memory=262144, **kw):
     return _fill(c, **kw)
 
 
+def cart_double_pole_config(memory=131072, **kw):
+    """cfg/cart_double_pole/sarsa.yaml of the reference (SARSA(lambda) tile coding on the cart-double-pole balancing task:
+    6-D observations, 3 actions, gamma 0.99, lambda 0.92 => a 51-entry trace ring, optimistic init 20..21)."""
+    c = Config()
+    _fill(c, dynamics=DYN_CART_DOUBLE_POLE, integration_steps=5, control_step=0.05, timeout=4.99, randomization=0.0,
+          tilings=16, memory=memory, obs_dims=6, n_actions=3,
+          resolution=[2.5, 0.0785375, 0.0785375, 2.5, 0.785375, 0.785375, 20], wrapping=[0] * 7,
+          actions=[-20.0, 0.0, 20.0],
+          alpha=0.2, gamma=0.99, lambda_=0.92, epsilon=0.02, trace=TRACE_REPLACING, test_interval=10,
+          init_min=20.0, init_max=21.0, seed=1, algo=ALGO_SARSA)
+    return _fill(c, **kw)
+
+
 def cart_double_pole_ac_config(memory=131072, **kw):
     """cfg/cart_double_pole/ac.yaml of the reference (actor-critic, two tile-coded tables per agent)."""
     c = Config()

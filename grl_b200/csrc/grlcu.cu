@@ -172,10 +172,11 @@ static int supported(const grlcu_config *cfg)
   if (cfg->algo != GRLCU_ALGO_SARSA && cfg->algo != GRLCU_ALGO_Q && cfg->algo != GRLCU_ALGO_EXPECTED_SARSA)
     return fail(GRLCU_ERR_UNSUPPORTED, "unknown algo %d", cfg->algo);
   if (cfg->algo == GRLCU_ALGO_EXPECTED_SARSA && cfg->target_epsilon > 1) return fail(GRLCU_ERR_ARG, "target_epsilon > 1");
-  if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE)
+  // cfg/pendulum/sarsa_tc.yaml, cfg/cart_pole/sarsa.yaml, cfg/cart_double_pole/sarsa.yaml of the reference
+  if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE && cfg->dynamics != GRLCU_DYN_CART_DOUBLE_POLE)
     return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for SARSA", cfg->dynamics);
   if (cfg->n_actions != 3) return fail(GRLCU_ERR_UNSUPPORTED, "n_actions %d: kernels are instantiated for 3", cfg->n_actions);
-  const int obs = cfg->dynamics == GRLCU_DYN_PENDULUM ? 2 : 4;
+  const int obs = cfg->dynamics == GRLCU_DYN_PENDULUM ? 2 : cfg->dynamics == GRLCU_DYN_CART_POLE ? 4 : 6;
   if (cfg->obs_dims != obs) return fail(GRLCU_ERR_ARG, "obs_dims %d does not match dynamics (%d)", cfg->obs_dims, obs);
   return 0;
 }
@@ -470,12 +471,7 @@ struct Scratch
     else if ((c)->cfg.dynamics == GRLCU_DYN_CART_POLE) { CALL(1); }  \
     else { CALL(2); }                                                \
   } while (0)
-// SARSA kernels are instantiated for pendulum and cart-pole only
-#define DISPATCH_SARSA(c, CALL)                                 \
-  do {                                                          \
-    if ((c)->cfg.dynamics == GRLCU_DYN_PENDULUM) { CALL(0); }   \
-    else { CALL(1); }                                           \
-  } while (0)
+#define DISPATCH_SARSA(c, CALL) DISPATCH_DYN(c, CALL)
 
 extern "C" int grlcu_project(grlcu_ctx *c, int64_t n, const double *in, uint32_t *hash, uint32_t *index)
 {
@@ -672,7 +668,8 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
   // the cache stays live between launches (values return to the tables lazily, see ensure_plain) unless the
   // agents run in cohorts or GRLCU_EAGER_CLOSE is set
   // GRLCU_MODE=2: sixteen lanes per agent, L2-sized cohorts (grlcu_coop.cuh); same eligibility as the value cache
-  if (c->p.mode == 2 && c->cfg.algo != GRLCU_ALGO_AC && c->cfg.tilings == kLanes && !c->p.force_slow &&
+  if (c->p.mode == 2 && c->cfg.algo != GRLCU_ALGO_AC && c->cfg.dynamics != GRLCU_DYN_CART_DOUBLE_POLE &&
+      c->cfg.tilings == kLanes && !c->p.force_slow &&
       c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64 && c->cfg.n_actions == 3)
   {
     if (int r = ensure_plain(c)) return r;

@@ -105,6 +105,25 @@ def cart_pole_config(memory=262144, **kw):
     return c
 
 
+def cart_double_pole_config(memory=131072, **kw):
+    """cfg/cart_double_pole/sarsa.yaml (reference) with a per-agent table size."""
+    c = Config()
+    c.dynamics, c.integration_steps, c.control_step = DYN_CART_DOUBLE_POLE, 5, 0.05
+    c.timeout, c.randomization = 4.99, 0.0
+    c.tilings, c.memory, c.obs_dims, c.n_actions = 16, memory, 6, 3
+    for i, v in enumerate([2.5, 0.0785375, 0.0785375, 2.5, 0.785375, 0.785375, 20]):
+        c.resolution[i] = v
+    for i, v in enumerate([-20.0, 0.0, 20.0]):
+        c.actions[i] = v
+    c.alpha, c.gamma, c.lambda_, c.epsilon = 0.2, 0.99, 0.92, 0.02
+    c.trace, c.test_interval = TRACE_REPLACING, 10
+    c.init_min, c.init_max, c.seed = 20.0, 21.0, 1
+    c.rng, c.algo = RNG_PHILOX, ALGO_SARSA
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
 def cart_double_pole_ac_config(memory=131072, **kw):
     """cfg/cart_double_pole/ac.yaml (reference): actor-critic with two tile-coded tables per agent."""
     c = Config()

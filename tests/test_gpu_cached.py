@@ -58,6 +58,9 @@ def _run(G, mk, mode, n, launches, sweep=False, coop_cohort=None, coop_lanes=Non
     # actor-critic (BASELINE configs[3]): the critic's trace goes through the cache, the actor table does not
     dict(which="ac", n=64, memory=131072, launches=[90, 1, 310], test_interval=3),
     dict(which="ac", n=32, memory=509, launches=[350], test_interval=-1, actor_alpha=0.5, sigma=15.0),
+    # SARSA on the cart-double-pole (cfg/cart_double_pole/sarsa.yaml): 51-entry ring
+    dict(which="cart_double_pole", n=64, memory=131072, launches=[150, 1, 250], test_interval=3, epsilon=0.1),
+    dict(which="cart_double_pole", n=32, memory=1021, launches=[300], test_interval=-1),
     # the same agent on the pendulum and on the cart-pole (cfg/pendulum/ac_tc.yaml, cfg/cart_pole/ac_tc.yaml)
     dict(which="pendulum_ac", n=64, memory=65536, launches=[120, 230], test_interval=2, randomization=1.0),
     dict(which="pendulum_ac", n=32, memory=263, launches=[300], test_interval=-1, randomization=1.0, sigma=3.0, actor_alpha=0.3),
@@ -69,6 +72,7 @@ def test_cached_equals_uncached(case):
     case = dict(case)
     which = case.pop("which")
     mk = {"pendulum": G.pendulum_config, "cart_pole": G.cart_pole_config, "ac": G.cart_double_pole_ac_config,
+          "cart_double_pole": G.cart_double_pole_config,
           "pendulum_ac": G.pendulum_ac_config, "cart_pole_ac": G.cart_pole_ac_config}[which]
     n, launches = case.pop("n"), case.pop("launches")
     if which in ("pendulum", "cart_pole"):

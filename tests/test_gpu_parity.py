@@ -24,14 +24,15 @@ def G():
 
 def _cfgs(G):
     return [("pendulum", G.pendulum_config, O.pendulum_config, 65536),
-            ("cart_pole", G.cart_pole_config, O.cart_pole_config, 262144)]
+            ("cart_pole", G.cart_pole_config, O.cart_pole_config, 262144),
+            ("cart_double_pole", G.cart_double_pole_config, O.cart_double_pole_config, 131072)]
 
 
 def _rel(a, b):
     return np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)) if a.size else 0.0
 
 
-@pytest.mark.parametrize("which", [0, 1])
+@pytest.mark.parametrize("which", [0, 1, 2])
 def test_tile_hash_bit_exact(G, orc, which):
     name, gcfg, ocfg, mem = _cfgs(G)[which]
     rng = np.random.default_rng(7 + which)
@@ -164,6 +165,15 @@ def test_replay_pendulum_small_table_collisions(G, orc):
 def test_replay_cart_pole(G, orc):
     _replay(G, G.cart_pole_config, O.cart_pole_config, n=32, steps=500, mem=262144,
             randomization=1.0, test_interval=3, epsilon=0.3)
+
+
+def test_replay_cart_double_pole_sarsa(G, orc):
+    """The reference's cfg/cart_double_pole/sarsa.yaml: 6-D observations (8 ints per hash), lambda = 0.92 with
+    gamma = 0.99 (a 51-entry trace ring, the 64-bit duplicate mask), optimistic initial values 20..21; early episodes
+    are short, so starts, absorbing ends and test episodes are frequent."""
+    _replay(G, G.cart_double_pole_config, O.cart_double_pole_config, n=32, steps=320, mem=131072, test_interval=3, epsilon=0.2)
+    _replay(G, G.cart_double_pole_config, O.cart_double_pole_config, n=16, steps=200, mem=521, test_interval=-1,
+            algo=O.ALGO_Q)
 
 
 def test_replay_per_agent_hyperparameters(G, orc):

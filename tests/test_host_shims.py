@@ -30,11 +30,13 @@ def check(grld, path, *extra):
 def test_shipped_configs_resolve_to_the_harness_configs(grld):
     import grl_b200
     for yaml, mk, agents in (("cfg/pendulum/sarsa_tc_cuda.yaml", grl_b200.pendulum_config, 65536),
-                             ("cfg/cart_pole/sarsa_tc_cuda.yaml", grl_b200.cart_pole_config, 32768)):
+                             ("cfg/cart_pole/sarsa_tc_cuda.yaml", grl_b200.cart_pole_config, 32768),
+                             ("cfg/cart_double_pole/sarsa_tc_cuda.yaml", grl_b200.cart_double_pole_config, 65536)):
         rc, out, err = check(grld, os.path.join(ROOT, yaml))
         assert rc == 0, err
         got = json.loads(out)
-        want = mk(memory=got["memory"], randomization=1.0, test_interval=got["test_interval"])
+        want = mk(memory=got["memory"], randomization=got["randomization"], test_interval=got["test_interval"])
+        assert got["randomization"] == (0.0 if "double" in yaml else 1.0)
         assert got["agents"] == agents
         for k in ("dynamics", "integration_steps", "control_step", "timeout", "randomization", "tilings", "memory",
                   "obs_dims", "n_actions", "alpha", "gamma", "epsilon", "trace", "init_min", "init_max", "seed", "algo"):
@@ -98,7 +100,8 @@ def swap_types(text):
 
 
 @pytest.mark.skipif(not os.path.isdir(REF_CFG), reason="reference tree not present (GPU box)")
-@pytest.mark.parametrize("name,dyn,mem", [("pendulum/sarsa_tc.yaml", 0, 8388608), ("cart_pole/sarsa.yaml", 1, 67108864)])
+@pytest.mark.parametrize("name,dyn,mem", [("pendulum/sarsa_tc.yaml", 0, 8388608), ("cart_pole/sarsa.yaml", 1, 67108864),
+                                          ("cart_double_pole/sarsa.yaml", 2, 67108864)])
 def test_reference_yaml_loads_with_only_the_type_names_swapped(grld, tmp_path, name, dyn, mem):
     src = open(os.path.join(REF_CFG, name)).read()
     dst = tmp_path / "swapped.yaml"
@@ -108,7 +111,7 @@ def test_reference_yaml_loads_with_only_the_type_names_swapped(grld, tmp_path, n
     got = json.loads(out)
     assert got["dynamics"] == dyn and got["memory"] == mem and got["seed"] == 7
     assert got["test_interval"] == 10 and got["trace"] == 1 and got["agents"] == 1
-    assert got["actions"] == ([-3.0, 0.0, 3.0] if dyn == 0 else [-15.0, 0.0, 15.0])   # discretizer via task/action_min,max
+    assert got["actions"] == [[-3.0, 0.0, 3.0], [-15.0, 0.0, 15.0], [-20.0, 0.0, 20.0]][dyn]   # discretizer via task/action_min,max
 
 
 @pytest.mark.skipif(not os.path.isdir(REF_CFG), reason="reference tree not present (GPU box)")
@@ -373,6 +376,7 @@ def test_grld_sweep_matches_ctypes_harness(grld, tmp_path):
     ("cfg/pendulum/sarsa_tc_cuda.yaml", "pendulum_config", dict(randomization=1.0, test_interval=-1)),
     ("cfg/cart_pole/sarsa_tc_cuda.yaml", "cart_pole_config", dict(randomization=1.0)),
     ("cfg/cart_double_pole/ac_tc_cuda.yaml", "cart_double_pole_ac_config", dict(test_interval=10)),
+    ("cfg/cart_double_pole/sarsa_tc_cuda.yaml", "cart_double_pole_config", dict()),
     ("cfg/pendulum/ac_tc_cuda.yaml", "pendulum_ac_config", dict(randomization=1.0)),
     ("cfg/cart_pole/ac_tc_cuda.yaml", "cart_pole_ac_config", dict()),
 ])
