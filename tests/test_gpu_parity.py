@@ -243,8 +243,9 @@ def test_free_running_matches_oracle_statistically(G, orc):
 def test_one_agent_views(G, orc):
     """grlcu_task_start / grlcu_read / grlcu_update: the single-agent views the L2-signature shims use."""
     for name, gcfg, ocfg, mem in _cfgs(G):
-        cfg = gcfg(memory=4096, randomization=1.0)
-        oc = ocfg(memory=4096, randomization=1.0)
+        rand = {} if name == "cart_double_pole" else dict(randomization=1.0)
+        cfg = gcfg(memory=4096, **rand)
+        oc = ocfg(memory=4096, **rand)
         b = G.Batch(cfg, 3)
         try:
             rng = np.random.default_rng(5)
@@ -252,11 +253,12 @@ def test_one_agent_views(G, orc):
             st, obs, term = b.task_start(u, test=0)
             st_t, obs_t, _ = b.task_start(u, test=1)
             S = b.S
-            # Task::start (pendulum.cpp:97-105, cart_pole.cpp:155-166): the randomised coordinate only
+            # Task::start (pendulum.cpp:97-105, cart_pole.cpp:155-166, cart_double_pole.cpp:250-262): the randomised
+            # coordinate only
             k = 0 if cfg.dynamics == 0 else 1
-            want = np.pi + (u * 2 * np.pi if cfg.dynamics == 0 else (0.1 * u - 0.05))
+            want = [np.pi + u * 2 * np.pi, np.pi + (0.1 * u - 0.05), u * 0.01 - 0.005][cfg.dynamics]
             assert np.array_equal(st[:, k], want), name
-            # pendulum test episodes are not randomised (pendulum.cpp:100); cart-pole ones are (cart_pole.cpp:160)
+            # pendulum test episodes are not randomised (pendulum.cpp:100); the others are (cart_pole.cpp:160)
             assert np.array_equal(st_t[:, k], np.full(64, np.pi) if cfg.dynamics == 0 else want), name
             mask = np.ones(S, bool); mask[k] = False
             assert not st[:, mask].any()
