@@ -349,6 +349,10 @@ def ours(args):
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         # sector-granular figure: the DRAM bytes the hardware moved per launch (ncu capture)
+                         # over this run's measured launch time, as a fraction of the same peak
+                         "traffic_frac": (traffic / (kern_ms / max(kern_launches, 1) * 1e-3) / 1e9 / peak)
+                                         if traffic and kern_ms > 0 else None,
                          "peak_source": peak_src, "random_access": random_access,
                          "bytes_per_agent_step": B, "V_mean": V,
                          "kernel": "grlcu::k_run_ac" if args.workload in AC_WORKLOADS else "grlcu::k_run",
