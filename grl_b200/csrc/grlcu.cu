@@ -172,6 +172,11 @@ static int supported(const grlcu_config *cfg)
   if (cfg->algo != GRLCU_ALGO_SARSA && cfg->algo != GRLCU_ALGO_Q && cfg->algo != GRLCU_ALGO_EXPECTED_SARSA)
     return fail(GRLCU_ERR_UNSUPPORTED, "unknown algo %d", cfg->algo);
   if (cfg->algo == GRLCU_ALGO_EXPECTED_SARSA && cfg->target_epsilon > 1) return fail(GRLCU_ERR_ARG, "target_epsilon > 1");
+  if (cfg->sampler != GRLCU_SAMPLER_EPSILON_GREEDY && cfg->sampler != GRLCU_SAMPLER_SOFTMAX)
+    return fail(GRLCU_ERR_UNSUPPORTED, "unknown sampler %d", cfg->sampler);
+  // softmax.cpp:34: tau in [1e-6, 100]
+  if (cfg->sampler == GRLCU_SAMPLER_SOFTMAX && !(cfg->softmax_tau >= 0.000001 && cfg->softmax_tau <= 100.))
+    return fail(GRLCU_ERR_ARG, "softmax_tau must be in [1e-6, 100]");
   // cfg/pendulum/sarsa_tc.yaml, cfg/cart_pole/sarsa.yaml, cfg/cart_double_pole/sarsa.yaml of the reference
   if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE && cfg->dynamics != GRLCU_DYN_CART_DOUBLE_POLE)
     return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for SARSA", cfg->dynamics);
@@ -284,6 +289,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   p.mode = getenv("GRLCU_MODE") ? atoi(getenv("GRLCU_MODE")) : 0;
   p.target_kind = cfg->algo == GRLCU_ALGO_Q ? 1 : cfg->algo == GRLCU_ALGO_EXPECTED_SARSA ? 2 : 0;
   p.target_epsilon = cfg->target_epsilon;
+  p.softmax_tau = cfg->sampler == GRLCU_SAMPLER_SOFTMAX ? cfg->softmax_tau : 0.;
   p.trace_cap = trace_capacity_for(cfg->gamma * cfg->lambda, cfg->trace);
   if (p.trace_cap < 0 || p.trace_cap > 160)
   {

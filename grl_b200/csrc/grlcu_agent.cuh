@@ -44,6 +44,7 @@ struct Params
   int32_t  mode;              // 0: trace value cache where eligible, 1: uncached
   int32_t  target_kind;       // bootstrap value: 0 Q(s',a') (SARSA), 1 max_a Q(s',a) (Q-learning), 2 policy value (expected SARSA)
   double   target_epsilon;    // expected SARSA: target policy's epsilon (< 0: greedy sampler)
+  double   softmax_tau;       // > 0: the learning policy's sampler is sampler/softmax with this temperature
   double   *cache_val;        // [cap*T][n] cached trace weights (grlcu_cached.cuh)
   uint32_t *cache_mask;       // [cap][n] valid bits per trace entry
   uint64_t *act_ctr, *test_act_ctr, *episode_ctr, *tt, *ss, *swept;
@@ -118,10 +119,50 @@ __device__ __forceinline__ double bootstrap_value(const double (&q)[A], int ai, 
   return qn;
 }
 
-// greedy.cpp:47-61 findmax + 63-86 / 151-218 sample (epsilon_.size() == 1, decay_ = 1)
+// SoftmaxSampler::distribution (softmax.cpp:61-101) + grl::sample(dist, 1.) (utils.h:227-240) on the uniform draw u.
+// Out of line: only contexts configured with sampler/softmax ever call it (code size, see q_values).
 template <int A>
-__device__ __forceinline__ int sample_action(const double (&q)[A], const Draws &d, double epsilon, bool test)
+__device__ __noinline__ int softmax_pick(const double *q, double tau, double u)
 {
+  double v[A], dist[A];
+  double max_power = -1.7976931348623157e308;
+#pragma unroll
+  for (int ii = 0; ii < A; ++ii)
+  {
+    v[ii] = 0;
+    const double pw = q[ii] / tau;
+    max_power = (max_power < pw) ? pw : max_power;
+  }
+  const double min_power = max_power + -100.;
+  const double center = (max_power + min_power) / 2.0;
+  double sum = 0;
+#pragma unroll
+  for (int ii = 0; ii < A; ++ii)
+  {
+    double pw = q[ii] / tau;
+    if (pw > min_power) { pw -= center; v[ii] = exp(pw); sum += v[ii]; dist[ii] = 1; }
+    else dist[ii] = 0;
+  }
+#pragma unroll
+  for (int ii = 0; ii < A; ++ii) dist[ii] *= v[ii] / sum;
+  const double r = u * 1.;
+  sum = 0;
+#pragma unroll
+  for (int ii = 0; ii < A; ++ii)
+  {
+    sum += dist[ii];
+    if (r < sum) return ii;
+  }
+  return A - 1;
+}
+
+// greedy.cpp:47-61 findmax + 63-86 / 151-218 sample (epsilon_.size() == 1, decay_ = 1); softmax_tau > 0: the learning
+// policy samples with sampler/softmax instead (test episodes stay greedy)
+template <int A>
+__device__ __forceinline__ int sample_action(const double (&q)[A], const Draws &d, double epsilon, bool test,
+                                             double softmax_tau = 0.)
+{
+  if (!test && softmax_tau > 0.) return softmax_pick<A>(q, softmax_tau, d.u);
   int mai = 0, man = 1;
 #pragma unroll
   for (int ii = 1; ii < A; ++ii)

@@ -420,7 +420,7 @@ k_run_coop(Params p, CoopArrays ca, int agent_begin, int agent_end, int64_t n_st
       }
 #pragma unroll
       for (int aa = 0; aa < A; ++aa) q[aa] = ordered_sum<L>(gm, w[aa]) / T;
-      ai = sample_action<A>(q, d, ag.epsilon, test);
+      ai = sample_action<A>(q, d, ag.epsilon, test, p.softmax_tau);
       qn = bootstrap_value<A>(q, ai, p.target_kind, p.target_epsilon);
     }
     else if (learn)

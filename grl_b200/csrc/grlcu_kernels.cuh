@@ -129,7 +129,7 @@ __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, co
     double q[A];
     if (CACHED) q_values<DYN, T, A>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, p.n, a, CacheResolve<T>{c});
     else q_values<DYN, T, A>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, p.n, a, NoResolve());
-    own = sample_action<A>(q, d, ag.epsilon, test);
+    own = sample_action<A>(q, d, ag.epsilon, test, p.softmax_tau);
     ai = force >= 0 ? force : own;
     if (o_q)
     {

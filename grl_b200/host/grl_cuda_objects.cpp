@@ -326,6 +326,8 @@ void CudaExpectedSARSAPredictor::contribute(CudaPath *p) const
   CudaSARSAPredictor::contribute(p);
   p->cfg.algo = GRLCU_ALGO_EXPECTED_SARSA;
   // GreedySampler::distribution (greedy.cpp:88-98) or EpsilonGreedySampler::distribution (greedy.cpp:220-238)
+  if (dynamic_cast<SoftmaxSampler *>(policy_->sampler))
+    throw Exception(path() + ": the expected-SARSA target policy must use sampler/greedy or sampler/epsilon_greedy");
   p->cfg.target_epsilon = dynamic_cast<EpsilonGreedySampler *>(policy_->sampler) ? policy_->sampler->epsilon : -1.;
 }
 

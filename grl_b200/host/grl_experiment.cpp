@@ -119,6 +119,12 @@ void OnlineLearningExperiment::assemble()
     c.n_actions = (int)qp->discretizer->values.size();
     for (int i = 0; i < c.n_actions; ++i) c.actions[i] = qp->discretizer->values[i];
     c.epsilon = qp->sampler->epsilon;
+    if (dynamic_cast<SoftmaxSampler *>(qp->sampler))
+    {
+      if (!sweep_epsilon_.empty()) throw bad_param("experiment/online_learning:sweep_epsilon");   // no epsilon to sweep
+      c.sampler = GRLCU_SAMPLER_SOFTMAX;
+      c.softmax_tau = qp->sampler->tau;
+    }
     env->attach(&path_); proj->attach(&path_); rep->attach(&path_);
     checkpoint_reps_ = {rep};
   }

@@ -19,6 +19,7 @@ REGISTER_CONFIGURABLE(CartDoublePoleBalancingTask)
 REGISTER_CONFIGURABLE(UniformDiscretizer)
 REGISTER_CONFIGURABLE(GreedySampler)
 REGISTER_CONFIGURABLE(EpsilonGreedySampler)
+REGISTER_CONFIGURABLE(SoftmaxSampler)
 REGISTER_CONFIGURABLE(ReplacingEnumeratedTrace)
 REGISTER_CONFIGURABLE(AccumulatingEnumeratedTrace)
 REGISTER_CONFIGURABLE(QPolicy)
@@ -175,6 +176,17 @@ void EpsilonGreedySampler::configure(Configuration &config)
   if (e.size() != 1) throw Exception(path() + ": the batched CUDA path supports a single epsilon");
   if ((double)config["decay_rate"] != 1.) throw bad_param("sampler/epsilon_greedy:decay_rate");
   epsilon = e[0];
+}
+
+void SoftmaxSampler::request(ConfigurationRequest *config)
+{
+  // softmax.cpp:32-35
+  config->push_back(CRP("tau", "Temperature of Boltzmann distribution", 1., CRP::Online, 0.000001, 100.));
+}
+void SoftmaxSampler::configure(Configuration &config)
+{
+  tau = config["tau"];
+  if (!(tau >= 0.000001 && tau <= 100.)) throw bad_param("sampler/softmax:tau");
 }
 
 void QPolicy::request(ConfigurationRequest *config)

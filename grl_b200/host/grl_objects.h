@@ -107,7 +107,7 @@ struct UniformDiscretizer : Configurable
   void configure(Configuration &config) override;
 };
 
-struct Sampler : Configurable { double epsilon = 0; };
+struct Sampler : Configurable { double epsilon = 0; double tau = 0; };   // tau > 0: sampler/softmax
 struct GreedySampler : Sampler
 {
   TYPEINFO("sampler/greedy", "Maximum search")
@@ -116,6 +116,13 @@ struct GreedySampler : Sampler
 struct EpsilonGreedySampler : Sampler
 {
   TYPEINFO("sampler/epsilon_greedy", "Maximum search with an epsilon chance of randomness")
+  void request(ConfigurationRequest *config) override;
+  void configure(Configuration &config) override;
+};
+
+struct SoftmaxSampler : Sampler
+{
+  TYPEINFO("sampler/softmax", "Softmax (Boltzmann) sampler")
   void request(ConfigurationRequest *config) override;
   void configure(Configuration &config) override;
 };

@@ -38,6 +38,7 @@ enum { GRLCU_TRACE_NONE = 0, GRLCU_TRACE_REPLACING = 1, GRLCU_TRACE_ACCUMULATING
 /* predictor: predictor/critic/sarsa (sarsa.cpp:98-124) | predictor/ac/action + predictor/critic/td (ac.cpp, td.cpp) |
  * predictor/critic/q (advantage.cpp:71-110) | predictor/critic/expected_sarsa (sarsa.cpp:167-194) */
 enum { GRLCU_ALGO_SARSA = 0, GRLCU_ALGO_AC = 1, GRLCU_ALGO_Q = 2, GRLCU_ALGO_EXPECTED_SARSA = 3 };
+enum { GRLCU_SAMPLER_EPSILON_GREEDY = 0, GRLCU_SAMPLER_SOFTMAX = 1 };
 enum { GRLCU_OK = 0, GRLCU_ERR_ARG = 1, GRLCU_ERR_CUDA = 2, GRLCU_ERR_UNSUPPORTED = 3,
        GRLCU_ERR_NOMEM = 4 };
 enum { GRLCU_RESET_TABLES = 1, GRLCU_RESET_AGENTS = 2, GRLCU_RESET_STATS = 4 };
@@ -73,7 +74,10 @@ typedef struct grlcu_config
                                  sarsa.cpp:145): < 0 sampler/greedy, else sampler/epsilon_greedy's epsilon */
   int32_t end_stop_penalty;   /* task/cart_pole/swingup end_stop_penalty (cart_pole.cpp:177,196; the reference's default
                                  is 1, cfg/cart_pole/ac_tc.yaml uses 0); ignored by the other tasks */
-  int32_t reserved_;          /* padding, must be 0 */
+  int32_t sampler;            /* the learning policy's sampler: GRLCU_SAMPLER_EPSILON_GREEDY (greedy.cpp:144-218, uses
+                                 `epsilon`) | GRLCU_SAMPLER_SOFTMAX (softmax.cpp:48-101, uses `softmax_tau`); test
+                                 episodes always use sampler/greedy */
+  double  softmax_tau;        /* sampler/softmax tau: temperature of the Boltzmann distribution (softmax.cpp:34) */
 } grlcu_config;
 
 typedef struct grlcu_ctx grlcu_ctx;

@@ -58,6 +58,7 @@ enum { ORC_DYN_PENDULUM = 0, ORC_DYN_CART_POLE = 1, ORC_DYN_CART_DOUBLE_POLE = 2
 enum { ORC_TRACE_NONE = 0, ORC_TRACE_REPLACING = 1, ORC_TRACE_ACCUMULATING = 2 };
 enum { ORC_ALGO_SARSA = 0, ORC_ALGO_AC = 1, ORC_ALGO_Q = 2, ORC_ALGO_EXPECTED_SARSA = 3 };
 enum { ORC_RNG_PHILOX = 0, ORC_RNG_GLIBC = 1 };
+enum { ORC_SAMPLER_EPSILON_GREEDY = 0, ORC_SAMPLER_SOFTMAX = 1 };
 
 /* Same field order as grlcu_config (include/grlcu.h) so one ctypes Structure
  * serves both; the two libraries share no code. */
@@ -91,7 +92,8 @@ typedef struct orc_config
   /* predictor/critic/expected_sarsa: the target policy's sampler; < 0: sampler/greedy, else epsilon-greedy */
   double  target_epsilon;
   int32_t end_stop_penalty;   /* task/cart_pole/swingup: end_stop_penalty (cart_pole.h:75 default 1) */
-  int32_t reserved_;
+  int32_t sampler;            /* ORC_SAMPLER_*: sampler/epsilon_greedy | sampler/softmax (learning policy) */
+  double  softmax_tau;        /* sampler/softmax: tau */
 } orc_config;
 
 /* Everything observable about one agent-step (one iteration of

@@ -226,8 +226,48 @@ static uint32_t draw_int(const orc_agent *a, uint32_t philox_word)
   return philox_word >> 1;
 }
 
-/* EpsilonGreedySampler::sample (greedy.cpp:151-218, epsilon_.size()==1, decay_ = 1)
- * when test == 0, GreedySampler::sample (greedy.cpp:63-86) when test != 0. */
+/* SoftmaxSampler::distribution (softmax.cpp:61-101) followed by grl::sample(dist, 1.) (utils.h:227-240) on the
+ * uniform draw u */
+static int softmax_pick(const double *values, int n, double tau, double u)
+{
+  double v[ORC_MAX_ACTIONS], dist[ORC_MAX_ACTIONS];
+  const double threshold = -100;
+  double max_power = -DBL_MAX;
+  for (int ii = 0; ii < n; ++ii)
+  {
+    v[ii] = 0;
+    double p = values[ii] / tau;
+    max_power = (max_power < p) ? p : max_power;
+  }
+  double min_power = max_power + threshold;
+  double center = (max_power + min_power) / 2.0;
+  double sum = 0;
+  for (int ii = 0; ii < n; ++ii)
+  {
+    double p = values[ii] / tau;
+    if (p > min_power)
+    {
+      p -= center;
+      v[ii] = exp(p);
+      sum += v[ii];
+      dist[ii] = 1;
+    }
+    else
+      dist[ii] = 0;
+  }
+  for (int ii = 0; ii < n; ++ii) dist[ii] *= v[ii] / sum;
+  double r = u * 1.;
+  sum = 0;
+  for (int ii = 0; ii < n; ++ii)
+  {
+    sum += dist[ii];
+    if (r < sum) return ii;
+  }
+  return n - 1;
+}
+
+/* EpsilonGreedySampler::sample (greedy.cpp:151-218, epsilon_.size()==1, decay_ = 1) or SoftmaxSampler::sample
+ * (softmax.cpp:48-59) when test == 0, GreedySampler::sample (greedy.cpp:63-86) when test != 0. */
 static int sample(orc_agent *a, const double *q, int test, act_draws *d)
 {
   const int A = a->c.n_actions;
@@ -240,6 +280,17 @@ static int sample(orc_agent *a, const double *q, int test, act_draws *d)
   {
     if (test) philox_for(a, STREAM_TEST_ACT, a->test_act_counter++, w);
     else      philox_for(a, STREAM_ACT, a->act_counter++, w);
+  }
+
+  if (!test && a->c.sampler == ORC_SAMPLER_SOFTMAX)
+  {
+    /* one uniform from RandGen (the thread's generator, not a sampler-owned Rand: utils.h:229) */
+    double r;
+    if (a->c.rng == ORC_RNG_GLIBC) drand48_r(&a->randgen, &r);
+    else r = u53(w[0], w[1]);
+    d->u = r;
+    d->explored = 1;                           /* *at = atExploratory, always (softmax.cpp:54-55) */
+    return softmax_pick(q, A, a->c.softmax_tau, r);
   }
 
   if (!test)
@@ -411,7 +462,8 @@ orc_agent *orc_create(const orc_config *c, uint64_t agent_id)
     else
     {
       table_init(a, a->table, STREAM_TABLE);
-      srand48_r(lrand48(), &a->sampler);
+      if (c->sampler != ORC_SAMPLER_SOFTMAX)            /* sampler/softmax owns no Rand (samplers/softmax.h) */
+        srand48_r(lrand48(), &a->sampler);
       srand48_r(lrand48(), &a->test_sampler);
     }
   }

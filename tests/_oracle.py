@@ -16,6 +16,7 @@ INVALID = 0xFFFFFFFF
 DYN_PENDULUM, DYN_CART_POLE, DYN_CART_DOUBLE_POLE = 0, 1, 2
 TRACE_NONE, TRACE_REPLACING, TRACE_ACCUMULATING = 0, 1, 2
 ALGO_SARSA, ALGO_AC, ALGO_Q, ALGO_EXPECTED_SARSA = 0, 1, 2, 3
+SAMPLER_EPSILON_GREEDY, SAMPLER_SOFTMAX = 0, 1
 RNG_PHILOX, RNG_GLIBC = 0, 1
 
 
@@ -35,7 +36,7 @@ class Config(C.Structure):
         ("action_min", C.c_double), ("action_max", C.c_double),
         ("actor_resolution", C.c_double * MAX_DIMS), ("actor_wrapping", C.c_double * MAX_DIMS),
         ("target_epsilon", C.c_double),
-        ("end_stop_penalty", C.c_int32), ("reserved_", C.c_int32),
+        ("end_stop_penalty", C.c_int32), ("sampler", C.c_int32), ("softmax_tau", C.c_double),
     ]
 
     def __init__(self, *a, **kw):

@@ -58,6 +58,8 @@ def _run(G, mk, mode, n, launches, sweep=False, coop_cohort=None, coop_lanes=Non
     # actor-critic (BASELINE configs[3]): the critic's trace goes through the cache, the actor table does not
     dict(which="ac", n=64, memory=131072, launches=[90, 1, 310], test_interval=3),
     dict(which="ac", n=32, memory=509, launches=[350], test_interval=-1, actor_alpha=0.5, sigma=15.0),
+    # sampler/softmax as the learning policy's sampler
+    dict(which="pendulum", n=64, memory=65536, launches=[140, 160], test_interval=3, sampler=1, softmax_tau=0.5),
     # SARSA on the cart-double-pole (cfg/cart_double_pole/sarsa.yaml): 51-entry ring
     dict(which="cart_double_pole", n=64, memory=131072, launches=[150, 1, 250], test_interval=3, epsilon=0.1),
     dict(which="cart_double_pole", n=32, memory=1021, launches=[300], test_interval=-1),

@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 def _full(G, mk, n, memory, steps, slices, hyper=None, **kw):
     import torch
     free, _ = torch.cuda.mem_get_info(0)
-    tables = 2 if mk is G.cart_double_pole_ac_config else 1
+    tables = 2 if mk(memory=16).algo == G.capi.ALGO_AC else 1
     need = n * memory * 8 * tables * 1.08 + (4 << 30)
     if free < need:
         pytest.skip("needs %.0f GiB of free HBM" % (need / 2**30))
@@ -71,6 +71,14 @@ def test_cart_pole_32768_agents_x_262144_entries():
 def test_actor_critic_65536_agents_x_2_x_131072_entries():
     import grl_b200 as G
     _full(G, G.cart_double_pole_ac_config, 65536, 131072, [180], [0, 65536 - 64], test_interval=10)
+
+
+def test_sibling_configurations_at_full_size():
+    """The reference's other tile-coded configs on these tasks at the bench sizes: actor-critic on the cart-pole
+    (2 x 64 GiB of tables: indices beyond 2^33 entries) and SARSA on the cart-double-pole (51-entry trace ring)."""
+    import grl_b200 as G
+    _full(G, G.cart_pole_ac_config, 32768, 262144, [230], [0, 32768 - 64], randomization=1.0, test_interval=4)
+    _full(G, G.cart_double_pole_config, 65536, 131072, [160, 60], [0, 40000 - 40000 % 64, 65536 - 64], test_interval=-1)
 
 
 def test_sweep_131072_agents_x_32768_entries():

@@ -203,6 +203,18 @@ def test_replay_q_learning_and_expected_sarsa(G, orc):
             randomization=1.0, test_interval=-1, algo=O.ALGO_EXPECTED_SARSA, target_epsilon=0.3)
 
 
+def test_replay_softmax_sampler(G, orc):
+    """sampler/softmax as the learning policy's sampler: own action choices from the fed uniform are
+    bit-exact against the oracle (device exp vs glibc exp can only matter within an ulp of a bucket boundary), test
+    episodes stay greedy; Q-learning on top of it as well."""
+    _replay(G, G.pendulum_config, O.pendulum_config, n=48, steps=330, mem=65536,
+            randomization=1.0, test_interval=2, sampler=O.SAMPLER_SOFTMAX, softmax_tau=0.5)
+    _replay(G, G.cart_pole_config, O.cart_pole_config, n=32, steps=300, mem=4099,
+            randomization=1.0, test_interval=-1, sampler=O.SAMPLER_SOFTMAX, softmax_tau=20.0, algo=O.ALGO_Q)
+    with pytest.raises(G.GrlcuError):
+        G.Batch(G.pendulum_config(memory=1024, sampler=O.SAMPLER_SOFTMAX, softmax_tau=0.0), 1)
+
+
 def test_replay_accumulating_and_no_trace(G, orc):
     _replay(G, G.pendulum_config, O.pendulum_config, n=16, steps=150, mem=8192,
             randomization=1.0, test_interval=-1, trace=2)

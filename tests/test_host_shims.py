@@ -192,6 +192,24 @@ def test_reference_q_learning_yaml_and_expected_sarsa(grld, tmp_path):
     assert (json.loads(out)["algo"], json.loads(out)["target_epsilon"]) == (3, 0.05)
 
 
+def test_softmax_sampler_from_yaml(grld, tmp_path):
+    """sampler/softmax (softmax.cpp:32-35: tau in [1e-6, 100]) in place of sampler/epsilon_greedy."""
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
+    old = "        type: sampler/epsilon_greedy\n        epsilon: 0.05"
+    assert old in base
+    p = tmp_path / "softmax.yaml"
+    p.write_text(base.replace(old, "        type: sampler/softmax\n        tau: 0.25"))
+    rc, out, err = check(grld, str(p))
+    assert rc == 0, err
+    got = json.loads(out)
+    assert (got["sampler"], got["softmax_tau"], got["algo"]) == (1, 0.25, 0)
+    p.write_text(base.replace(old, "        type: sampler/softmax\n        tau: 0"))
+    rc, out, err = check(grld, str(p))
+    assert rc == 1 and "tau" in err
+    rc, out, err = check(grld, os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml"))
+    assert json.loads(out)["sampler"] == 0
+
+
 def test_error_behaviour(grld, tmp_path):
     base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
     cases = {

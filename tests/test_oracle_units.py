@@ -160,6 +160,40 @@ def test_sibling_actor_critic_configs_in_the_oracle(orc):
     assert 2 in terms and min(lens) < 200 and rmin < -9000
 
 
+def test_softmax_sampler_in_the_oracle(orc):
+    """sampler/softmax (softmax.cpp:48-101): the learning policy draws one uniform and picks from the Boltzmann
+    distribution of Q/tau; empirical frequencies match an independent numpy restatement, a tiny tau is greedy, test
+    episodes stay greedy (sampler/greedy) and the agent still learns."""
+    import ctypes as C
+    import numpy as np
+    import _oracle as O
+    rec = O.Record()
+    for tau in (0.5, 1e-6):
+        c = O.pendulum_config(memory=1 << 16, test_interval=1, randomization=1.0, sampler=O.SAMPLER_SOFTMAX, softmax_tau=tau)
+        a = orc.orc_create(C.byref(c), 4)
+        try:
+            n = hit = 0
+            for t in range(3000):
+                orc.orc_step(a, C.byref(rec))
+                if rec.terminal == 2 or rec.action_index < 0:
+                    continue
+                q = np.array(rec.q[:3])
+                if rec.test:
+                    assert rec.action_index == int(np.argmax(q)) or (q == q.max()).sum() > 1
+                    continue
+                # independent restatement: softmax of q / tau, cumulative pick on u
+                z = q / tau
+                pr = np.exp(z - z.max()); pr /= pr.sum()
+                pick = int(np.searchsorted(np.cumsum(pr), rec.u, side="right"))
+                n += 1
+                hit += min(pick, 2) == rec.action_index
+                if tau < 1e-3 and (q.max() - np.sort(q)[-2]) / tau > 50:
+                    assert rec.action_index == int(np.argmax(q))
+            assert n > 1000 and hit >= n - 2          # (u within an ulp of a boundary may differ)
+        finally:
+            orc.orc_destroy(a)
+
+
 def test_q_learning_and_expected_sarsa_targets(orc):
     """predictor/critic/q (advantage.cpp:84-90) and predictor/critic/expected_sarsa (sarsa.cpp:172-173 ->
     q.cpp:56-68, greedy.cpp:88-98,220-238): the oracle's targets against a direct restatement on its own
