@@ -38,6 +38,29 @@ def test_config_struct_matches_header_layout():
     assert Config.seed.offset == Config.init_max.offset + 8
 
 
+def test_config_struct_matches_the_c_compiler(tmp_path):
+    """sizeof / offsetof of every grlcu_config and orc_config field as gcc lays them out, against the ctypes mirrors
+    (a field added to one header and not to a mirror shifts everything after it)."""
+    import subprocess
+    from grl_b200.capi import Config
+    import _oracle
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    names = [f[0] for f in Config._fields_]
+    cname = lambda n: "lambda" if n == "lambda_" else n
+    for header, struct, mirror in (("include/grlcu.h", "grlcu_config", Config), ("oracle/grl_oracle.h", "orc_config", _oracle.Config)):
+        assert [f[0] for f in mirror._fields_] == names
+        src = tmp_path / (struct + ".c")
+        body = "".join('  printf("%%s %%zu\\n", "%s", offsetof(%s, %s));\n' % (n, struct, cname(n)) for n in names)
+        src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "%s"\nint main(void)\n{\n  printf("sizeof %%zu\\n", sizeof(%s));\n%s  return 0;\n}\n'
+                       % (os.path.join(root, header), struct, body))
+        exe = tmp_path / struct
+        subprocess.run(["gcc", "-o", str(exe), str(src)], check=True)
+        out = dict(l.split() for l in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+        assert int(out["sizeof"]) == C.sizeof(mirror), struct
+        for n in names:
+            assert int(out[n]) == getattr(mirror, n).offset, (struct, n)
+
+
 def test_no_cpu_fallback_without_gpu(lib):
     import torch
     if torch.cuda.is_available():
