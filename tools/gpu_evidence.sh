@@ -5,9 +5,10 @@ TAG=${TAG:-v8}
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -q -rs > gpurun_out/pytest_gpu_${TAG}.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu_${TAG}.log
 tail -2 gpurun_out/pytest_gpu_${TAG}.log
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke_${TAG}.log 2>&1; echo "smoke exit $?"
 python bench.py > gpurun_out/bench_${TAG}.json 2> gpurun_out/bench_${TAG}.err; echo "bench exit $?"
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref_${TAG}.json 2> gpurun_out/bench_ref_${TAG}.err; echo "ref exit $?"
-for w in cart_pole cart_double_pole_ac sweep; do
+for w in cart_pole cart_double_pole_ac sweep cart_double_pole pendulum_ac cart_pole_ac; do
   python bench.py --workload $w --no-cpu > gpurun_out/bench_${w}_${TAG}.json 2> gpurun_out/bench_${w}_${TAG}.err; echo "$w exit $?"
 done
 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 &&
