@@ -14,9 +14,18 @@ done
 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_${TAG}.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launches.log 2>&1
-for w in pendulum cart_pole cart_double_pole_ac; do
+for w in ${NCU_WORKLOADS:-pendulum cart_pole cart_double_pole_ac}; do
   python bench.py --workload $w --steps 2 --warmup 3 --no-cpu > gpurun_out/plain_$w.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:k_run -s 3 -c 1 -o gpurun_out/prof_${TAG}_$w \
       python bench.py --workload $w --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full_$w.log 2>&1
+  # summarise on the box (gpurun_out/ is capped at 64 MiB and one report is ~27 MB): counters + per-source-line attribution
+  k=k_run; [ $w = cart_double_pole_ac ] && k=k_run_ac
+  { echo "# ncu --set full --clock-control none --import-source on -k regex:k_run -s 3 -c 1 python bench.py --workload $w --steps 2 --warmup 3 --no-cpu"
+    echo "# (tools/gpu_evidence.sh, TAG=$TAG; one launch = 100 agent-steps per agent; times under ncu are not bench values)"
+    python tools/ncu_summary.py gpurun_out/prof_${TAG}_$w.ncu-rep
+    echo; echo "# per source line (tools/ncu_by_line.py)"
+    python tools/ncu_by_line.py gpurun_out/prof_${TAG}_$w.ncu-rep grl_b200/csrc/libgrlcu.so $k 25 2>&1
+  } > gpurun_out/ncu_${TAG}_$w.txt
+  [ "$KEEP_REP" = "$w" ] || rm -f gpurun_out/prof_${TAG}_$w.ncu-rep
 done
 ls -la gpurun_out
