@@ -84,6 +84,9 @@ int main()
     run<38, 10, 14, 144>("compulsory fetches only", tbl, tmask, stream, smask, sink);
     run<64, 16, 14, 0>("today without the dense stream", tbl, tmask, stream, smask, sink);
     run<48, 10, 14, 0>("stable slots without the dense stream", tbl, tmask, stream, smask, sink);
+    // the actor-critic agent: 4 x 16 reads, 16 actor stores + 16 sentinels on words just read, ~12 pops, V = 64
+    run<64, 32, 12, 64>("actor-critic today (k_run_ac)", tbl, tmask, stream, smask, sink);
+    run<48, 26, 12, 64>("actor-critic, critic's p registered at act time + stable slots", tbl, tmask, stream, smask, sink);
   }
   return 0;
 }
