@@ -84,6 +84,10 @@ int main()
     run<38, 10, 14, 144>("compulsory fetches only", tbl, tmask, stream, smask, sink);
     run<64, 16, 14, 0>("today without the dense stream", tbl, tmask, stream, smask, sink);
     run<48, 10, 14, 0>("stable slots without the dense stream", tbl, tmask, stream, smask, sink);
+    // marginal costs of the three kinds of operation
+    run<64, 0, 14, 144>("today without the 16 L2-hit stores", tbl, tmask, stream, smask, sink);
+    run<64, 16, 0, 144>("today without the 14 pops", tbl, tmask, stream, smask, sink);
+    run<48, 16, 14, 144>("today without 16 of the reads", tbl, tmask, stream, smask, sink);
     // the actor-critic agent: 4 x 16 reads, 16 actor stores + 16 sentinels on words just read, ~12 pops, V = 64
     run<64, 32, 12, 64>("actor-critic today (k_run_ac)", tbl, tmask, stream, smask, sink);
     run<48, 26, 12, 64>("actor-critic, critic's p registered at act time + stable slots", tbl, tmask, stream, smask, sink);
