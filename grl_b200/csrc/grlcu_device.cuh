@@ -145,7 +145,9 @@ template <> struct Dyn<1>
     const double g = 9.8, mass_cart = 1.0, mass_pole = 0.1, length = 0.5;
     const double total_mass = mass_cart + mass_pole;
     const double pole_mass_length = mass_pole * length;
-    double theta = x[1], dtheta = x[3];
+    // cart_pole.cpp:66: theta = state[end_stop_], dtheta = state[3-2*end_stop_]; with end_stop_ = 1 both are state[1]
+    // (the reference uses the pole angle where the angular velocity belongs; reproduced as is)
+    double theta = x[1], dtheta = x[3 - 2 * 1];
     double costheta = cos(theta), sintheta = sin(theta);
     double temp = (u + pole_mass_length * dtheta * dtheta * sintheta) / total_mass;
     double thetaacc = (g * sintheta - costheta * temp) /

@@ -156,6 +156,9 @@ void orc_rk4(int dynamics, double tau, int steps, const double *x, double u, dou
 int  orc_state_dims(int dynamics);
 void orc_observe(const orc_config *c, const double *x, double *obs, int32_t *terminal);
 double orc_evaluate(const orc_config *c, const double *x, double action, const double *next);
+void orc_task_start(const orc_config *c, int test, double r, double *state);
+/* pin against tests/template/cart_pole_balancing-pid-0.txt (grl_oracle_pin.c) */
+void orc_pin_cart_pole_pid(long seed, const double *p_gains, double timeout, int trials, double *rewards, int32_t *steps);
 /* one environment step: actuate + rk4 + observe + evaluate (modeled.cpp:160-213) */
 void orc_env_step(const orc_config *c, const double *x, double action,
                   double *next, double *obs, double *reward, int32_t *terminal);

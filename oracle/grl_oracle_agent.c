@@ -343,13 +343,7 @@ static double task_start(orc_agent *a, int test, double *state)
     r = u53(w[0], w[1]);
   }
   a->episode_counter++;
-  for (int i = 0; i < a->S; ++i) state[i] = 0;
-  if (c->dynamics == ORC_DYN_PENDULUM)
-    state[0] = M_PI + c->randomization * (test == 0) * r * 2 * M_PI;
-  else if (c->dynamics == ORC_DYN_CART_POLE)
-    state[1] = M_PI + (int)c->randomization * ((r * 0.1) - 0.05);   /* int randomization_ (cart_pole.h:73) */
-  else
-    state[1] = (r * 0.01) - 0.005;
+  orc_task_start(c, test, r, state);
   return r;
 }
 

@@ -127,7 +127,11 @@ static void eom_cart_pole(const double *state, double u, double *xd)
   const double total_mass_ = mass_cart_ + mass_pole_;
   const double pole_mass_length_ = mass_pole_ * length_;
   double acc, thetaacc, costheta, sintheta, temp;
-  double theta = state[1], dtheta = state[3];
+  /* cart_pole.cpp:66: `theta = state[end_stop_], dtheta = state[3-2*end_stop_]`.  With end_stop_ = 1 (the default and
+   * the only form the 5-state tasks accept) BOTH are state[1]: the reference feeds the pole ANGLE where the angular
+   * velocity belongs.  Reproduced as is (found by compiling the reference's cart_pole.cpp, tests/test_oracle_vs_ref.py). */
+  const int end_stop_ = 1;
+  double theta = state[end_stop_], dtheta = state[3 - 2 * end_stop_];
 
   costheta = cos(theta);
   sintheta = sin(theta);
@@ -305,6 +309,20 @@ void orc_observe(const orc_config *c, const double *x, double *obs, int32_t *ter
     else if (x[6] > c->timeout) *terminal = 1;
     else *terminal = 0;
   }
+}
+
+/* Task::start with the uniform draw r (always consumed): pendulum.cpp:97-103, cart_pole.cpp:152-160,
+ * cart_double_pole.cpp:250-262 */
+void orc_task_start(const orc_config *c, int test, double r, double *state)
+{
+  const int S = orc_state_dims(c->dynamics);
+  for (int i = 0; i < S; ++i) state[i] = 0;
+  if (c->dynamics == ORC_DYN_PENDULUM)
+    state[0] = M_PI + c->randomization * (test == 0) * r * 2 * M_PI;
+  else if (c->dynamics == ORC_DYN_CART_POLE)
+    state[1] = M_PI + (int)c->randomization * ((r * 0.1) - 0.05);   /* int randomization_ (cart_pole.h:73) */
+  else
+    state[1] = (r * 0.01) - 0.005;
 }
 
 /* cart_pole.cpp:229-235 */
