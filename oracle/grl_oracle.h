@@ -183,9 +183,12 @@ double *orc_actor_table(orc_agent *a);      /* memory doubles (AC only) */
 int orc_step(orc_agent *a, orc_record *rec);
 /* run n learning steps without recording (CPU baseline timing) */
 uint64_t orc_run(orc_agent *a, uint64_t n_steps);
+/* run n agent-steps, test-episode steps included (the count grlcu_run takes) */
+void orc_run_total(orc_agent *a, uint64_t n_steps);
 /* statistics */
 void orc_stats(const orc_agent *a, uint64_t *steps, uint64_t *episodes, uint64_t *swept,
                double *last_return, double *last_test_return);
+double orc_pending_action(const orc_agent *a);
 /* current state (for replay feeding) */
 void orc_get_state(const orc_agent *a, double *state, double *prev_obs, double *prev_action,
                    int32_t *in_episode);

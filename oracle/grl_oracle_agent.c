@@ -502,6 +502,9 @@ void orc_get_state(const orc_agent *a, double *state, double *prev_obs, double *
   if (in_episode) *in_episode = a->in_episode;
 }
 
+/* the action that the next environment step will apply */
+double orc_pending_action(const orc_agent *a) { return a->action; }
+
 static int ac_step(orc_agent *a, orc_record *rec);
 
 /* ---- one agent-step (online_learning.cpp:154-222) ------------------------ */
@@ -607,6 +610,12 @@ uint64_t orc_run(orc_agent *a, uint64_t n_steps)
   while (n < n_steps)
     n += (uint64_t)orc_step(a, NULL);
   return n;
+}
+
+/* n agent-steps counting test-episode steps as well (what grlcu_run counts) */
+void orc_run_total(orc_agent *a, uint64_t n_steps)
+{
+  for (uint64_t n = 0; n < n_steps; ++n) orc_step(a, NULL);
 }
 
 /* ---- actor-critic (cfg 4: cfg/cart_double_pole/ac.yaml) ----------------------------------

@@ -156,6 +156,13 @@ def test_replay_pendulum(G, orc):
             randomization=1.0, test_interval=2)
 
 
+def test_replay_pendulum_shipped_memory(G, orc):
+    """The reference's shipped table size (cfg/pendulum/sarsa_tc.yaml:32, memory 8,388,608 = 64 MiB per agent) at a
+    reduced agent count, for index parity with the shipped configuration."""
+    _replay(G, G.pendulum_config, O.pendulum_config, n=8, steps=300, mem=8388608,
+            randomization=1.0, test_interval=2)
+
+
 def test_replay_pendulum_small_table_collisions(G, orc):
     # memory 257: many intra-projection and cross-tiling collisions (duplicate indices)
     _replay(G, G.pendulum_config, O.pendulum_config, n=32, steps=330, mem=257,
