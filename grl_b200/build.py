@@ -6,7 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libgrlcu.so")
 SOURCES = ["grlcu.cu"]
-HEADERS = ["grlcu_device.cuh", "grlcu_agent.cuh", "grlcu_cached.cuh", "grlcu_kernels.cuh", "grlcu_ac.cuh", "grlcu_coop.cuh", os.path.join("..", "..", "include", "grlcu.h")]
+HEADERS = ["grlcu_device.cuh", "grlcu_agent.cuh", "grlcu_cached.cuh", "grlcu_kernels.cuh", "grlcu_ac.cuh", "grlcu_layout.h", os.path.join("..", "..", "include", "grlcu.h")]
 
 # -fmad=false: the reference binary has no FMA contraction (CMakeLists.txt:19), see DESIGN.md.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-fmad=false", "-lineinfo",

@@ -3,7 +3,7 @@
 #include "../../include/grlcu.h"
 #include "grlcu_kernels.cuh"
 #include "grlcu_ac.cuh"
-#include "grlcu_coop.cuh"
+#include "grlcu_layout.h"
 
 #include <cuda_runtime.h>
 #include <cfloat>
@@ -47,12 +47,15 @@ struct grlcu_ctx
   double *d_alpha, *d_lambda, *d_epsilon, *d_start;
   int64_t launches;
   int sm_count;
-  CoopArrays coop;            // agent-major cache of one cohort (grlcu_coop.cuh), allocated on first use
-  int coop_cohort, coop_lanes;
+  bool geo;                   // tile-major physical table layout in use (struct Geo)
+  uint32_t inbox_words, shared_words;
+  double *d_stage;            // [memory] staging row for logical <-> physical table copies
   bool cache_live;            // the trace value cache of the fused kernel is live (tables hold directory sentinels)
   // run-kernel timing (events recorded around every k_run launch)
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending;
   std::vector<cudaEvent_t> ev_pool;
+  double ev_ms; int64_t ev_n;  // time / count of the launches already folded out of ev_pending
+  bool traces_live;           // agents have stepped since the last GRLCU_RESET_AGENTS (traces may be non-empty)
   int block;
 };
 
@@ -226,14 +229,11 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   c->OBS = cfg->obs_dims;
   c->d_alpha = c->d_lambda = c->d_epsilon = c->d_start = nullptr;
   c->launches = 0;
+  c->ev_ms = 0; c->ev_n = 0; c->traces_live = false;
+  c->geo = false; c->inbox_words = c->shared_words = 0; c->d_stage = nullptr;
   c->cache_live = false;
   c->block = 64;
   c->sm_count = 148;
-  memset(&c->coop, 0, sizeof(c->coop));
-  c->coop_cohort = 4096;
-  if (const char *b = getenv("GRLCU_COOP_COHORT")) { int v = atoi(b); if (v >= 4) c->coop_cohort = v; }
-  c->coop_lanes = 4;
-  if (const char *b = getenv("GRLCU_COOP_LANES")) { int v = atoi(b); if (v == 2 || v == 4 || v == 8 || v == 16) c->coop_lanes = v; }
   cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
   if (const char *b = getenv("GRLCU_BLOCK")) { int v = atoi(b); if (v >= 32 && v <= kMaxBlock && v % 32 == 0) c->block = v; }
 
@@ -297,6 +297,20 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     return fail(GRLCU_ERR_UNSUPPORTED, "gamma*lambda = %g needs an unbounded or too long trace", cfg->gamma * cfg->lambda);
   }
 
+  // physical table layout: tile-major where the task's tiles fit the table (GRLCU_LAYOUT=0: the reference's raw
+  // hash order, kept for A/B runs and as the other side of tests/test_gpu_cached.py)
+  p.tstride = (uint32_t)cfg->memory;
+  grlcu_host::Layout lay;
+  if (!(getenv("GRLCU_LAYOUT") && atoi(getenv("GRLCU_LAYOUT")) == 0))
+    lay = grlcu_host::build_layout(*cfg, p.proj.scaling, p.proj.wrap);
+  if (lay.enabled)
+  {
+    c->geo = true; c->inbox_words = lay.inbox_words; c->shared_words = lay.shared_words;
+    p.tstride = lay.tstride;
+    p.geo.enabled = 1;
+    for (int i = 0; i < cfg->obs_dims; ++i) { p.geo.kn[i] = lay.kn[i]; p.geo.koff[i] = lay.koff[i]; p.geo.wrapped[i] = lay.wrapped[i]; }
+  }
+
   const size_t n = (size_t)n_agents, T = (size_t)cfg->tilings;
   if (n * T * (size_t)p.trace_cap >= (1ull << 31))
   {
@@ -304,7 +318,26 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     return fail(GRLCU_ERR_UNSUPPORTED, "n_agents * tilings * trace capacity (%d) must stay below 2^31 per context", p.trace_cap);
   }
   int r = 0;
-  if (!r) r = dalloc(c, &p.table, n * (size_t)cfg->memory);
+  if (!r && lay.enabled)
+  {
+    auto up = [&](const uint32_t **dst, const std::vector<uint32_t> &v) -> int
+    {
+      uint32_t *d = nullptr;
+      if (int e = dalloc(c, &d, v.size())) return e;
+      if (cudaMemcpy(d, v.data(), v.size() * sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess)
+        return fail(GRLCU_ERR_CUDA, "uploading the table layout failed");
+      *dst = d;
+      return 0;
+    };
+    if (!r) r = up(&p.geo.perm, lay.perm);
+    if (!r) r = up(&p.geo.iperm, lay.iperm);
+    if (!r) r = up(&p.geo.slotmap, lay.slotmap);
+    if (!r) r = up(&p.geo.gflags, lay.gflags);
+    if (!r) r = dalloc(c, &p.geo.mismatch, 1);
+    if (!r && cudaMemset(p.geo.mismatch, 0, sizeof(int32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
+    if (!r) r = dalloc(c, &c->d_stage, (size_t)cfg->memory);
+  }
+  if (!r) r = dalloc(c, &p.table, n * (size_t)p.tstride);
   memset(&c->ac, 0, sizeof(c->ac));
   if (!r && is_ac)
   {
@@ -390,8 +423,12 @@ static int launch_reset(grlcu_ctx *c, int what)
   if (what & GRLCU_RESET_TABLES)
   {
     const int64_t work = ((int64_t)c->cfg.memory + 1) / 2 * p.n;
-    k_table_init<<<grid_for(work, 256, 148 * 32), 256, 0, c->stream>>>(
-        p.table, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_TABLE);
+    if (c->geo)
+      k_table_init_phys<<<grid_for((int64_t)p.tstride * p.n, 256, 148 * 32), 256, 0, c->stream>>>(
+          p.table, p.n, p.tstride, p.geo.iperm, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_TABLE);
+    else
+      k_table_init<<<grid_for(work, 256, 148 * 32), 256, 0, c->stream>>>(
+          p.table, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_TABLE);
     c->launches++;
     if (c->ac.actor)
     {
@@ -400,7 +437,7 @@ static int launch_reset(grlcu_ctx *c, int what)
       c->launches++;
     }
   }
-  if (what & GRLCU_RESET_AGENTS) { k_reset_agents<<<grd, blk, 0, c->stream>>>(p); c->launches++; }
+  if (what & GRLCU_RESET_AGENTS) { k_reset_agents<<<grd, blk, 0, c->stream>>>(p); c->launches++; c->traces_live = false; }
   if (what & GRLCU_RESET_STATS) { k_reset_stats<<<grd, blk, 0, c->stream>>>(p); c->launches++; }
   CU(cudaGetLastError());
   return 0;
@@ -442,6 +479,11 @@ extern "C" int grlcu_set_hyper(grlcu_ctx *c, const double *alpha, const double *
   CU(cudaSetDevice(c->device));
   if (lambda)
   {
+    // the trace ring stores no per-entry decay: the sweep and the pops would apply the NEW gamma*lambda to entries
+    // pushed under the old one (the reference divides by front().decay, trace.h:229-233)
+    if (c->traces_live)
+      return fail(GRLCU_ERR_ARG, "grlcu_set_hyper: per-agent lambda can only change while every trace is empty "
+                  "(right after grlcu_create or grlcu_reset(GRLCU_RESET_AGENTS))");
     double mx = 0;
     for (int i = 0; i < c->p.n; ++i) mx = lambda[i] > mx ? lambda[i] : mx;
     int cap = trace_capacity_for(c->cfg.gamma * mx, c->cfg.trace);
@@ -583,26 +625,28 @@ extern "C" int grlcu_task_start(grlcu_ctx *c, int64_t n, int32_t test, const dou
 // one thread: the reference's sequential order is the contract (linear.cpp:147-151, 207-215)
 // [lo, hi]: the representation's output_min / output_max (+-DBL_MAX when unset, linear.cpp:88-98); the read is
 // clamped to it (linear.cpp:179-180) and, with limit = 1, so is every updated weight (linear.cpp:207-211)
-__global__ void k_table_read(const double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
+// perm: logical index -> physical slot (struct Geo), or NULL
+__global__ void k_table_read(const double *tbl, const uint32_t *perm, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
                              double *value, int *bad)
 {
   double r = 0;
   for (int i = 0; i < n_idx; ++i)
   {
     if (idx[i] >= memory) { *bad = 1; return; }
-    r += tbl[idx[i]];
+    r += tbl[perm ? perm[idx[i]] : idx[i]];
   }
   *value = fmin(fmax(r / n_idx, lo), hi);
 }
 
-__global__ void k_table_update(double *tbl, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
+__global__ void k_table_update(double *tbl, const uint32_t *perm, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
                                double delta, int *bad)
 {
   for (int i = 0; i < n_idx; ++i)
   {
     if (idx[i] == ~0ull) continue;                    // IndexProjection::invalid_index()
     if (idx[i] >= memory) { *bad = 1; return; }
-    tbl[idx[i]] = fmin(fmax(tbl[idx[i]] + delta, lo), hi);
+    const uint64_t s = perm ? perm[idx[i]] : idx[i];
+    tbl[s] = fmin(fmax(tbl[s] + delta, lo), hi);
   }
 }
 
@@ -619,10 +663,11 @@ static int table_view(grlcu_ctx *c, bool actor, int32_t agent, int32_t n_idx, co
   if (!d_i || !d_v || !d_bad) return fail(GRLCU_ERR_NOMEM, "grlcu_read/update: out of device memory");
   CU(cudaMemcpyAsync(d_i, idx, sizeof(uint64_t) * n_idx, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
-  double *tbl = (actor ? c->ac.actor : c->p.table) + (size_t)agent * c->cfg.memory;
+  double *tbl = (actor ? c->ac.actor : c->p.table) + (size_t)agent * c->p.tstride;
   const double lo = actor ? c->ac.action_min : -DBL_MAX, hi = actor ? c->ac.action_max : DBL_MAX;
-  if (value) k_table_read<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, d_v, d_bad);
-  else k_table_update<<<1, 1, 0, c->stream>>>(tbl, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, delta, d_bad);
+  const uint32_t *perm = c->geo ? c->p.geo.perm : nullptr;
+  if (value) k_table_read<<<1, 1, 0, c->stream>>>(tbl, perm, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, d_v, d_bad);
+  else k_table_update<<<1, 1, 0, c->stream>>>(tbl, perm, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, delta, d_bad);
   c->launches++;
   CU(cudaGetLastError());
   int bad = 0;
@@ -664,6 +709,25 @@ static cudaEvent_t get_event(grlcu_ctx *c)
   return e;
 }
 
+// Fold the event pairs of finished launches into the running total so that ev_pending stays short when a caller
+// never asks for the kernel time (OnlineLearningExperiment::run loops grlcu_run + grlcu_get_results for hours).
+static void drain_events(grlcu_ctx *c)
+{
+  size_t k = 0;
+  for (auto &pr : c->ev_pending)
+  {
+    float t = 0;
+    if (cudaEventQuery(pr.second) == cudaSuccess && cudaEventElapsedTime(&t, pr.first, pr.second) == cudaSuccess)
+    {
+      c->ev_ms += t; c->ev_n += 1;
+      c->ev_pool.push_back(pr.first); c->ev_pool.push_back(pr.second);
+    }
+    else c->ev_pending[k++] = pr;
+  }
+  c->ev_pending.resize(k);
+  cudaGetLastError();      // cudaEventQuery reports cudaErrorNotReady through the sticky-free error state
+}
+
 extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
 {
   if (!c || n_steps < 0) return fail(GRLCU_ERR_ARG, "grlcu_run: bad arguments");
@@ -673,44 +737,8 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
   if (cohort <= 0 || cohort > n) cohort = n;
   // the cache stays live between launches (values return to the tables lazily, see ensure_plain) unless the
   // agents run in cohorts or GRLCU_EAGER_CLOSE is set
-  // GRLCU_MODE=2: sixteen lanes per agent, L2-sized cohorts (grlcu_coop.cuh); same eligibility as the value cache
-  if (c->p.mode == 2 && c->cfg.algo != GRLCU_ALGO_AC && c->cfg.dynamics != GRLCU_DYN_CART_DOUBLE_POLE &&
-      c->cfg.tilings == kLanes && !c->p.force_slow &&
-      c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64 && c->cfg.n_actions == 3)
-  {
-    if (int r = ensure_plain(c)) return r;
-    int cc = c->coop_cohort < n ? c->coop_cohort : n;
-    if (cohort < cc) cc = cohort;
-    if (!c->coop.cv)
-    {
-      const size_t slots = (size_t)c->coop_cohort * c->p.trace_cap * kLanes;
-      if (int r = dalloc(c, &c->coop.cv, slots)) return r;
-      if (int r = dalloc(c, &c->coop.ring, slots)) return r;
-      if (int r = dalloc(c, &c->coop.vmask, (size_t)c->coop_cohort * c->p.trace_cap)) return r;
-    }
-    for (int begin = 0; begin < n; begin += cc)
-    {
-      const int end = begin + cc < n ? begin + cc : n;
-      cudaEvent_t e0 = get_event(c), e1 = get_event(c);
-      CU(cudaEventRecord(e0, c->stream));
-#define COOP(D, L, MB) k_run_coop<D, 3, L, MB><<<((end - begin) * L + kMaxBlock - 1) / kMaxBlock, kMaxBlock, 0, c->stream>>>(c->p, c->coop, begin, end, n_steps)
-      const bool pend = c->cfg.dynamics == GRLCU_DYN_PENDULUM;
-      const bool roomy = getenv("GRLCU_COOP_ROOMY") != nullptr;     // 255 registers, half the resident warps
-      switch (c->coop_lanes)
-      {
-        case 16: if (pend) COOP(0, 16, 8); else COOP(1, 16, 8); break;
-        case 8:  if (pend) COOP(0, 8, 8); else COOP(1, 8, 8); break;
-        case 2:  if (roomy) { if (pend) COOP(0, 2, 4); else COOP(1, 2, 4); } else { if (pend) COOP(0, 2, 8); else COOP(1, 2, 8); } break;
-        default: if (roomy) { if (pend) COOP(0, 4, 4); else COOP(1, 4, 4); } else { if (pend) COOP(0, 4, 8); else COOP(1, 4, 8); } break;
-      }
-#undef COOP
-      CU(cudaEventRecord(e1, c->stream));
-      c->ev_pending.push_back({e0, e1});
-      c->launches++;
-    }
-    CU(cudaGetLastError());
-    return 0;
-  }
+  if (c->ev_pending.size() >= 32) drain_events(c);
+  c->traces_live = true;
   const bool lazy = cohort == n && !getenv("GRLCU_EAGER_CLOSE");
   if (!lazy) if (int r = ensure_plain(c)) return r;
   for (int begin = 0; begin < n; begin += cohort)
@@ -724,13 +752,14 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
     // at most 8 warps per SM: the 255-register instantiation (see k_run)
     const int ctas_per_sm = (grd + c->sm_count - 1) / c->sm_count;
     const bool roomy = ctas_per_sm * (c->block / 32) <= 8 && !getenv("GRLCU_MINB7");
-#define CALL(D)                                                                                    \
+#define CALL_G(D, G)                                                                               \
     do {                                                                                           \
-      if (cached && roomy) k_run<D, 16, 3, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
-      else if (cached) k_run<D, 16, 3, true, 7><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
-      else if (roomy) k_run<D, 16, 3, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0); \
-      else k_run<D, 16, 3, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0);      \
+      if (cached && roomy) k_run<D, 16, 3, true, 4, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
+      else if (cached) k_run<D, 16, 3, true, 7, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
+      else if (roomy) k_run<D, 16, 3, false, 4, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0); \
+      else k_run<D, 16, 3, false, 7, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0);      \
     } while (0)
+#define CALL(D) CALL_G(D, false)
 #define CALL_AC(D)                                                                                 \
     do {                                                                                           \
       if (cached && roomy) k_run_ac<D, 16, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
@@ -739,9 +768,11 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
       else k_run_ac<D, 16, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0);      \
     } while (0)
     if (c->cfg.algo == GRLCU_ALGO_AC) DISPATCH_DYN(c, CALL_AC);
+    else if (c->geo) CALL_G(0, true);              // the tile-major layout is instantiated for the pendulum (grlcu_layout.h)
     else DISPATCH_SARSA(c, CALL);
 #undef CALL_AC
 #undef CALL
+#undef CALL_G
     if (cached && lazy && begin + cohort >= n) c->cache_live = true;
     CU(cudaEventRecord(e1, c->stream));
     c->ev_pending.push_back({e0, e1});
@@ -764,7 +795,7 @@ extern "C" int grlcu_run_kernel_time(grlcu_ctx *c, double *ms, int64_t *launches
   if (!c) return fail(GRLCU_ERR_ARG, "null context");
   CU(cudaSetDevice(c->device));
   CU(cudaStreamSynchronize(c->stream));
-  double total = 0;
+  double total = c->ev_ms;
   for (auto &pr : c->ev_pending)
   {
     float t = 0;
@@ -773,8 +804,9 @@ extern "C" int grlcu_run_kernel_time(grlcu_ctx *c, double *ms, int64_t *launches
     c->ev_pool.push_back(pr.first); c->ev_pool.push_back(pr.second);
   }
   if (ms) *ms = total;
-  if (launches) *launches = (int64_t)c->ev_pending.size();
+  if (launches) *launches = c->ev_n + (int64_t)c->ev_pending.size();
   c->ev_pending.clear();
+  c->ev_ms = 0; c->ev_n = 0;
   return 0;
 }
 
@@ -850,8 +882,16 @@ extern "C" int grlcu_get_table(grlcu_ctx *c, int32_t agent, double *out)
   if (!c || !out || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_get_table: bad arguments");
   CU(cudaSetDevice(c->device));
   if (int r = ensure_plain(c)) return r;
-  CU(cudaMemcpyAsync(out, c->p.table + (size_t)agent * c->cfg.memory, sizeof(double) * c->cfg.memory,
-                     cudaMemcpyDeviceToHost, c->stream));
+  const double *src = c->p.table + (size_t)agent * c->p.tstride;
+  if (c->geo)
+  {
+    // physical (tile-major) -> the reference's logical order
+    k_table_gather<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(src, c->p.geo.perm, c->cfg.memory, c->d_stage);
+    c->launches++;
+    CU(cudaGetLastError());
+    src = c->d_stage;
+  }
+  CU(cudaMemcpyAsync(out, src, sizeof(double) * c->cfg.memory, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -861,8 +901,25 @@ extern "C" int grlcu_set_table(grlcu_ctx *c, int32_t agent, const double *in)
   if (!c || !in || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_set_table: bad arguments");
   CU(cudaSetDevice(c->device));
   if (int r = ensure_plain(c)) return r;
-  CU(cudaMemcpyAsync(c->p.table + (size_t)agent * c->cfg.memory, in, sizeof(double) * c->cfg.memory,
-                     cudaMemcpyHostToDevice, c->stream));
+  // The fused kernel keeps a directory inside the table: a word whose high half is kSentinelHi (a signalling-NaN
+  // pattern no arithmetic produces) names a cache slot.  A checkpoint must not smuggle one in.
+  for (int32_t x = 0; x < c->cfg.memory; ++x)
+  {
+    uint64_t bits;
+    memcpy(&bits, in + x, sizeof(bits));
+    if ((uint32_t)(bits >> 32) == (uint32_t)kSentinelHi)
+      return fail(GRLCU_ERR_ARG, "grlcu_set_table: entry %d holds the NaN pattern 0x%08X........ that the kernels reserve", x, kSentinelHi);
+  }
+  double *dst = c->p.table + (size_t)agent * c->p.tstride;
+  if (c->geo)
+  {
+    CU(cudaMemcpyAsync(c->d_stage, in, sizeof(double) * c->cfg.memory, cudaMemcpyHostToDevice, c->stream));
+    k_table_scatter<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(dst, c->p.geo.perm, c->cfg.memory, c->d_stage);
+    c->launches++;
+    CU(cudaGetLastError());
+  }
+  else
+    CU(cudaMemcpyAsync(dst, in, sizeof(double) * c->cfg.memory, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -918,6 +975,7 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
     return fail(GRLCU_ERR_ARG, "grlcu_replay_step: missing input array");
   CU(cudaSetDevice(c->device));
   if (int r = ensure_plain(c)) return r;
+  c->traces_live = true;
   // AC mode: one projection row (the fed observation) and four value rows (pi(s'), V(s'), u, a')
   const size_t n = (size_t)c->p.n, S = (size_t)c->S, OBS = (size_t)c->OBS, T = (size_t)c->cfg.tilings,
                A = is_ac ? 4 : (size_t)c->cfg.n_actions, HA = is_ac ? 1 : A, cap = (size_t)c->p.trace_cap;
@@ -953,9 +1011,10 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
 #undef OUTB
   if (oom) return fail(GRLCU_ERR_NOMEM, "grlcu_replay_step: device scratch allocation/copy failed");
   const int blk = 64, grd = ((int)n + blk - 1) / blk;
-#define CALL(D) k_replay<D, 16, 3><<<grd, blk, 0, c->stream>>>(c->p, io)
+#define CALL(D) k_replay<D, 16, 3, false><<<grd, blk, 0, c->stream>>>(c->p, io)
 #define CALL_AC(D) k_replay_ac<D, 16><<<grd, blk, 0, c->stream>>>(c->p, c->ac, io)
   if (is_ac) DISPATCH_DYN(c, CALL_AC);
+  else if (c->geo) k_replay<0, 16, 3, true><<<grd, blk, 0, c->stream>>>(c->p, io);
   else DISPATCH_SARSA(c, CALL);
 #undef CALL_AC
 #undef CALL
@@ -972,6 +1031,10 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
   DOWN(o_swept, swept, int32_t, n); DOWN(o_trace_len, trace_len, int32_t, n);
   DOWN(o_trace_index, trace_index, uint32_t, cap * T * n);
 #undef DOWN
+  int32_t mismatch = 0;
+  if (c->geo) CU(cudaMemcpyAsync(&mismatch, c->p.geo.mismatch, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  if (mismatch)
+    return fail(GRLCU_ERR_CUDA, "grlcu_replay_step: a tile's geometric slot differs from perm[hash index] (layout bug)");
   return 0;
 }

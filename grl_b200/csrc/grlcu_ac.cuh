@@ -180,8 +180,8 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
   uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
-  double *critic = p.table + (size_t)a * p.proj.memory;
-  double *actor = ac.actor + (size_t)a * p.proj.memory;
+  double *critic = p.table + (size_t)a * p.tstride;
+  double *actor = ac.actor + (size_t)a * p.tstride;
   const uint64_t gid = (uint64_t)(p.first_id + a);
   Cache<T> c;
   c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
@@ -265,8 +265,8 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
   uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
-  double *critic = p.table + (size_t)a * p.proj.memory;
-  double *actor = ac.actor + (size_t)a * p.proj.memory;
+  double *critic = p.table + (size_t)a * p.tstride;
+  double *actor = ac.actor + (size_t)a * p.tstride;
   const uint64_t gid = (uint64_t)(p.first_id + a);
   const bool test = io.test[a] != 0;
   ACOut o;

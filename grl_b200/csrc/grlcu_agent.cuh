@@ -16,6 +16,32 @@
 
 namespace grlcu {
 
+// Physical table layout ("tile-major").  The reference addresses its table with the raw hash,
+// x = h % memory (tile_coding.h:116-118), so the A words of Q(s', .) that belong to one tile of one tiling are A
+// unrelated DRAM requests.  x stays the LOGICAL address (what replay reports, what grlcu_get_table / set_table and
+// checkpoints use); word x is STORED at physical slot perm[x], one permutation per context shared by all its agents
+// (same hash, same memory => the same collisions for every agent), built on the host by grlcu_create:
+//   * the tiles inside the task's observation box are enumerated cell by cell (cell = the T-aligned coarse tile
+//     coordinates k_i of every observation dimension), tiling by tiling, action by action; the A action words of one
+//     (cell, tiling) group get consecutive slots, padded to one 32-byte sector: slot = ((cell * T) + j) * 4 + a;
+//   * a word whose index x was already placed by an earlier tile (a hash collision) simply shares that earlier slot
+//     (slotmap[] names it, its bit in gflags[] is clear): semantics unchanged by construction;
+//   * indices no tile of the box maps to fill the holes and the tail.
+// The fused kernel computes the slot from the tile coordinates (no hash, no lookup) for every word that lives in
+// its own group's sector; the MurmurHash2 path + perm[] serve observations outside the box.
+struct Geo
+{
+  int32_t  enabled;
+  int32_t  kn[kMaxDims];        // coarse cells per observation dimension
+  int32_t  koff[kMaxDims];      // k + koff in [0, kn) inside the box (unwrapped dimensions)
+  int32_t  wrapped[kMaxDims];   // dimension wraps (wrap = kn * T): k mod kn
+  const uint32_t *perm;         // [memory] logical index -> physical slot
+  const uint32_t *iperm;        // [tstride] physical slot -> logical index (kInvalidIndex: padding)
+  const uint32_t *slotmap;      // [ncells * T * 4] physical slot of every in-box tile word
+  const uint32_t *gflags;       // 4 bits per (cell, tiling) group: bit a = action a's word is in the group's own sector
+  int32_t  *mismatch;           // replay kernels: geometric slot != perm[hash index] seen (must stay 0)
+};
+
 struct Params
 {
   int32_t  n;                 // agents in this context
@@ -24,6 +50,8 @@ struct Params
   double   tau; int32_t isteps; double timeout, randomization;
   int32_t  end_stop_penalty;  // task/cart_pole/swingup end_stop_penalty (cart_pole.cpp:177,196)
   Projector proj;
+  Geo      geo;
+  uint32_t tstride;           // doubles per agent in `table` (memory, or more with the padded tile-major layout)
   uint32_t kact[8][16];      // pre-mixed MurmurHash2 word of the action coordinate, per (action, tiling)
   uint32_t kj[16];           // pre-mixed word of the tiling number
   uint32_t mem_mask;         // memory-1 if memory is a power of two, else 0
@@ -261,17 +289,20 @@ struct Agent
 // (tile_coding.cpp:103-149) + LinearRepresentation::read (linear.cpp:136-184: sequential sum in tiling
 // order, then / T).  The MurmurHash2 state after the observation coordinates is shared by the A actions
 // (the action coordinate and the tiling number are the last two words and are pre-mixed on the host).
-// Indices go to the shared-memory stash `sid` (element (aa*T+j) at sid[(aa*T+j)*kMaxBlock]).
+// PHYSICAL slots go to the shared-memory stash `sid` (element (aa*T+j) at sid[(aa*T+j)*kMaxBlock]); with GEO they
+// come from the tile coordinates (see struct Geo), otherwise slot = index.  hash_out / index_out (replay): the
+// reference's hash and logical index h % memory of every word.
 // The gathers are issued in two groups (actions 0..A-2, then action A-1 together with the T entries of
 // the previous projection p) to bound the registers holding loads in flight.
-template <int DYN, int T, int A, typename Resolve>
+template <int DYN, int T, int A, bool GEO, typename Resolve>
 __device__ __forceinline__ void q_values(const Params &p, const double *tbl, const double (&obs)[Dyn<DYN>::OBS],
                                          uint32_t *sid, double (&q)[A], const uint32_t (&pidx)[T],
-                                         double (&vp)[T], bool with_p, uint32_t *hash_out, int n, int a, Resolve resolve)
+                                         double (&vp)[T], bool with_p, uint32_t *hash_out, uint32_t *index_out,
+                                         int n, int a, Resolve resolve)
 {
   constexpr int OBS = Dyn<DYN>::OBS;
   const uint32_t m = 0x5bd1e995u;
-  // Phase 1: the A*T indices into the stash.  Pure integer work, rolled over the tilings on purpose: unrolled it
+  // Phase 1: the A*T slots into the stash.  Pure integer work, rolled over the tilings on purpose: unrolled it
   // is ~100 KB of SASS per call site and the fused kernels are instruction-fetch bound.
   {
     int32_t qz[OBS];
@@ -280,27 +311,68 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
 #pragma unroll 1
     for (int j = 0; j < T; ++j)
     {
-      uint32_t h = 449u ^ (uint32_t)(OBS + 2);
-#pragma unroll
-      for (int i = 0; i < OBS; ++i)
+      bool inbox = false;
+      uint32_t group = 0;
+      if (GEO)
       {
-        int32_t c = qz[i] - safe_mod(qz[i] - j * (1 + 2 * i), T);
-        if (p.proj.wrap[i] != 0) c = safe_mod(c, p.proj.wrap[i]);
-        h = (h * m) ^ murmur_mix((uint32_t)c);
+        // coarse tile coordinate of tiling j in dimension i: c_i = b + T*k with b = j(1+2i) mod T (tile_coding.cpp:122-131)
+        inbox = true;
+        uint32_t cell = 0;
+#pragma unroll
+        for (int i = 0; i < OBS; ++i)
+        {
+          int32_t k = (qz[i] - ((j * (1 + 2 * i)) & (T - 1))) >> (T == 16 ? 4 : T == 8 ? 3 : 5);
+          k += p.geo.koff[i];
+          if (p.geo.wrapped[i]) k = k < 0 ? k + p.geo.kn[i] : k >= p.geo.kn[i] ? k - p.geo.kn[i] : k;   // one period either way
+          inbox &= (uint32_t)k < (uint32_t)p.geo.kn[i];            // anything else takes the hash path below
+          cell = cell * (uint32_t)p.geo.kn[i] + (uint32_t)k;
+        }
+        group = cell * T + j;
       }
-#pragma unroll
-      for (int aa = 0; aa < A; ++aa)
+      if (GEO && inbox)
       {
-        uint32_t g = (h * m) ^ p.kact[aa][j];
-        g = (g * m) ^ p.kj[j];
-        g ^= g >> 13; g *= m; g ^= g >> 15;
-        if (hash_out) hash_out[((size_t)aa * T + j) * n + a] = g;
-        sid[(aa * T + j) * kMaxBlock] = reduce_index(p, g);
+        const uint32_t own = (__ldg(p.geo.gflags + (group >> 3)) >> ((group & 7u) * 4u)) & 15u;
+#pragma unroll
+        for (int aa = 0; aa < A; ++aa)
+        {
+          uint32_t slot = group * 4u + aa;
+          if (!((own >> aa) & 1u)) slot = __ldg(p.geo.slotmap + slot);     // collided with an earlier tile: shares its slot
+          sid[(aa * T + j) * kMaxBlock] = slot;
+        }
+      }
+      if (!GEO || !inbox || hash_out || index_out)
+      {
+        uint32_t h = 449u ^ (uint32_t)(OBS + 2);
+#pragma unroll
+        for (int i = 0; i < OBS; ++i)
+        {
+          int32_t c = qz[i] - safe_mod(qz[i] - j * (1 + 2 * i), T);
+          if (p.proj.wrap[i] != 0) c = safe_mod(c, p.proj.wrap[i]);
+          h = (h * m) ^ murmur_mix((uint32_t)c);
+        }
+#pragma unroll
+        for (int aa = 0; aa < A; ++aa)
+        {
+          uint32_t g = (h * m) ^ p.kact[aa][j];
+          g = (g * m) ^ p.kj[j];
+          g ^= g >> 13; g *= m; g ^= g >> 15;
+          const uint32_t x = reduce_index(p, g);
+          if (hash_out) hash_out[((size_t)aa * T + j) * n + a] = g;
+          if (index_out) index_out[((size_t)aa * T + j) * n + a] = x;
+          if (!GEO) sid[(aa * T + j) * kMaxBlock] = x;
+          else
+          {
+            const uint32_t slot = __ldg(p.geo.perm + x);
+            if (!inbox) sid[(aa * T + j) * kMaxBlock] = slot;
+            else if (slot != sid[(aa * T + j) * kMaxBlock]) *p.geo.mismatch = 1;   // replay only: must never happen
+          }
+        }
       }
     }
   }
   // Phase 2: the gathers, issued in two groups (actions 0..A-2, then action A-1 together with p's T words) to
-  // bound the registers holding loads in flight.
+  // bound the registers holding loads in flight.  With GEO the A loads of one tiling normally hit ONE 32-byte
+  // sector (L1 merges them into one request).
   {
     double w[A - 1][T];
 #pragma unroll

@@ -31,6 +31,36 @@ __global__ void k_table_init(double *table, int32_t n, int32_t memory, int64_t f
   }
 }
 
+// The same initial values under the tile-major physical layout (struct Geo): one thread per physical slot, the
+// value of logical entry x = iperm[slot] is half (x & 1) of Philox counter x / 2; padding slots are zero.
+__global__ void k_table_init_phys(double *table, int32_t n, uint32_t tstride, const uint32_t *iperm, int64_t first_id,
+                                  uint64_t seed, double init_min, double init_max, int stream_id)
+{
+  const int64_t total = (int64_t)tstride * n;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x)
+  {
+    const int64_t a = t / tstride;
+    const uint32_t x = __ldg(iperm + (t - a * tstride));
+    double v = 0;
+    if (x != kInvalidIndex)
+    {
+      Philox4 w = philox_for(seed, (uint64_t)(first_id + a), stream_id, (uint64_t)(x >> 1));
+      v = init_min + ((x & 1u) ? u53(w.w[2], w.w[3]) : u53(w.w[0], w.w[1])) * (init_max - init_min);
+    }
+    table[t] = v;
+  }
+}
+
+// logical <-> physical copies of one agent's table (grlcu_get_table / grlcu_set_table under the tile-major layout)
+__global__ void k_table_gather(const double *tbl, const uint32_t *perm, int32_t memory, double *out)
+{
+  for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < memory; x += gridDim.x * blockDim.x) out[x] = tbl[__ldg(perm + x)];
+}
+__global__ void k_table_scatter(double *tbl, const uint32_t *perm, int32_t memory, const double *in)
+{
+  for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < memory; x += gridDim.x * blockDim.x) tbl[__ldg(perm + x)] = in[x];
+}
+
 // K2: TileCodingProjector::_project for n independent inputs ([n][DIMS] row-major).
 template <int DIMS, int T>
 __global__ void k_project(Projector proj, int64_t n, const double *in, uint32_t *hash, uint32_t *index)
@@ -112,11 +142,11 @@ template <int T> struct CacheResolve
 //   act   : there is a next action to choose (TDAgent::start / step; false for TDAgent::end, td.cpp:76-81)
 //   learn : there is a transition to learn from (TDAgent::step / end of a learning episode, td.cpp:63-81)
 // Returns the policy's own action choice (-1 when !act); commits `force` instead when force >= 0 (replay).
-template <int DYN, int T, int A, bool CACHED>
+template <int DYN, int T, int A, bool CACHED, bool GEO>
 __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                           uint32_t *sid, int a,
                                           const double (&obs)[Dyn<DYN>::OBS], double reward, bool act, bool learn,
-                                          bool test, const Draws &d, int force, uint32_t *hash_out, double *o_q,
+                                          bool test, const Draws &d, int force, uint32_t *hash_out, uint32_t *index_out, double *o_q,
                                           double &qp, double &target, double &delta, int &swept)
 {
   qp = target = delta = 0; swept = 0;
@@ -127,8 +157,8 @@ __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, co
   {
     // act on the new observation first (td.cpp:63-74), then update with (s,a,r,s',a')
     double q[A];
-    if (CACHED) q_values<DYN, T, A>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, p.n, a, CacheResolve<T>{c});
-    else q_values<DYN, T, A>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, p.n, a, NoResolve());
+    if (CACHED) q_values<DYN, T, A, GEO>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, index_out, p.n, a, CacheResolve<T>{c});
+    else q_values<DYN, T, A, GEO>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, index_out, p.n, a, NoResolve());
     own = sample_action<A>(q, d, ag.epsilon, test, p.softmax_tau);
     ai = force >= 0 ? force : own;
     if (o_q)
@@ -158,7 +188,7 @@ __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, co
 
 // Episode start (online_learning.cpp:160-178): observe the start state, TDAgent::start /
 // FixedAgent::start (trace clear + first act).  Used by the replay kernel; k_run inlines the same sequence.
-template <int DYN, int T, int A, bool CACHED>
+template <int DYN, int T, int A, bool CACHED, bool GEO>
 __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                               uint32_t *sid, int a, const Draws &d, bool test, double *o_q, int *o_ai)
 {
@@ -175,21 +205,21 @@ __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag
   ag.total_reward = 0;
   ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
   double qp, target, delta; int swept;
-  const int ai = agent_core<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, 0., true, false, test, d, -1, nullptr, o_q,
-                                               qp, target, delta, swept);
+  const int ai = agent_core<DYN, T, A, CACHED, GEO>(p, ag, c, tbl, sid, a, obs, 0., true, false, test, d, -1, nullptr, nullptr, o_q,
+                                                    qp, target, delta, swept);
   if (o_ai) *o_ai = ai;
 }
 
 // The agent half of one step (TDAgent::step / end, td.cpp:63-81; FixedAgent for test episodes).
-template <int DYN, int T, int A, bool CACHED>
+template <int DYN, int T, int A, bool CACHED, bool GEO>
 __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                           uint32_t *sid, int a,
                                           const double (&obs)[Dyn<DYN>::OBS], double reward, int terminal, bool test,
-                                          const Draws &d, int force, uint32_t *hash_out, double *o_q,
+                                          const Draws &d, int force, uint32_t *hash_out, uint32_t *index_out, double *o_q,
                                           double &qp, double &target, double &delta, int &swept)
 {
-  return agent_core<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !test, test, d, force,
-                                       hash_out, o_q, qp, target, delta, swept);
+  return agent_core<DYN, T, A, CACHED, GEO>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !test, test, d, force,
+                                            hash_out, index_out, o_q, qp, target, delta, swept);
 }
 
 // Fused K1-K4: each thread owns one agent and runs n_steps iterations of the hot loop with the
@@ -199,7 +229,7 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, co
 // so 14 warps means 4 warps on some of them and the kernel is bounded at 128 registers per thread
 // (MINB = 7).  Launches with at most 8 warps per SM (BASELINE configs[2], [3]: 32,768 agents) use the
 // MINB = 4 instantiation, which may use up to 255 registers and does not spill.
-template <int DYN, int T, int A, bool CACHED, int MINB>
+template <int DYN, int T, int A, bool CACHED, int MINB, bool GEO>
 __global__ void __launch_bounds__(kMaxBlock, MINB)
 k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, int do_close)
 {
@@ -210,7 +240,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
   uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
-  double *tbl = p.table + (size_t)a * p.proj.memory;
+  double *tbl = p.table + (size_t)a * p.tstride;
   const uint64_t gid = (uint64_t)(p.first_id + a);
   Cache<T> c;
   c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
@@ -270,8 +300,8 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
     double qp, target, delta; int swept;
     Draws d; d.u = 1.; d.r_explore = 0; d.r_tie = 0;
     if (terminal != 2) d = next_draws<DYN, T>(p, ag, a, gid, test);
-    agent_core<DYN, T, A, CACHED>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !starting && !test, test, d, -1,
-                                  nullptr, nullptr, qp, target, delta, swept);
+    agent_core<DYN, T, A, CACHED, GEO>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !starting && !test, test, d, -1,
+                                       nullptr, nullptr, nullptr, qp, target, delta, swept);
     if (!starting)
     {
       if (!test) ag.dsteps++;
@@ -294,13 +324,13 @@ __global__ void k_cache_close(Params p)
   ag.load(p, a);
   Cache<T> c;
   c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
-  cache_close<DYN, T>(p, ag, c, p.table + (size_t)a * p.proj.memory);
+  cache_close<DYN, T>(p, ag, c, p.table + (size_t)a * p.tstride);
   ag.store(p, a);
 }
 
 // Replay: one agent-step per agent with states, observations, rewards, draws (and optionally the
 // committed action) fed from outside; emits everything observable for comparison.
-template <int DYN, int T, int A>
+template <int DYN, int T, int A, bool GEO>
 __global__ void __launch_bounds__(kMaxBlock)
 k_replay(Params p, ReplayIO io)
 {
@@ -312,7 +342,7 @@ k_replay(Params p, ReplayIO io)
   uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
-  double *tbl = p.table + (size_t)a * p.proj.memory;
+  double *tbl = p.table + (size_t)a * p.tstride;
   const bool test = io.test[a] != 0;
 
   if (io.started[a])
@@ -321,7 +351,7 @@ k_replay(Params p, ReplayIO io)
     for (int i = 0; i < S; ++i) ag.x[i] = io.start_state[(size_t)i * n + a];
     Draws d; d.u = io.start_u[a]; d.r_explore = io.start_r_explore[a]; d.r_tie = io.start_r_tie[a];
     int ai;
-    episode_start<DYN, T, A, false>(p, ag, Cache<T>(), tbl, sid, a, d, test, io.o_start_q, &ai);
+    episode_start<DYN, T, A, false, GEO>(p, ag, Cache<T>(), tbl, sid, a, d, test, io.o_start_q, &ai);
     if (io.o_start_action_index) io.o_start_action_index[a] = ai;
     p.episode_ctr[a] += 1;
   }
@@ -351,12 +381,10 @@ k_replay(Params p, ReplayIO io)
   double qp, target, delta; int swept;
   Draws d; d.u = io.u[a]; d.r_explore = io.r_explore[a]; d.r_tie = io.r_tie[a];
   const int force = (io.force_action && terminal != 2) ? io.force_action[a] : -1;
-  const int own = agent_half<DYN, T, A, false>(p, ag, Cache<T>(), tbl, sid, a, obs, reward, terminal, test, d, force,
-                                        io.o_hash, io.o_q, qp, target, delta, swept);
+  const int own = agent_half<DYN, T, A, false, GEO>(p, ag, Cache<T>(), tbl, sid, a, obs, reward, terminal, test, d, force,
+                                             io.o_hash, io.o_index, io.o_q, qp, target, delta, swept);
   if (terminal != 2)
   {
-    if (io.o_index)
-      for (int k = 0; k < A * T; ++k) io.o_index[(size_t)k * n + a] = sid[k * kMaxBlock];
     if (test) p.test_act_ctr[a] += 1; else ag.act_ctr++;
   }
   if (io.o_action_index) io.o_action_index[a] = own;
@@ -370,8 +398,12 @@ k_replay(Params p, ReplayIO io)
     {
       const int pos = ring_pos(ag.head, k, p.trace_cap);
       for (int j = 0; j < T; ++j)
-        io.o_trace_index[((size_t)k * T + j) * n + a] =
-            k < ag.len ? p.trace_idx[((size_t)pos * T + j) * n + a] : kInvalidIndex;
+      {
+        // the ring holds physical slots; the reference's trace holds the logical indices
+        uint32_t x = k < ag.len ? p.trace_idx[((size_t)pos * T + j) * n + a] : kInvalidIndex;
+        if (GEO && x != kInvalidIndex) x = __ldg(p.geo.iperm + x);
+        io.o_trace_index[((size_t)k * T + j) * n + a] = x;
+      }
     }
   if (!test) ag.dsteps++;
   if (terminal) ag.episode_end(p, a, test);

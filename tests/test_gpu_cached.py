@@ -1,5 +1,6 @@
-"""The trace value cache (grlcu_cached.cuh) is an internal optimisation of the fused kernel: it must
-leave tables, traces, counters and returns bit-identical to the uncached path, which the replay tests
+"""The trace value cache (grlcu_cached.cuh) and the tile-major physical table layout (struct Geo, grlcu_layout.h)
+are internal optimisations of the fused kernel: they must leave tables (in the reference's logical order), traces,
+counters and returns bit-identical to the uncached path on the reference's raw hash order, which the replay tests
 pin to the oracle step by step.  Both paths run the same device dynamics and Philox streams, so every
 bit has to agree, across launch boundaries, test episodes, absorbing ends and index collisions."""
 import os
@@ -10,18 +11,14 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _run(G, mk, mode, n, launches, sweep=False, coop_cohort=None, coop_lanes=None, **kw):
+def _run(G, mk, mode, n, launches, sweep=False, layout=1, **kw):
     os.environ["GRLCU_MODE"] = str(mode)
-    if coop_cohort:
-        os.environ["GRLCU_COOP_COHORT"] = str(coop_cohort)
-    if coop_lanes:
-        os.environ["GRLCU_COOP_LANES"] = str(coop_lanes)
+    os.environ["GRLCU_LAYOUT"] = str(layout)
     try:
         b = G.Batch(mk(**kw), n)
     finally:
         os.environ.pop("GRLCU_MODE", None)
-        os.environ.pop("GRLCU_COOP_COHORT", None)
-        os.environ.pop("GRLCU_COOP_LANES", None)
+        os.environ.pop("GRLCU_LAYOUT", None)
     try:
         if sweep:
             # per-agent hyperparameters (MultiExperiment / grlo sweeps): trace lengths differ inside a warp
@@ -44,6 +41,9 @@ def _run(G, mk, mode, n, launches, sweep=False, coop_cohort=None, coop_lanes=Non
 @pytest.mark.parametrize("case", [
     dict(which="pendulum", n=96, memory=65536, launches=[37, 100, 63, 1, 250], test_interval=3),
     dict(which="pendulum", n=64, memory=257, launches=[150, 75], test_interval=-1),      # heavy collisions
+    # tiles of the box / table entries = 0.76: a third of the tile words share an earlier tile's slot (tile-major layout)
+    dict(which="pendulum", n=64, memory=32768, launches=[100, 200], test_interval=3),
+    dict(which="pendulum", n=16, memory=8388608, launches=[300], test_interval=-1),      # the shipped table size
     dict(which="pendulum", n=64, memory=4099, launches=[220], test_interval=2),          # non power of two
     dict(which="cart_pole", n=64, memory=262144, launches=[180, 333], test_interval=4, epsilon=0.2),
     dict(which="cart_pole", n=32, memory=1031, launches=[400], test_interval=-1, epsilon=0.5),
@@ -79,15 +79,13 @@ def test_cached_equals_uncached(case):
     n, launches = case.pop("n"), case.pop("launches")
     if which in ("pendulum", "cart_pole"):
         case["randomization"] = 1.0
-    r1, t1, s1 = _run(G, mk, 1, n, launches, **case)
-    # mode 0: one thread per agent with the value cache; mode 2: sixteen lanes per agent in L2-sized cohorts
-    # (grlcu_coop.cuh; SARSA family only), once as a single cohort and once as several ragged ones
-    variants = [dict(mode=0)]
-    if which in ("pendulum", "cart_pole"):
-        variants += [dict(mode=2, coop_lanes=4), dict(mode=2, coop_lanes=4, coop_cohort=20), dict(mode=2, coop_lanes=16),
-                     dict(mode=2, coop_lanes=8, coop_cohort=28), dict(mode=2, coop_lanes=2)]
+    # the reference's literal form: uncached, raw hash order
+    r1, t1, s1 = _run(G, mk, 1, n, launches, layout=0, **case)
+    # mode 0: the value cache; layout 1: tile-major physical layout where the context is eligible (the pendulum cases
+    # with tiles <= memory; everywhere else layout 1 is the raw order again and the variant repeats an earlier one)
+    variants = [dict(mode=0, layout=1), dict(mode=0, layout=0), dict(mode=1, layout=1)]
     for v in variants:
-        r0, t0, s0 = _run(G, mk, v["mode"], n, launches, coop_cohort=v.get("coop_cohort"), coop_lanes=v.get("coop_lanes"), **case)
+        r0, t0, s0 = _run(G, mk, v["mode"], n, launches, layout=v["layout"], **case)
         assert not np.isnan(t0).any(), v                   # no directory sentinel left in a table
         assert np.array_equal(t0, t1), v
         for k in r0:
