@@ -161,7 +161,8 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_run_host", "grlcu_replay_step", "grlcu_get_results", "grlcu_get_table",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
            "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update",
-           "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor", "grlcu_probe_random_access"]
+           "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor", "grlcu_probe_random_access",
+           "grlcu_device_count", "grlcu_group_create", "grlcu_group_destroy", "grlcu_group_run", "grlcu_group_results"]
 
 _lib = None
 
@@ -204,6 +205,10 @@ def load(build=True):
     L.grlcu_probe_random_access.argtypes = [C.c_int32, C.c_uint64, _dp, _dp, _dp]
     L.grlcu_read_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, _dp]
     L.grlcu_update_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, C.c_double]
+    L.grlcu_group_create.argtypes = [_P(vp), C.c_int32, _P(vp)]
+    L.grlcu_group_destroy.argtypes = [vp]
+    L.grlcu_group_run.argtypes = [vp, C.c_int64]
+    L.grlcu_group_results.argtypes = [vp, _P(Results), _dp]
     _lib = L
     return L
 

@@ -6,6 +6,8 @@
 #include "grlcu_layout.h"
 
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>          // types only: the library is loaded with dlopen on first use (grlcu_group_*)
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
@@ -354,7 +356,18 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   if (!r) r = dalloc(c, &p.total_decay, n);
   if (!r) r = dalloc(c, &p.flags, n);
   if (!r) r = dalloc(c, &p.dupmask, n);
-  if (!r) r = dalloc(c, &p.cache_val, n * T * (size_t)p.trace_cap);
+  {
+    // one contiguous block of cache_val per launch cohort (see grlcu_run): [blocks][cap*T][cblock]
+    const int roomy_cap = c->sm_count * 8 * 32 / c->block * c->block;
+    p.cblock = (uint32_t)n_agents;
+    if (n_agents > roomy_cap)
+    {
+      const int parts = (n_agents + roomy_cap - 1) / roomy_cap;
+      p.cblock = (uint32_t)(((n_agents + parts - 1) / parts + c->block - 1) / c->block * c->block);
+    }
+    const size_t blocks = (n + p.cblock - 1) / p.cblock;
+    if (!r) r = dalloc(c, &p.cache_val, blocks * p.cblock * T * (size_t)p.trace_cap);
+  }
   if (!r) r = dalloc(c, &p.cache_mask, n * (size_t)p.trace_cap);
   if (!r) r = dalloc(c, &p.act_ctr, n);
   if (!r) r = dalloc(c, &p.test_act_ctr, n);
@@ -413,7 +426,7 @@ __global__ void k_begin_override(Params p)
 {
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= p.n) return;
-  p.flags[a] = 4;     // not in episode, start-state override pending
+  p.flags[a] = (p.flags[a] & 16) | 4;     // not in episode, start-state override pending (bit4: the agent's cache stays as it is)
 }
 
 static int launch_reset(grlcu_ctx *c, int what)
@@ -739,33 +752,40 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
   // agents run in cohorts or GRLCU_EAGER_CLOSE is set
   if (c->ev_pending.size() >= 32) drain_events(c);
   c->traces_live = true;
-  const bool lazy = cohort == n && !getenv("GRLCU_EAGER_CLOSE");
-  if (!lazy) if (int r = ensure_plain(c)) return r;
+  // the trace value cache applies to the replacing trace (unique owner slot per index); it stays live between
+  // launches, agent by agent (values return to the tables lazily, see ensure_plain), unless GRLCU_EAGER_CLOSE is set
+  const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64;
+  const int do_close = getenv("GRLCU_EAGER_CLOSE") ? 1 : 0;
+  // Register budget: a launch with more than 8 warps per SM gets the 128-register instantiation, which spills
+  // ~0.5 KB per thread; two launches of half the agents at up to 255 registers are faster (profiles/r02_residency.txt:
+  // 5.76e8 against 4.38e8 agent-steps/s for the same 32,768 agents).  So, unless the caller chose a cohort size, the
+  // agents run in the fewest equal cohorts that fit 8 warps per SM.  Agents are independent: the order cannot matter.
+  // (per-agent lambda: trace lengths differ from warp to warp, and one launch lets the hardware backfill blocks as the
+  // short-trace warps finish: measured 3.75e8 all at once against 3.27e8 in four cohorts on the sweep workload)
+  if (cohort == n && (int)c->p.cblock < n && !c->p.lambda_a && !getenv("GRLCU_MINB7")) cohort = (int)c->p.cblock;
   for (int begin = 0; begin < n; begin += cohort)
   {
     const int end = begin + cohort < n ? begin + cohort : n;
     const int grd = (end - begin + c->block - 1) / c->block;
     cudaEvent_t e0 = get_event(c), e1 = get_event(c);
     CU(cudaEventRecord(e0, c->stream));
-    // the trace value cache applies to the replacing trace (unique owner slot per index)
-    const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64;
     // at most 8 warps per SM: the 255-register instantiation (see k_run)
     const int ctas_per_sm = (grd + c->sm_count - 1) / c->sm_count;
     const bool roomy = ctas_per_sm * (c->block / 32) <= 8 && !getenv("GRLCU_MINB7");
 #define CALL_G(D, G)                                                                               \
     do {                                                                                           \
-      if (cached && roomy) k_run<D, 16, 3, true, 4, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
-      else if (cached) k_run<D, 16, 3, true, 7, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
-      else if (roomy) k_run<D, 16, 3, false, 4, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0); \
-      else k_run<D, 16, 3, false, 7, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0, 0);      \
+      if (cached && roomy) k_run<D, 16, 3, true, 4, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, do_close); \
+      else if (cached) k_run<D, 16, 3, true, 7, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, do_close); \
+      else if (roomy) k_run<D, 16, 3, false, 4, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0); \
+      else k_run<D, 16, 3, false, 7, G><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0);      \
     } while (0)
 #define CALL(D) CALL_G(D, false)
 #define CALL_AC(D)                                                                                 \
     do {                                                                                           \
-      if (cached && roomy) k_run_ac<D, 16, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
-      else if (cached) k_run_ac<D, 16, true, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, !c->cache_live, lazy ? 0 : 1); \
-      else if (roomy) k_run_ac<D, 16, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0); \
-      else k_run_ac<D, 16, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0, 0);      \
+      if (cached && roomy) k_run_ac<D, 16, true, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, do_close); \
+      else if (cached) k_run_ac<D, 16, true, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, do_close); \
+      else if (roomy) k_run_ac<D, 16, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0); \
+      else k_run_ac<D, 16, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0);      \
     } while (0)
     if (c->cfg.algo == GRLCU_ALGO_AC) DISPATCH_DYN(c, CALL_AC);
     else if (c->geo) CALL_G(0, true);              // the tile-major layout is instantiated for the pendulum (grlcu_layout.h)
@@ -773,7 +793,7 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
 #undef CALL_AC
 #undef CALL
 #undef CALL_G
-    if (cached && lazy && begin + cohort >= n) c->cache_live = true;
+    if (cached && !do_close) c->cache_live = true;
     CU(cudaEventRecord(e1, c->stream));
     c->ev_pending.push_back({e0, e1});
     c->launches++;
@@ -1036,5 +1056,201 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
   CU(cudaStreamSynchronize(c->stream));
   if (mismatch)
     return fail(GRLCU_ERR_CUDA, "grlcu_replay_step: a tile's geometric slot differs from perm[hash index] (layout bug)");
+  return 0;
+}
+
+// ---- several GPUs of one box (include/grlcu.h) ------------------------------------------------------------------
+namespace {
+struct NcclApi
+{
+  void *handle = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+// By soname: a process that already holds an NCCL (torch's bundled one) gets that one, not a second copy.
+int load_nccl(NcclApi *api)
+{
+  static NcclApi g;
+  if (!g.handle)
+  {
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+    if (!h) return fail(GRLCU_ERR_UNSUPPORTED, "grlcu_group: cannot load libnccl.so.2 (%s)", dlerror());
+    g.CommInitAll = (decltype(g.CommInitAll))dlsym(h, "ncclCommInitAll");
+    g.CommDestroy = (decltype(g.CommDestroy))dlsym(h, "ncclCommDestroy");
+    g.GroupStart = (decltype(g.GroupStart))dlsym(h, "ncclGroupStart");
+    g.GroupEnd = (decltype(g.GroupEnd))dlsym(h, "ncclGroupEnd");
+    g.AllGather = (decltype(g.AllGather))dlsym(h, "ncclAllGather");
+    g.GetErrorString = (decltype(g.GetErrorString))dlsym(h, "ncclGetErrorString");
+    if (!g.CommInitAll || !g.CommDestroy || !g.GroupStart || !g.GroupEnd || !g.AllGather || !g.GetErrorString)
+    {
+      dlclose(h);
+      return fail(GRLCU_ERR_UNSUPPORTED, "grlcu_group: libnccl.so.2 lacks a needed entry point");
+    }
+    g.handle = h;
+  }
+  *api = g;
+  return 0;
+}
+}  // namespace
+
+extern "C" int grlcu_device_count(void)
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+constexpr int kResultWords = 7;    // 8-byte words per agent in the gather: the seven grlcu_results fields
+
+struct grlcu_group
+{
+  std::vector<grlcu_ctx *> ctxs;
+  std::vector<ncclComm_t> comms;
+  std::vector<uint64_t *> send, recv;      // per context: [kResultWords][n] and [n_ctx][kResultWords][n]
+  std::vector<uint64_t> host;              // pinned-size staging of one recv buffer
+  NcclApi nccl;
+  int n;                                   // agents per context
+};
+
+// the seven per-agent result arrays of one context as rows of 8-byte words (episodes widened)
+__global__ void k_pack_results(Params p, uint64_t *out)
+{
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= p.n) return;
+  const size_t n = (size_t)p.n;
+  out[0 * n + a] = (uint64_t)__double_as_longlong(p.last_return[a]);
+  out[1 * n + a] = (uint64_t)__double_as_longlong(p.last_test_return[a]);
+  out[2 * n + a] = (uint64_t)__double_as_longlong(p.return_sum[a]);
+  out[3 * n + a] = p.ss[a];
+  out[4 * n + a] = (uint64_t)p.episodes[a];
+  out[5 * n + a] = p.swept[a];
+  out[6 * n + a] = p.tblw[a];
+}
+
+extern "C" int grlcu_group_create(grlcu_ctx *const *ctxs, int32_t n_ctx, grlcu_group **out)
+{
+  if (!ctxs || n_ctx < 1 || !out) return fail(GRLCU_ERR_ARG, "grlcu_group_create: bad arguments");
+  *out = nullptr;
+  for (int i = 0; i < n_ctx; ++i)
+  {
+    if (!ctxs[i]) return fail(GRLCU_ERR_ARG, "grlcu_group_create: null context");
+    if (ctxs[i]->p.n != ctxs[0]->p.n) return fail(GRLCU_ERR_ARG, "grlcu_group_create: every context must hold the same number of agents");
+    for (int j = 0; j < i; ++j)
+      if (ctxs[j]->device == ctxs[i]->device) return fail(GRLCU_ERR_ARG, "grlcu_group_create: two contexts on device %d", ctxs[i]->device);
+  }
+  grlcu_group *g = new (std::nothrow) grlcu_group();
+  if (!g) return fail(GRLCU_ERR_NOMEM, "out of host memory");
+  g->ctxs.assign(ctxs, ctxs + n_ctx);
+  g->n = ctxs[0]->p.n;
+  g->send.assign(n_ctx, nullptr); g->recv.assign(n_ctx, nullptr);
+  const size_t words = (size_t)kResultWords * g->n;
+  int r = 0;
+  for (int i = 0; i < n_ctx && !r; ++i)
+  {
+    if (cudaSetDevice(ctxs[i]->device) != cudaSuccess) { r = fail(GRLCU_ERR_CUDA, "cudaSetDevice failed"); break; }
+    if (cudaMalloc(&g->send[i], words * sizeof(uint64_t)) != cudaSuccess ||
+        cudaMalloc(&g->recv[i], words * n_ctx * sizeof(uint64_t)) != cudaSuccess)
+      r = fail(GRLCU_ERR_NOMEM, "grlcu_group_create: out of device memory");
+  }
+  if (!r && n_ctx > 1)
+  {
+    r = load_nccl(&g->nccl);
+    if (!r)
+    {
+      std::vector<int> devs(n_ctx);
+      for (int i = 0; i < n_ctx; ++i) devs[i] = ctxs[i]->device;
+      g->comms.assign(n_ctx, nullptr);
+      ncclResult_t e = g->nccl.CommInitAll(g->comms.data(), n_ctx, devs.data());
+      if (e != ncclSuccess) { g->comms.clear(); r = fail(GRLCU_ERR_CUDA, "ncclCommInitAll failed: %s", g->nccl.GetErrorString(e)); }
+    }
+  }
+  g->host.resize(words * n_ctx);
+  if (r) { grlcu_group_destroy(g); return r; }
+  *out = g;
+  return 0;
+}
+
+extern "C" int grlcu_group_destroy(grlcu_group *g)
+{
+  if (!g) return 0;
+  for (size_t i = 0; i < g->ctxs.size(); ++i)
+  {
+    cudaSetDevice(g->ctxs[i]->device);
+    cudaStreamSynchronize(g->ctxs[i]->stream);
+    if (i < g->comms.size() && g->comms[i]) g->nccl.CommDestroy(g->comms[i]);
+    if (g->send[i]) cudaFree(g->send[i]);
+    if (g->recv[i]) cudaFree(g->recv[i]);
+  }
+  delete g;
+  return 0;
+}
+
+extern "C" int grlcu_group_run(grlcu_group *g, int64_t n_steps)
+{
+  if (!g) return fail(GRLCU_ERR_ARG, "null group");
+  for (grlcu_ctx *c : g->ctxs)
+    if (int r = grlcu_run(c, n_steps, 0)) return r;       // asynchronous: the devices run concurrently
+  return 0;
+}
+
+extern "C" int grlcu_group_results(grlcu_group *g, grlcu_results *res, double *collective_ms)
+{
+  if (!g || !res) return fail(GRLCU_ERR_ARG, "grlcu_group_results: bad arguments");
+  const int G = (int)g->ctxs.size(), n = g->n;
+  const size_t words = (size_t)kResultWords * n;
+  for (int i = 0; i < G; ++i)
+  {
+    grlcu_ctx *c = g->ctxs[i];
+    CU(cudaSetDevice(c->device));
+    k_pack_results<<<(n + 255) / 256, 256, 0, c->stream>>>(c->p, g->send[i]);
+    c->launches++;
+    CU(cudaGetLastError());
+  }
+  const uint64_t *src = g->send[0];
+  if (collective_ms) *collective_ms = 0;
+  if (G > 1)
+  {
+    // the job's only collective: every GPU receives every GPU's block (NVLink / NVSwitch)
+    cudaEvent_t e0, e1;
+    CU(cudaSetDevice(g->ctxs[0]->device));
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    for (int i = 0; i < G; ++i) { CU(cudaSetDevice(g->ctxs[i]->device)); CU(cudaStreamSynchronize(g->ctxs[i]->stream)); }
+    CU(cudaSetDevice(g->ctxs[0]->device));
+    CU(cudaEventRecord(e0, g->ctxs[0]->stream));
+    ncclResult_t e = g->nccl.GroupStart();
+    for (int i = 0; i < G && e == ncclSuccess; ++i)
+    {
+      CU(cudaSetDevice(g->ctxs[i]->device));
+      e = g->nccl.AllGather(g->send[i], g->recv[i], words, ncclUint64, g->comms[i], g->ctxs[i]->stream);
+    }
+    if (e == ncclSuccess) e = g->nccl.GroupEnd();
+    if (e != ncclSuccess) return fail(GRLCU_ERR_CUDA, "ncclAllGather failed: %s", g->nccl.GetErrorString(e));
+    CU(cudaSetDevice(g->ctxs[0]->device));
+    CU(cudaEventRecord(e1, g->ctxs[0]->stream));
+    for (int i = 0; i < G; ++i) { CU(cudaSetDevice(g->ctxs[i]->device)); CU(cudaStreamSynchronize(g->ctxs[i]->stream)); }
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    if (collective_ms) *collective_ms = ms;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    src = g->recv[0];
+  }
+  CU(cudaSetDevice(g->ctxs[0]->device));
+  CU(cudaMemcpyAsync(g->host.data(), src, words * G * sizeof(uint64_t), cudaMemcpyDeviceToHost, g->ctxs[0]->stream));
+  CU(cudaStreamSynchronize(g->ctxs[0]->stream));
+  for (int i = 0; i < G; ++i)
+  {
+    const uint64_t *blk = g->host.data() + (size_t)i * words;
+    const size_t o = (size_t)i * n;
+    auto f64 = [&](double *dst, int row) { if (dst) memcpy(dst + o, blk + (size_t)row * n, sizeof(double) * n); };
+    auto u64 = [&](uint64_t *dst, int row) { if (dst) memcpy(dst + o, blk + (size_t)row * n, sizeof(uint64_t) * n); };
+    f64(res->last_return, 0); f64(res->last_test_return, 1); f64(res->return_sum, 2);
+    u64(res->steps, 3); u64(res->swept, 5); u64(res->table_writes, 6);
+    if (res->episodes) for (int a = 0; a < n; ++a) res->episodes[o + a] = (uint32_t)blk[(size_t)4 * n + a];
+  }
   return 0;
 }

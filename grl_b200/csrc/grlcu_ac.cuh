@@ -171,7 +171,7 @@ __device__ __forceinline__ void ac_core(const Params &p, const ACParams &ac, Age
 // One loop iteration is an episode start (no step consumed) or one environment step + TDAgent::step/end.
 template <int DYN, int T, bool CACHED, int MINB>
 __global__ void __launch_bounds__(kMaxBlock, MINB)
-k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps, int do_open, int do_close)
+k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps, int do_close)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
   __shared__ uint32_t s_idx[T][kMaxBlock];
@@ -184,8 +184,8 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
   double *actor = ac.actor + (size_t)a * p.tstride;
   const uint64_t gid = (uint64_t)(p.first_id + a);
   Cache<T> c;
-  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
-  if (CACHED && do_open) cache_open<DYN, T>(p, ag, c, critic);
+  c.bind(p, a);
+  if (CACHED && !(ag.flags & 16)) { cache_open<DYN, T>(p, ag, c, critic); ag.flags |= 16; }
   ACOut o;
   double noise, qp, target, delta;
   int swept;
@@ -221,7 +221,7 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
         else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
       }
       ag.total_reward = 0;
-      ag.flags = 1 | (test ? 2 : 0);
+      ag.flags = (ag.flags & 16) | 1 | (test ? 2 : 0);
     }
     else
     {
@@ -245,7 +245,7 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
       ++step;
     }
   }
-  if (CACHED && do_close) cache_close<DYN, T>(p, ag, c, critic);
+  if (CACHED && do_close) { cache_close<DYN, T>(p, ag, c, critic); ag.flags &= ~16; }
   ag.store(p, a);
 }
 
@@ -282,7 +282,7 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
     observe<DYN>(ag.x, p.timeout, obs0, term0, p.end_stop_penalty);
     if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
     ag.total_reward = 0;
-    ag.flags = 1 | (test ? 2 : 0);
+    ag.flags = (ag.flags & 16) | 1 | (test ? 2 : 0);
     ac_core<DYN, T, false>(p, ac, ag, Cache<T>(), critic, actor, sid, a, gid, obs0, 0., true, false, test, true,
                            io.start_u[a], nullptr, nullptr, o, noise, qp, target, delta, swept);
     if (io.o_start_q) { io.o_start_q[a] = o.pi; io.o_start_q[(size_t)3 * n + a] = o.action; }

@@ -66,14 +66,16 @@ struct Params
   uint32_t *prev_idx, *trace_idx;
   int32_t  *trace_len, *trace_head;
   double   *total_decay;
-  int32_t  *flags;            // bit0 in_episode, bit1 test, bit2 start override pending, bit3 prev projection has duplicate indices
+  int32_t  *flags;            // bit0 in_episode, bit1 test, bit2 start override pending, bit3 prev projection has duplicate indices,
+                              // bit4 the agent's trace value cache is live (its table holds directory sentinels, grlcu_cached.cuh)
   uint64_t *dupmask;          // bit k: trace entry of age k holds duplicate indices (fast paths: cap <= 64)
   int32_t  force_slow;        // 1: always take the sequential update path (A/B testing)
   int32_t  mode;              // 0: trace value cache where eligible, 1: uncached
   int32_t  target_kind;       // bootstrap value: 0 Q(s',a') (SARSA), 1 max_a Q(s',a) (Q-learning), 2 policy value (expected SARSA)
   double   target_epsilon;    // expected SARSA: target policy's epsilon (< 0: greedy sampler)
   double   softmax_tau;       // > 0: the learning policy's sampler is sampler/softmax with this temperature
-  double   *cache_val;        // [cap*T][n] cached trace weights (grlcu_cached.cuh)
+  double   *cache_val;        // [n / cblock][cap*T][cblock] cached trace weights (grlcu_cached.cuh): one contiguous block per cohort
+  uint32_t cblock;            // agents per block of cache_val (= the launch cohort, so that a cohort's cache is one address range)
   uint32_t *cache_mask;       // [cap][n] valid bits per trace entry
   uint64_t *act_ctr, *test_act_ctr, *episode_ctr, *tt, *ss, *swept;
   uint64_t *tblw;             // random 8-byte table stores issued (roofline accounting)
@@ -277,7 +279,7 @@ struct Agent
   // online_learning.cpp:223-262 bookkeeping at the end of an episode
   __device__ __forceinline__ void episode_end(const Params &p, int a, bool test)
   {
-    flags = 0;
+    flags &= 16;
     p.tt[a] += 1;
     p.episodes[a] += 1;
     if (test) p.last_test_return[a] = total_reward;

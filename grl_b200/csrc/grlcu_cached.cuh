@@ -41,7 +41,14 @@ struct Cache
   uint32_t *vmask;   // + a
   uint32_t *ring;    // trace_idx + a
   uint32_t  n;       // element indices fit 32 bits: trace_cap * T * n < 2^31 is checked by grlcu_create
-  __device__ __forceinline__ double &val(int slot) const { return cv[(uint32_t)slot * n]; }
+  uint32_t  cn;      // stride of cv (agents per cache block)
+  __device__ __forceinline__ void bind(const Params &p, int a)
+  {
+    const uint32_t blk = (uint32_t)a / p.cblock;
+    cv = p.cache_val + (size_t)blk * ((size_t)p.trace_cap * T) * p.cblock + ((uint32_t)a - blk * p.cblock);
+    vmask = p.cache_mask + a; ring = p.trace_idx + a; n = (uint32_t)p.n; cn = p.cblock;
+  }
+  __device__ __forceinline__ double &val(int slot) const { return cv[(uint32_t)slot * cn]; }
   __device__ __forceinline__ uint32_t &mask(int pos) const { return vmask[(uint32_t)pos * n]; }
   __device__ __forceinline__ uint32_t &idx(int pos, int j) const { return ring[(uint32_t)(pos * T + j) * n]; }
 };

@@ -203,7 +203,7 @@ __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag
     else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
   }
   ag.total_reward = 0;
-  ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
+  ag.flags = (ag.flags & 16) | 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
   double qp, target, delta; int swept;
   const int ai = agent_core<DYN, T, A, CACHED, GEO>(p, ag, c, tbl, sid, a, obs, 0., true, false, test, d, -1, nullptr, nullptr, o_q,
                                                     qp, target, delta, swept);
@@ -231,7 +231,7 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, co
 // MINB = 4 instantiation, which may use up to 255 registers and does not spill.
 template <int DYN, int T, int A, bool CACHED, int MINB, bool GEO>
 __global__ void __launch_bounds__(kMaxBlock, MINB)
-k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, int do_close)
+k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_close)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
   __shared__ uint32_t s_idx[A * T][kMaxBlock];
@@ -243,8 +243,9 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
   double *tbl = p.table + (size_t)a * p.tstride;
   const uint64_t gid = (uint64_t)(p.first_id + a);
   Cache<T> c;
-  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
-  if (CACHED && do_open) cache_open<DYN, T>(p, ag, c, tbl);
+  c.bind(p, a);
+  // the cache stays live between launches, agent by agent (flags bit4): values return to the tables lazily
+  if (CACHED && !(ag.flags & 16)) { cache_open<DYN, T>(p, ag, c, tbl); ag.flags |= 16; }
 
   // One loop iteration is either an episode start (observe the start state, first action; consumes no step) or
   // one environment step + TDAgent::step/end.  Both go through the single agent_core call below.
@@ -280,7 +281,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
         else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
       }
       ag.total_reward = 0;
-      ag.flags = 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
+      ag.flags = (ag.flags & 16) | 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
     }
     else
     {
@@ -309,7 +310,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_open, in
       ++step;
     }
   }
-  if (CACHED && do_close) cache_close<DYN, T>(p, ag, c, tbl);
+  if (CACHED && do_close) { cache_close<DYN, T>(p, ag, c, tbl); ag.flags &= ~16; }
   ag.store(p, a);
 }
 
@@ -320,11 +321,13 @@ __global__ void k_cache_close(Params p)
 {
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= p.n) return;
+  if (!(p.flags[a] & 16)) return;
   Agent<DYN, T> ag;
   ag.load(p, a);
   Cache<T> c;
-  c.cv = p.cache_val + a; c.vmask = p.cache_mask + a; c.ring = p.trace_idx + a; c.n = (uint32_t)p.n;
+  c.bind(p, a);
   cache_close<DYN, T>(p, ag, c, p.table + (size_t)a * p.tstride);
+  ag.flags &= ~16;
   ag.store(p, a);
 }
 

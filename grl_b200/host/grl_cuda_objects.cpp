@@ -220,7 +220,8 @@ void CudaLinearRepresentation::reconfigure(const Configuration &config)
   const std::string action = config["action"].str();
   if (action == "reset")
   {
-    if (path_->ctx && !actor_) CudaPath::check(grlcu_reset(path_->ctx, GRLCU_RESET_TABLES));   // resets both tables of an AC context
+    if (path_->ctx && !actor_)
+      for (grlcu_ctx *c : path_->ctxs) CudaPath::check(grlcu_reset(c, GRLCU_RESET_TABLES));   // resets both tables of an AC context
     return;
   }
   if (action != "save" && action != "load") return;
@@ -234,9 +235,11 @@ void CudaLinearRepresentation::reconfigure(const Configuration &config)
   for (int a = 0; a < count; ++a)
   {
     const std::string file = base + cfg_path + (a ? "-agent" + std::to_string(a) : std::string()) + ".dat";
+    int local = 0;
+    grlcu_ctx *ctx = path_->contextOf(a, &local);
     if (action == "save")
     {
-      CudaPath::check((actor_ ? grlcu_get_actor_table : grlcu_get_table)(path_->context(), a, p.data()));
+      CudaPath::check((actor_ ? grlcu_get_actor_table : grlcu_get_table)(ctx, local, p.data()));
       FILE *f = fopen(file.c_str(), "wb");
       if (!f) { WARNING("Could not open '" << file << "' for writing"); return; }
       fwrite(p.data(), sizeof(double), p.size(), f);
@@ -251,7 +254,7 @@ void CudaLinearRepresentation::reconfigure(const Configuration &config)
       fseek(f, 0, SEEK_SET);
       if (fread(p.data(), sizeof(double), p.size(), f) != p.size()) { WARNING("Could not read '" << file << "'"); fclose(f); return; }
       fclose(f);
-      CudaPath::check((actor_ ? grlcu_set_actor_table : grlcu_set_table)(path_->context(), a, p.data()));
+      CudaPath::check((actor_ ? grlcu_set_actor_table : grlcu_set_table)(ctx, local, p.data()));
     }
   }
 }

@@ -32,7 +32,12 @@ void OnlineLearningExperiment::request(ConfigurationRequest *config)
   // new on the batched path
   config->push_back(CRP("agents", "Independent agents learning side by side on the GPU (per run)", agents_, CRP::Configuration, 1));
   config->push_back(CRP("steps_per_launch", "Agent-steps per agent between two reports", steps_per_launch_, CRP::Configuration, 1));
-  config->push_back(CRP("device", "CUDA device ordinal", device_, CRP::Configuration, 0));
+  // Several GPUs of one box (what MultiExperiment's instances on threads are to the reference, experiments/multi.cpp:44-75):
+  // the agents are sharded over `devices` in contiguous ranges of global agent ids, one context per device, and the
+  // per-agent results are all-gathered over NCCL before every report.  Results are keyed by global agent id, so the
+  // output does not depend on the number of devices.
+  config->push_back(CRP("device", "CUDA device ordinal (-1: every visible device whose count divides `agents`)", device_, CRP::Configuration, -1));
+  config->push_back(CRP("devices", "CUDA device ordinals to shard the agents over (overrides `device`)", Vector(), CRP::Configuration));
   // Hyper-parameter grid on the agents axis: what MultiExperiment `instances` (experiments/multi.cpp:38-60) and a
   // grlo `parameters` list (bin/optimize.yaml) do with one process per setting.  For the agent with global id g:
   // lambda is constant over blocks of 32 consecutive agents (a warp sweeps as long as its longest trace), block
@@ -53,6 +58,9 @@ void OnlineLearningExperiment::configure(Configuration &config)
   rate_ = config["rate"]; test_interval_ = config["test_interval"]; test_trials_ = config["test_trials"];
   output_ = config["output"].str(); load_file_ = config["load_file"].str(); save_every_ = config["save_every"].str();
   agents_ = config["agents"]; steps_per_launch_ = config["steps_per_launch"]; device_ = config["device"];
+  devices_ = config["devices"].v();
+  for (double d : devices_) if (d < 0 || d != floor(d)) throw bad_param("experiment/online_learning:devices");
+  if (!devices_.empty() && agents_ % (int)devices_.size()) throw bad_param("experiment/online_learning:{agents,devices}");
   sweep_alpha_ = config["sweep_alpha"].v(); sweep_lambda_ = config["sweep_lambda"].v(); sweep_epsilon_ = config["sweep_epsilon"].v();
   for (double v : sweep_alpha_) if (!(v > 0)) throw bad_param("experiment/online_learning:sweep_alpha");
   for (double v : sweep_lambda_) if (!(v >= 0 && v <= 1)) throw bad_param("experiment/online_learning:sweep_lambda");
@@ -181,7 +189,9 @@ void OnlineLearningExperiment::assemble()
   c.test_interval = test_interval_;
   c.seed = seed;
   path_.agents = agents_;
-  path_.device = device_;
+  path_.device = device_ < 0 ? 0 : device_;
+  path_.devices.clear();
+  for (double d : devices_) path_.devices.push_back((int)d);
   assembled_ = true;
 }
 
@@ -205,7 +215,16 @@ std::vector<double> OnlineLearningExperiment::run()
     // every run is a fresh set of agents with its own Philox streams (global agent ids rr*agents ...)
     path_.release();
     path_.first_agent_id = (long long)rr * agents_;
-    grlcu_ctx *ctx = path_.context();
+    if (devices_.empty() && device_ < 0)
+    {
+      // default: every visible device, as many as divide the agents evenly
+      int G = std::max(1, grlcu_device_count());
+      while (G > 1 && agents_ % G) --G;
+      path_.devices.clear();
+      for (int g = 0; g < G; ++g) path_.devices.push_back(g);
+    }
+    path_.context();
+    const int per = path_.perContext();
     const size_t na = std::max<size_t>(sweep_alpha_.size(), 1), nl = std::max<size_t>(sweep_lambda_.size(), 1),
                  ne = std::max<size_t>(sweep_epsilon_.size(), 1), cells = na * nl * ne;
     const bool sweeping = !sweep_alpha_.empty() || !sweep_lambda_.empty() || !sweep_epsilon_.empty();
@@ -223,7 +242,8 @@ std::vector<double> OnlineLearningExperiment::run()
         la[a] = sweep_lambda_.empty() ? path_.cfg.lambda : sweep_lambda_[il];
         ep[a] = sweep_epsilon_.empty() ? path_.cfg.epsilon : sweep_epsilon_[ie];
       }
-      CudaPath::check(grlcu_set_hyper(ctx, al.data(), la.data(), ep.data()));
+      for (size_t g = 0; g < path_.ctxs.size(); ++g)
+        CudaPath::check(grlcu_set_hyper(path_.ctxs[g], al.data() + g * per, la.data() + g * per, ep.data() + g * per));
     }
     std::ofstream ofs, cfs;
     if (!output_.empty())
@@ -258,8 +278,10 @@ std::vector<double> OnlineLearningExperiment::run()
     }
     for (;;)
     {
-      CudaPath::check(grlcu_run(ctx, steps_per_launch_, 0));
-      CudaPath::check(grlcu_get_results(ctx, &res));
+      CudaPath::check(grlcu_group_run(path_.group, steps_per_launch_));
+      double collective_ms = 0;
+      CudaPath::check(grlcu_group_results(path_.group, &res, &collective_ms));   // the only collective: NCCL all-gather
+      collective_ms_total_ += collective_ms;
       const uint64_t min_ss = *std::min_element(ss.begin(), ss.end());
       const uint32_t min_tt = *std::min_element(episodes.begin(), episodes.end());
       const std::vector<double> &r = test_interval_ >= 0 ? last_test : last_return;

@@ -267,13 +267,45 @@ grlcu_ctx *CudaPath::context()
   if (!have_env || !have_projector || !have_representation || !have_predictor)
     throw Exception("CUDA path used before environment/model/cuda_batched, projector/tile_coding/cuda, "
                     "representation/linear/cuda and predictor/sarsa/cuda were all configured in one experiment");
-  check(grlcu_create(&cfg, agents, first_agent_id, device, nullptr, &ctx));
+  // Agents shard trivially over the devices: device g owns the global ids [first + g*agents/G, first + (g+1)*agents/G)
+  std::vector<int> devs = devices.empty() ? std::vector<int>{device} : devices;
+  const int G = (int)devs.size();
+  if (agents % G) throw Exception("`agents` must be a multiple of the number of devices");
+  const int per = agents / G;
+  try
+  {
+    for (int g = 0; g < G; ++g)
+    {
+      grlcu_ctx *c = nullptr;
+      check(grlcu_create(&cfg, per, first_agent_id + (long long)g * per, devs[g], nullptr, &c));
+      ctxs.push_back(c);
+    }
+    check(grlcu_group_create(ctxs.data(), G, &group));
+  }
+  catch (...)
+  {
+    release();
+    throw;
+  }
+  ctx = ctxs[0];
   return ctx;
+}
+
+grlcu_ctx *CudaPath::contextOf(int agent, int *local)
+{
+  context();
+  const int per = agents / (int)ctxs.size();
+  if (agent < 0 || agent >= agents) throw Exception("agent index out of range");
+  *local = agent % per;
+  return ctxs[agent / per];
 }
 
 void CudaPath::release()
 {
-  if (ctx) grlcu_destroy(ctx);
+  if (group) grlcu_group_destroy(group);
+  group = nullptr;
+  for (grlcu_ctx *c : ctxs) grlcu_destroy(c);
+  ctxs.clear();
   ctx = nullptr;
 }
 

@@ -174,13 +174,18 @@ struct FixedAgent : Agent
 struct CudaPath
 {
   grlcu_config cfg;
-  grlcu_ctx *ctx = nullptr;
+  grlcu_ctx *ctx = nullptr;              ///< the first context (global agent ids start here): the one-agent role interfaces use it
+  std::vector<grlcu_ctx *> ctxs;         ///< one context per device, contiguous ranges of global agent ids
+  grlcu_group *group = nullptr;          ///< drives the contexts together; the one collective (NCCL all-gather of results)
+  std::vector<int> devices;              ///< CUDA device ordinals; empty: {device}
   int agents = 1, device = 0;
   long long first_agent_id = 0;
   bool have_env = false, have_projector = false, have_representation = false, have_predictor = false;
   CudaPath();
   ~CudaPath();
-  grlcu_ctx *context();                  ///< creates the context on first use; throws grl::Exception
+  grlcu_ctx *context();                  ///< creates the contexts on first use; throws grl::Exception
+  grlcu_ctx *contextOf(int agent, int *local);   ///< context and index within it of agent `agent` of this run
+  int perContext() { context(); return agents / (int)ctxs.size(); }
   void release();
   static void check(int rc);             ///< non-zero C-ABI return -> grl::Exception(grlcu_last_error())
 };
@@ -329,19 +334,22 @@ class OnlineLearningExperiment : public Experiment
     /// The C-ABI configuration this experiment resolves to (no device needed): used by --check and tests.
     const grlcu_config &resolved() { assemble(); return path_.cfg; }
     int agents() const { return agents_; }
+    double collectiveMs() const { return collective_ms_total_; }   ///< device time spent in the NCCL all-gathers of run()
     CudaPath &cudaPath() { return path_; }
     unsigned long long seed = 1;
     std::string identity;
   private:
     void assemble();
     int runs_ = 1, run_offset_ = 0, trials_ = 0, steps_ = 0, rate_ = 0, test_interval_ = -1, test_trials_ = 1;
-    int agents_ = 1, steps_per_launch_ = 100, device_ = 0;
+    int agents_ = 1, steps_per_launch_ = 100, device_ = -1;
+    Vector devices_;                                       // CUDA devices the agents are sharded over (empty: see configure)
     std::string output_, load_file_, save_every_ = "never";
     Environment *environment_ = nullptr; Agent *agent_ = nullptr, *test_agent_ = nullptr;
     CudaPath path_;
     Vector sweep_alpha_, sweep_lambda_, sweep_epsilon_;   // hyper-parameter grid over the agents axis (MultiExperiment / grlo)
     std::vector<Representation *> checkpoint_reps_;     // tables written by save_every / read by load_file
     bool assembled_ = false;
+    double collective_ms_total_ = 0;
 };
 
 }  // namespace grl

@@ -228,6 +228,25 @@ int grlcu_set_actor_table(grlcu_ctx *ctx, int32_t agent, const double *in);
 /* Environment state ([S]) and pending action of one agent. */
 int grlcu_get_state(grlcu_ctx *ctx, int32_t agent, double *state, double *action, int32_t *in_episode);
 
+/* ---- several GPUs of one box ---------------------------------------------------------------------------------
+ * One job = one context per GPU, each owning a contiguous range of global agent ids (the agents never exchange
+ * anything while they learn).  A group drives the contexts together from one host thread (launches are
+ * asynchronous, so the GPUs run concurrently) and performs the job's ONLY collective: an all-gather of the
+ * per-agent results over NCCL (NVLink/NVSwitch), after which every GPU -- and the host, from the first context's
+ * device -- holds the results of all agents in global id order.  libnccl.so.2 is loaded on first use; a group of
+ * one context never touches NCCL.  All contexts must hold the same number of agents.
+ * Replaces: MultiExperiment's role as "many independent runs at once" (experiments/multi.cpp:44-75: N instances on
+ * N threads of one process) for the batched path. */
+typedef struct grlcu_group grlcu_group;
+int grlcu_device_count(void);                     /* usable CUDA devices (0 when there is none) */
+int grlcu_group_create(grlcu_ctx *const *ctxs, int32_t n_ctx, grlcu_group **out);
+int grlcu_group_destroy(grlcu_group *group);       /* does not destroy the contexts */
+/* grlcu_run on every context (cohort 0). */
+int grlcu_group_run(grlcu_group *group, int64_t n_steps);
+/* Per-agent results of ALL agents of the group (host arrays of n_ctx * n_agents, context order = global id order).
+ * collective_ms (may be NULL): device time of the all-gather alone, CUDA events on the first context's stream. */
+int grlcu_group_results(grlcu_group *group, grlcu_results *results, double *collective_ms);
+
 /* Trace capacity (entries) the context allocated per agent. */
 int grlcu_trace_capacity(grlcu_ctx *ctx);
 /* Counters for the roofline: launches of our kernels so far, and kernel name list. */

@@ -24,7 +24,7 @@ for w in ${NCU_WORKLOADS:-pendulum cart_pole cart_double_pole_ac}; do
     echo "# (tools/gpu_evidence.sh, TAG=$TAG; one launch = 100 agent-steps per agent; times under ncu are not bench values)"
     python tools/ncu_summary.py gpurun_out/prof_${TAG}_$w.ncu-rep
     echo; echo "# per source line (tools/ncu_by_line.py)"
-    python tools/ncu_by_line.py gpurun_out/prof_${TAG}_$w.ncu-rep grl_b200/csrc/libgrlcu.so $k 25 2>&1
+    python tools/ncu_by_line.py gpurun_out/prof_${TAG}_$w.ncu-rep grl_b200/csrc/libgrlcu.so 25 2>&1
   } > gpurun_out/ncu_${TAG}_$w.txt
   [ "$KEEP_REP" = "$w" ] || rm -f gpurun_out/prof_${TAG}_$w.ncu-rep
 done

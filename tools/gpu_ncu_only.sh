@@ -11,7 +11,7 @@ for w in ${NCU_WORKLOADS:-sweep pendulum_ac cart_pole_ac}; do
     echo "# (tools/gpu_ncu_only.sh, TAG=$TAG; one launch = 100 agent-steps per agent; times under ncu are not bench values)"
     python tools/ncu_summary.py gpurun_out/prof_${TAG}_$w.ncu-rep
     echo; echo "# per source line (tools/ncu_by_line.py)"
-    python tools/ncu_by_line.py gpurun_out/prof_${TAG}_$w.ncu-rep grl_b200/csrc/libgrlcu.so $k 25 2>&1
+    python tools/ncu_by_line.py gpurun_out/prof_${TAG}_$w.ncu-rep grl_b200/csrc/libgrlcu.so 25 2>&1
   } > gpurun_out/ncu_${TAG}_$w.txt
   rm -f gpurun_out/prof_${TAG}_$w.ncu-rep
   echo "$w done"
