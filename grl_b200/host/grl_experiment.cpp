@@ -13,6 +13,7 @@
 namespace grl {
 
 REGISTER_CONFIGURABLE(OnlineLearningExperiment)
+REGISTER_CONFIGURABLE(MultiExperiment)
 
 void OnlineLearningExperiment::request(ConfigurationRequest *config)
 {
@@ -69,7 +70,11 @@ void OnlineLearningExperiment::configure(Configuration &config)
   if (agents_ < 1) throw bad_param("experiment/online_learning:agents");
   if (steps_per_launch_ < 1) throw bad_param("experiment/online_learning:steps_per_launch");
   if (test_trials_ != 1) throw bad_param("experiment/online_learning:test_trials");
-  if (save_every_ != "never" && save_every_ != "run") throw bad_param("experiment/online_learning:save_every");
+  // online_learning.cpp:62: {"never", "run", "test", "trial"}.  On the batched path a report (every steps_per_launch
+  // agent-steps) is the unit of progress: "trial" saves after every report, "test" after every report once the agents
+  // have finished a new test episode, into `output`-run<r>-trial<min finished episodes>-...
+  if (save_every_ != "never" && save_every_ != "run" && save_every_ != "test" && save_every_ != "trial")
+    throw bad_param("experiment/online_learning:save_every");
   if (test_interval_ >= 0 && !test_agent_) throw bad_param("experiment/online_learning:test_agent");
 }
 
@@ -261,11 +266,16 @@ std::vector<double> OnlineLearningExperiment::run()
       }
     }
     size_t report = 0;
+    uint32_t saved_tests = 0;
     if (!load_file_.empty())
     {
       Configuration loadconfig;
       loadconfig.set("action", "load");
-      loadconfig.set("file", load_file_ + "-");
+      // online_learning.cpp:141-150: `load_file` + "-", with "$run" replaced by the run number
+      std::string load_file = load_file_ + "-";
+      for (size_t at = load_file.find("$run"); at != std::string::npos; at = load_file.find("$run", at))
+        load_file.replace(at, 4, std::to_string(rr));
+      loadconfig.set("file", load_file);
       loadconfig.set("agents", agents_);
       for (Representation *r : checkpoint_reps_) r->reconfigure(loadconfig);
     }
@@ -314,6 +324,19 @@ std::vector<double> OnlineLearningExperiment::run()
               << pct(0.9) << std::endl;
         }
       }
+      // online_learning.cpp:281-291: save the policy every trial / every test trial
+      const bool new_test = test_interval_ >= 0 && min_tt / (uint32_t)(test_interval_ + 1) > saved_tests;
+      if ((save_every_ == "trial" || (save_every_ == "test" && new_test)) && !output_.empty())
+      {
+        saved_tests = min_tt / (uint32_t)(test_interval_ >= 0 ? test_interval_ + 1 : 1);
+        std::ostringstream soss;
+        soss << output_ << "-run" << rr << "-trial" << min_tt << "-";
+        Configuration saveconfig;
+        saveconfig.set("action", "save");
+        saveconfig.set("file", soss.str());
+        saveconfig.set("agents", agents_);
+        for (Representation *r : checkpoint_reps_) r->reconfigure(saveconfig);
+      }
       ++report;
       if ((steps_ && min_ss >= (uint64_t)steps_) || (trials_ && min_tt >= (uint32_t)trials_)) break;
     }
@@ -336,6 +359,38 @@ std::vector<double> OnlineLearningExperiment::run()
     }
   }
   return curve;
+}
+
+}  // namespace grl
+
+namespace grl {
+
+void MultiExperiment::request(ConfigurationRequest *config)
+{
+  config->push_back(CRP("instances", "Number of experiments to run in parallel", instances_, CRP::Configuration, 1));
+  config->push_back(CRP("experiment", "experiment", "Experiment to run", prototype_));
+}
+
+void MultiExperiment::configure(Configuration &config)
+{
+  instances_ = config["instances"];
+  prototype_ = dynamic_cast<OnlineLearningExperiment *>(config["experiment"].ptr());
+  if (instances_ < 1) throw bad_param("experiment/multi:instances");
+  if (!prototype_) throw Exception(path() + ": experiment must be an experiment/online_learning");
+  // Every clone must own its tables (see the class comment): the policy has to be configured inside the prototype.
+  Agent *agent = prototype_->agent();
+  const std::string inside = prototype_->path() + "/";
+  if (!agent || !agent->policy || agent->policy->path().compare(0, inside.size(), inside) != 0)
+    throw Exception(path() + ": the instances share one policy (" + (agent && agent->policy ? agent->policy->path() : std::string("?")) +
+                    " lies outside " + prototype_->path() + "): the reference's clones would then update ONE table from several "
+                    "threads without synchronisation (cfg/pendulum/multi_sarsa_tc.yaml), which is not what independent agents "
+                    "compute.  Configure the policy inside the experiment, or use `agents` / `sweep_*` of experiment/online_learning");
+  prototype_->setAgents(instances_ * prototype_->agents());
+}
+
+std::vector<double> MultiExperiment::run()
+{
+  return prototype_->run();
 }
 
 }  // namespace grl

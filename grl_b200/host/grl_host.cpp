@@ -1,6 +1,9 @@
 // grl_host.cpp -- registry, YAML-subset reader and configurator behind grl_host.h.
 #include "grl_host.h"
 
+#include <dlfcn.h>
+#include <glob.h>
+
 #include <algorithm>
 #include <cmath>
 #include <fstream>
@@ -190,16 +193,41 @@ Configurator::~Configurator()
   for (auto it = objects_.rbegin(); it != objects_.rend(); ++it) delete it->second;
 }
 
-Configurable *Configurator::object(const std::string &path) const
+int loadPlugins(const std::string &dir)
 {
+  glob_t globbuf;
+  int loaded = 0;
+  const std::string pattern = dir + "/libaddon*.so";
+  NOTICE("Looking for plugins in '" << pattern << "'");
+  if (glob(pattern.c_str(), 0, nullptr, &globbuf) == 0)
+  {
+    for (size_t ii = 0; ii < globbuf.gl_pathc; ++ii)
+    {
+      NOTICE("Loading plugin '" << globbuf.gl_pathv[ii] << "'");
+      if (!dlopen(globbuf.gl_pathv[ii], RTLD_NOW | RTLD_GLOBAL))
+        ERROR("Error loading plugin '" << globbuf.gl_pathv[ii] << "': " << dlerror());
+      else
+        ++loaded;
+    }
+    globfree(&globbuf);
+  }
+  return loaded;
+}
+
+Configurable *Configurator::object(const std::string &path_in) const
+{
+  // a leading '/' anchors the path at the root (configurable.cpp: absolute references, cfg/pendulum/multi_sarsa_tc.yaml);
+  // every path here is already root-relative
+  const std::string path = !path_in.empty() && path_in[0] == '/' ? path_in.substr(1) : path_in;
   auto it = by_path_.find(path);
   if (it != by_path_.end()) return it->second;
   auto jt = value_objects_.find(path);
   return jt == value_objects_.end() ? nullptr : jt->second;
 }
 
-bool Configurator::value(const std::string &path, std::string *out) const
+bool Configurator::value(const std::string &path_in, std::string *out) const
 {
+  const std::string path = !path_in.empty() && path_in[0] == '/' ? path_in.substr(1) : path_in;
   auto it = values_.find(path);
   if (it != values_.end()) { *out = it->second; return true; }
   // a path through a parameter that was itself given as a reference ("…/critic/projector/memory" where

@@ -157,6 +157,10 @@ class ConfigurableFactory
     static std::string expand(const std::string &type);
     static Configurable *create(const std::string &type);
 };
+/// dlopen (RTLD_NOW | RTLD_GLOBAL) every `libaddon*.so` in `dir` so that the static REGISTER_CONFIGURABLE objects of
+/// the addons register their types (reference: loadPlugins(), base/src/grl.cpp:73-111).  Returns the number loaded.
+int loadPlugins(const std::string &dir);
+
 #define REGISTER_CONFIGURABLE(subx) \
   static bool registered_##subx##__ = grl::ConfigurableFactory::add(subx::s_type(), []() -> grl::Configurable * { return new subx(); });
 

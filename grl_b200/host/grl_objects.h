@@ -334,6 +334,8 @@ class OnlineLearningExperiment : public Experiment
     /// The C-ABI configuration this experiment resolves to (no device needed): used by --check and tests.
     const grlcu_config &resolved() { assemble(); return path_.cfg; }
     int agents() const { return agents_; }
+    void setAgents(int n) { agents_ = n; assembled_ = false; }   ///< experiment/multi: instances on the agents axis
+    Agent *agent() const { return agent_; }
     double collectiveMs() const { return collective_ms_total_; }   ///< device time spent in the NCCL all-gathers of run()
     CudaPath &cudaPath() { return path_; }
     unsigned long long seed = 1;
@@ -350,6 +352,27 @@ class OnlineLearningExperiment : public Experiment
     std::vector<Representation *> checkpoint_reps_;     // tables written by save_every / read by load_file
     bool assembled_ = false;
     double collective_ms_total_ = 0;
+};
+
+/// experiment/multi (experiments/multi.cpp:38-75): the reference clones the prototype experiment `instances` times and
+/// runs the clones on threads.  On the batched path the instances become agents: the prototype runs once with
+/// instances x agents independent agents (instance i owns the agent ids [i*agents, (i+1)*agents) of each run).  That is
+/// the same computation only when every clone would own its policy, i.e. when the policy's tables are configured
+/// INSIDE the prototype; the reference's own example (cfg/pendulum/multi_sarsa_tc.yaml) points every clone at one
+/// top-level policy, so that its threads update one shared table without synchronisation -- a different algorithm,
+/// which is rejected here with an explanation instead of being silently replaced.
+class MultiExperiment : public Experiment
+{
+  public:
+    TYPEINFO("experiment/multi", "Run multiple experiments in parallel (as independent agents on the GPU)")
+    void request(ConfigurationRequest *config) override;
+    void configure(Configuration &config) override;
+    std::vector<double> run() override;
+    OnlineLearningExperiment *prototype() const { return prototype_; }
+    int instances() const { return instances_; }
+  private:
+    int instances_ = 4;
+    OnlineLearningExperiment *prototype_ = nullptr;
 };
 
 }  // namespace grl

@@ -92,8 +92,10 @@ int main(int argc, char **argv)
     Configurator configurator;
     NOTICE("Instantiating configuration");
     configurator.instantiate(*doc);
-    OnlineLearningExperiment *experiment = dynamic_cast<OnlineLearningExperiment *>(configurator.object("experiment"));
-    if (!experiment)
+    Experiment *top = dynamic_cast<Experiment *>(configurator.object("experiment"));
+    OnlineLearningExperiment *experiment = dynamic_cast<OnlineLearningExperiment *>(top);
+    if (MultiExperiment *multi = dynamic_cast<MultiExperiment *>(top)) experiment = multi->prototype();   // instances -> agents
+    if (!top || !experiment)
     {
       ERROR("YAML configuration does not specify an experiment");
       return 1;
@@ -106,7 +108,8 @@ int main(int argc, char **argv)
     }
     if (interfaces) return exercise_interfaces(configurator, experiment);
     NOTICE("Starting experiment");
-    experiment->run();
+    top->run();
+    if (experiment->collectiveMs() > 0) NOTICE("NCCL all-gather of the per-agent results: " << experiment->collectiveMs() << " ms in total");
     NOTICE("Exiting");
   }
   catch (Exception &e)

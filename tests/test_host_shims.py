@@ -429,3 +429,156 @@ def test_role_interfaces_of_the_shims(grld, tmp_path, yaml, mk, kw):
         assert got["next_obs"] == list(obs2[0]) and got["reward"] == rew[0] and got["terminal"] == term[0] and got["tau"] == 1.0
     finally:
         b.close()
+
+
+# ---- round 2: registration by dlopen, experiment/multi, load_file / save_every, several GPUs --------------------------
+def test_addon_registers_its_types_when_dlopened(grld):
+    """GRL finds addons by globbing libaddon*.so and dlopen(RTLD_NOW|RTLD_GLOBAL) (grl.cpp:73-111); the static
+    REGISTER_CONFIGURABLE objects do the rest (factory.h:81-91).  plugin_probe links the framework library only."""
+    probe = os.path.join(HOST, "plugin_probe")
+    ldd = subprocess.run(["ldd", probe], capture_output=True, text=True).stdout
+    assert "libgrl_b200.so" in ldd and "addon" not in ldd and "grlcu" not in ldd
+    types = ["environment/model/cuda_batched", "projector/tile_coding/cuda", "representation/linear/cuda",
+             "predictor/sarsa/cuda", "experiment/online_learning", "experiment/multi"]
+    out = subprocess.run([probe] + types + ["no/such/type"], capture_output=True, text=True)
+    lines = [l for l in out.stdout.splitlines() if not l.startswith("[")]      # (log lines: [NTC] ...)
+    assert lines[0].startswith("plugins 1 types_before 0 types_after ")
+    assert int(lines[0].split()[-1]) >= 20
+    for t, l in zip(types, lines[1:]):
+        assert l == "%s %s" % (t, t)
+    assert lines[-1].startswith("no/such/type MISSING") and out.returncode == 1
+
+
+def _multi_yaml(instances, agents):
+    """cfg/pendulum/sarsa_tc_cuda.yaml wrapped in an experiment/multi: the policy is configured INSIDE the prototype."""
+    body = [l for l in open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read().split("\n") if not l.startswith("#")]
+    assert body[0] == "experiment:"
+    inner = "\n".join("  " + l for l in body[1:] if l.strip())
+    inner = inner.replace("experiment/agent", "experiment/experiment/agent").replace("experiment/environment", "experiment/experiment/environment")
+    y = "experiment:\n  type: experiment/multi\n  instances: %d\n  experiment:\n%s\n" % (instances, inner)
+    return y.replace("agents: 65536", "agents: %d" % agents)
+
+
+def test_experiment_multi_maps_instances_onto_agents(grld, tmp_path):
+    """experiment/multi (experiments/multi.cpp:38-75): instances become agents when every clone would own its policy;
+    the reference's own example shares ONE policy between the clones and is rejected with an explanation."""
+    p = tmp_path / "multi.yaml"
+    p.write_text(_multi_yaml(4, 24))
+    rc, out, err = check(grld, str(p))
+    assert rc == 0, err
+    assert json.loads(out)["agents"] == 96
+    if os.path.isdir(REF_CFG):
+        q = tmp_path / "shared.yaml"
+        q.write_text(swap_types(open(os.path.join(REF_CFG, "pendulum/multi_sarsa_tc.yaml")).read()))
+        rc, out, err = check(grld, str(q))
+        assert rc == 1 and "share one policy" in err and "multi_sarsa_tc.yaml" in err
+
+
+def test_save_every_values(grld, tmp_path):
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
+    for v, ok in (("never", True), ("run", True), ("test", True), ("trial", True), ("sometimes", False)):
+        p = tmp_path / ("se_%s.yaml" % v)
+        p.write_text(base.replace("  runs: 1", "  runs: 1\n  save_every: %s" % v))
+        rc, out, err = check(grld, str(p))
+        assert (rc == 0) == ok, (v, err)
+
+
+@pytest.mark.gpu
+def test_load_file_round_trip_from_reference_format(grld, tmp_path, orc):
+    """f1: tables written by fwrite in the reference's layout (representation.h:201-263: raw little-endian doubles,
+    `file` + path with '/' -> '_' + ".dat") -- here the ORACLE's learned tables -- load through `load_file`
+    (online_learning.cpp:141-150, with $run substitution) and learning continues bit-exactly: grld_b200's per-agent results
+    equal the ctypes harness started from the same tables, and a replay from the loaded tables stays in lock-step with
+    the oracle."""
+    import ctypes as C
+    import grl_b200
+    import _oracle as O
+    n, mem = 32, 4096
+    oc = O.pendulum_config(memory=mem, randomization=1.0, test_interval=-1, seed=9)
+    L = O.lib()
+    L.orc_run_total.restype = None
+    L.orc_run_total.argtypes = [C.c_void_p, C.c_uint64]
+    tables = []
+    stem = str(tmp_path / "pol-0")                       # load_file: pol-$run
+    for i in range(n):
+        a = L.orc_create(C.byref(oc), 500 + i)
+        L.orc_run_total(a, 400)
+        t = np.ctypeslib.as_array(L.orc_table(a), shape=(mem,)).copy()
+        L.orc_destroy(a)
+        tables.append(t)
+        t.tofile("%s-experiment_agent_policy_representation%s.dat" % (stem, "" if i == 0 else "-agent%d" % i))
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
+    y = base.replace("agents: 65536", "agents: %d" % n).replace("steps: 10000", "steps: 300") \
+            .replace("memory: 65536", "memory: %d" % mem) \
+            .replace("  runs: 1", "  runs: 1\n  output: %s\n  load_file: %s\n  save_every: trial" % (tmp_path / "out", tmp_path / "pol-$run"))
+    p = tmp_path / "load.yaml"
+    p.write_text(y)
+    out = subprocess.run([grld, "-s", "9", str(p)], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr + out.stdout
+    rows = [l.split() for l in open(str(tmp_path / "out") + "-0.txt") if l.startswith("# ") and l[2].isdigit()]
+    assert len(rows) == n
+    cfg = grl_b200.pendulum_config(memory=mem, randomization=1.0, test_interval=-1, seed=9)
+    b = grl_b200.Batch(cfg, n)
+    try:
+        for i in range(n):
+            b.set_table(i, tables[i])
+        for _ in range(3):
+            b.run(100)
+        r = b.results()
+        for a, row in enumerate(rows):
+            assert int(row[2]) == r["steps"][a] and float(row[4]) == r["last_return"][a]
+        # save_every: trial wrote a checkpoint after every report, named by the finished episodes (online_learning.cpp:281-291)
+        ck = np.fromfile(str(tmp_path / "out") + "-run0-trial3-experiment_agent_policy_representation-agent5.dat", dtype=np.float64)
+        assert np.array_equal(ck, b.get_table(5))
+        # a reserved bit pattern must not get in through a checkpoint
+        bad = tables[0].copy()
+        bad.view(np.uint64)[17] = np.uint64(0x7FF4C0DE00000003)
+        with pytest.raises(grl_b200.GrlcuError):
+            b.set_table(0, bad)
+    finally:
+        b.close()
+    # replay from the loaded tables: fresh agents on both sides, the oracle's tables overwritten with the same files
+    b = grl_b200.Batch(cfg, n, first_agent_id=500)
+    ob = O.OracleBatch(oc, n, first_id=500)
+    try:
+        for i in range(n):
+            b.set_table(i, tables[i])
+            ob.table(i)[:] = tables[i]
+        for t in range(150):
+            d = ob.step()
+            inp = dict(d)
+            inp["force_action"] = np.maximum(d["action_index"], 0).astype(np.int32)
+            o = b.replay_step(inp, want_trace=False)
+            assert np.array_equal(o["index"], d["index"]) and np.array_equal(o["action_index"], d["action_index"]), t
+            assert np.array_equal(o["q"], d["q"]) and np.array_equal(o["delta"], d["delta"]), t
+        for i in range(n):
+            assert np.array_equal(b.get_table(i), ob.table(i))
+    finally:
+        b.close(); ob.close()
+
+
+@pytest.mark.gpu
+def test_grld_on_two_gpus_equals_one_gpu(grld, tmp_path):
+    """Agents shard over the GPUs of the box behind the plugin API (`devices`), one NCCL all-gather of the per-agent
+    results per report: the output is keyed by global agent id and must not depend on the number of devices.  (The last
+    column of a report row is wall time and is not compared.)"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_sweep_cuda.yaml")).read()
+    outs = {}
+    for tag, devs in (("one", "[0]"), ("two", "[0, 1]")):
+        y = re.sub(r"agents: \d+", "agents: 256", base)
+        y = re.sub(r"steps: \d+", "steps: 500", y, count=1)
+        y = re.sub(r"memory: \d+\n", "memory: 32768\n", y, count=1)
+        y = y.replace("  runs: 1", "  runs: 1\n  devices: %s\n  output: %s" % (devs, tmp_path / tag))
+        p = tmp_path / (tag + ".yaml")
+        p.write_text(y)
+        out = subprocess.run([grld, "-v", "-s", "4", str(p)], capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr + out.stdout
+        outs[tag] = out.stdout + out.stderr
+        assert os.path.exists(str(tmp_path / tag) + "-0-cells.txt")
+    strip = lambda path: [l if l.startswith("#") else " ".join(l.split()[:-1]) for l in open(path)]
+    assert strip(str(tmp_path / "one") + "-0.txt") == strip(str(tmp_path / "two") + "-0.txt")
+    assert open(str(tmp_path / "one") + "-0-cells.txt").read() == open(str(tmp_path / "two") + "-0-cells.txt").read()
+    assert "NCCL all-gather" in outs["two"] and "NCCL all-gather" not in outs["one"]
