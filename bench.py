@@ -88,6 +88,18 @@ def table_bytes_per_step(workload, V):
     return (768 if workload in AC_WORKLOADS else 640) + 16 * V
 
 
+def kernel_sources_sha():
+    """sha1 over the CUDA sources of libgrlcu.so: ties a committed ncu capture to the tree it was taken from."""
+    import hashlib
+    h = hashlib.sha1()
+    d = os.path.join(ROOT, "grl_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".h")):
+            h.update(f.encode())
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -258,7 +270,9 @@ def ours(args):
     writes = int((r1["table_writes"] - r0["table_writes"]).sum())
 
     # ---- end to end through the host-buffer call: every step copies ITS OWN start-state batch in from pinned host
-    # memory and its per-agent results out into pinned host memory (the batches are generated before the clock starts)
+    # memory and its per-agent results out into pinned host memory (the batches are generated before the clock starts).
+    # An agent takes its row when it BEGINS its next episode; episodes in progress continue, so this leg runs the same
+    # trajectory phase as the device-resident one (it does not restart every agent every step)
     rng = np.random.default_rng(1234 + rank)
     n_batches = max(args.steps, 1)
     starts = torch.zeros((n_batches, n, S), dtype=torch.float64).pin_memory()
@@ -287,10 +301,17 @@ def ours(args):
     h2d = n * S * 8
     d2h = n * (8 * 3 + 8 + 4 + 8 + 8)
 
-    # ---- max over ranks; the only collective: final statistics gather over NCCL
+    # ---- max over ranks; the only collective: final statistics gather over NCCL (outside the timed region; timed
+    # here on the device so that the line shows what is outside the clock)
     from grl_b200.dist import finalize
+    barrier()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
     (dev_ms, e2e_s, kern_ms), (steps_all, swept_all, writes_all), ret = finalize(
         [dev_ms, e2e_s, kern_ms], [steps_done, swept, writes], r1["last_return"], "cuda")
+    c1.record()
+    torch.cuda.synchronize()
+    collective_ms = c0.elapsed_time(c1)
     mean_return = float(ret.mean())
 
     if rank == 0:
@@ -300,12 +321,16 @@ def ours(args):
         per_gpu_steps = steps_all / world
         achieved = per_gpu_steps * B / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
         # DRAM traffic of one launch, from the committed ncu capture of this exact workload (if there is one)
-        traffic, traffic_src = None, None
+        # (a cross-reference, not a measurement of this run: it is only turned into a fraction when the kernel
+        # sources are byte-identical to the ones the capture was taken from)
+        traffic, traffic_src, traffic_tree, traffic_current = None, None, None, False
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                 t = json.load(f).get("%s:%d:%d" % (args.workload, args.agents, args.memory))
             if t:
-                traffic, traffic_src = t["dram_bytes_per_launch"], t["capture"]
+                traffic, traffic_src = t["dram_bytes_per_pass"], t["capture"]
+                traffic_tree = t.get("kernel_sources_sha")
+                traffic_current = traffic_tree == kernel_sources_sha()
         except Exception:
             pass
         # What actually bounds the path: every table access is a hash-random 8-byte word.  Ceilings measured on
@@ -351,14 +376,19 @@ def ours(args):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                          # sector-granular figure: the DRAM bytes the hardware moved per launch (ncu capture)
                          # over this run's measured launch time, as a fraction of the same peak
-                         "traffic_frac": (traffic / (kern_ms / max(kern_launches, 1) * 1e-3) / 1e9 / peak)
-                                         if traffic and kern_ms > 0 else None,
+                         "traffic_tree": traffic_tree, "traffic_is_of_this_tree": traffic_current,
+                         "traffic_frac": (traffic / (kern_ms / max(args.steps, 1) * 1e-3) / 1e9 / peak)
+                                         if traffic and kern_ms > 0 and traffic_current else None,
                          "peak_source": peak_src, "random_access": random_access,
                          "bytes_per_agent_step": B, "V_mean": V,
                          "kernel": "grlcu::k_run_ac" if args.workload in AC_WORKLOADS else "grlcu::k_run",
                          "kernel_ms_per_launch": kern_ms / max(kern_launches, 1),
+                         "kernel_ms_per_pass": kern_ms / max(args.steps, 1),
                          "kernel_launches": int(kern_launches)},
             "mean_last_return": mean_return,
+            "collective_ms": collective_ms,
+            "collective": "one all-gather of the per-agent returns + two all-reduces (timings MAX, counters SUM) after the "
+                          "timed region (grl_b200/dist.py); nothing collective runs inside it",
         }
         if world == 1 and not args.no_cpu:
             rate0, procs, _ = cpu_oracle_rate(args, 50000)

@@ -426,7 +426,7 @@ __global__ void k_begin_override(Params p)
 {
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= p.n) return;
-  p.flags[a] = (p.flags[a] & 16) | 4;     // not in episode, start-state override pending (bit4: the agent's cache stays as it is)
+  p.flags[a] |= 4;     // start-state override pending: consumed by the next episode this agent begins (k_run)
 }
 
 static int launch_reset(grlcu_ctx *c, int what)

@@ -279,7 +279,7 @@ struct Agent
   // online_learning.cpp:223-262 bookkeeping at the end of an episode
   __device__ __forceinline__ void episode_end(const Params &p, int a, bool test)
   {
-    flags &= 16;
+    flags &= (16 | 4);       // keep: cache live, start-state override pending
     p.tt[a] += 1;
     p.episodes[a] += 1;
     if (test) p.last_test_return[a] = total_reward;

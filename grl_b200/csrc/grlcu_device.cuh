@@ -27,7 +27,6 @@ __device__ __forceinline__ double ld_tbl(const double *p)
   asm volatile("ld.global.L2::64B.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
   return v;
 }
-
 // ---- Philox4x32-10 (Salmon et al., SC'11) -------------------------------------------------
 struct Philox4 { uint32_t w[4]; };
 

@@ -199,9 +199,9 @@ int grlcu_run(grlcu_ctx *ctx, int64_t n_steps, int32_t cohort);
 int grlcu_sync(grlcu_ctx *ctx);
 
 /* Plugin-facing end-to-end call with HOST buffers: uploads a batch of start states
- * ([n_agents][S] row-major; every agent begins a new learning episode from its row,
- * replacing Task::start), runs n_steps agent-steps per agent, downloads the results,
- * and synchronises.  start_states may be NULL (Philox starts). */
+ * ([n_agents][S] row-major; the next episode an agent BEGINS starts from its row, in
+ * place of Task::start -- episodes in progress continue), runs n_steps agent-steps per
+ * agent, downloads the results, and synchronises.  start_states may be NULL (Philox starts). */
 int grlcu_run_host(grlcu_ctx *ctx, const double *start_states, int64_t n_steps, int32_t cohort,
                    grlcu_results *results);
 

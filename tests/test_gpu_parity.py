@@ -315,3 +315,28 @@ def test_random_access_probe(G):
     assert 1e10 < m < w < r < 1e12            # B200: about 37 G reads/s, 20 G writes/s, 13.5 G read-modify-writes/s
     with pytest.raises(G.GrlcuError):
         G.capi.probe_random_access(0, 3 << 20)
+
+
+def test_run_host_start_states_apply_to_the_next_episode_an_agent_begins(G):
+    """grlcu_run_host: the uploaded start-state row replaces Task::start for the next episode the agent BEGINS; an episode
+    in progress continues (so the end-to-end leg of bench.py runs the same trajectory phase as the device-resident one)."""
+    cfg = G.pendulum_config(memory=4096, randomization=1.0, test_interval=-1)
+    n = 8
+    b = G.Batch(cfg, n)
+    try:
+        s1 = np.zeros((n, 3)); s1[:, 0] = 1.0 + 0.1 * np.arange(n)
+        b.run_host(s1, 1)
+        st = np.array([b.get_state(i)[0] for i in range(n)])
+        assert np.allclose(st[:, 2], 0.03) and np.all(np.abs(st[:, 0] - s1[:, 0]) < 0.2)      # began from the rows
+        s2 = np.zeros((n, 3)); s2[:, 0] = -2.0
+        b.run_host(s2, 1)
+        st2 = np.array([b.get_state(i)[0] for i in range(n)])
+        assert np.allclose(st2[:, 2], 0.06) and np.all(np.abs(st2[:, 0] - st[:, 0]) < 0.5)     # episode in progress continues
+        b.run_host(None, 98)                                                                    # ... to its end (100 steps)
+        r = b.results()
+        assert np.all(r["episodes"] == 1)
+        b.run_host(None, 1)                                                                     # next episode: from the pending rows
+        st3 = np.array([b.get_state(i)[0] for i in range(n)])
+        assert np.allclose(st3[:, 2], 0.03) and np.all(np.abs(st3[:, 0] + 2.0) < 0.2)
+    finally:
+        b.close()
