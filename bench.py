@@ -241,6 +241,7 @@ def ours(args):
     first_id, _ = shard(rank, world, args.agents)
     batch = grl_b200.Batch(cfg, args.agents, first_agent_id=first_id, device=local, stream=stream)
     n, S = args.agents, batch.S
+    layout = batch.layout_info()
     bufs = batch.result_buffers()
     if args.workload == "sweep":
         batch.set_hyper(*sweep_hyper(first_id, n))
@@ -351,9 +352,14 @@ def ours(args):
             cached = os.environ.get("GRLCU_MODE", "0") == "0"
             W = writes_all / max(steps_all, 1)
             R = (4 * 16 if ac else 3 * 16 + 16) + (0 if cached else V)      # cached path: the sweep runs on the dense cache
+            if layout["tile_major"]:
+                # one sector request per tiling for Q(s', .), one more per word that shares an earlier tile's slot, T for Q(p)
+                R = 16 + 48.0 * layout["shared_words"] / max(layout["inbox_words"], 1) + 16
             floor_ns = R / ceil["read_G_per_s"] + W / ceil["write_G_per_s"]
             got_ns = kern_ms * 1e6 / max(per_gpu_steps, 1)
-            random_access = {"reads_per_agent_step": R, "writes_per_agent_step": W,
+            random_access = {"kind": "model estimate, not a ceiling: the probe's addresses are uniformly random, the "
+                                     "kernel's are clustered (a fraction above 1 means the clustering pays)",
+                             "reads_per_agent_step": R, "writes_per_agent_step": W,
                              "read_ceiling_G_per_s": ceil["read_G_per_s"], "write_ceiling_G_per_s": ceil["write_G_per_s"],
                              "ns_per_agent_step_at_ceiling": floor_ns, "ns_per_agent_step": got_ns,
                              "frac": floor_ns / got_ns if got_ns > 0 else None,
@@ -381,6 +387,8 @@ def ours(args):
                                          if traffic and kern_ms > 0 and traffic_current else None,
                          "peak_source": peak_src, "random_access": random_access,
                          "bytes_per_agent_step": B, "V_mean": V,
+                         "table_layout": dict(layout, note="tile-major: the 3 action words of one tile share a 32-byte sector, "
+                                              "slot computed from tile coordinates (DESIGN.md section 4); else the reference's raw hash order"),
                          "kernel": "grlcu::k_run_ac" if args.workload in AC_WORKLOADS else "grlcu::k_run",
                          "kernel_ms_per_launch": kern_ms / max(kern_launches, 1),
                          "kernel_ms_per_pass": kern_ms / max(args.steps, 1),

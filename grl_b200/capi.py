@@ -162,7 +162,7 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
            "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update",
            "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor", "grlcu_probe_random_access",
-           "grlcu_device_count", "grlcu_group_create", "grlcu_group_destroy", "grlcu_group_run", "grlcu_group_results"]
+           "grlcu_layout_info", "grlcu_device_count", "grlcu_group_create", "grlcu_group_destroy", "grlcu_group_run", "grlcu_group_results"]
 
 _lib = None
 
@@ -205,6 +205,7 @@ def load(build=True):
     L.grlcu_probe_random_access.argtypes = [C.c_int32, C.c_uint64, _dp, _dp, _dp]
     L.grlcu_read_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, _dp]
     L.grlcu_update_actor.argtypes = [vp, C.c_int32, C.c_int32, _u64p, C.c_double]
+    L.grlcu_layout_info.argtypes = [vp, _i32p, _u32p, _u32p, _u32p]
     L.grlcu_group_create.argtypes = [_P(vp), C.c_int32, _P(vp)]
     L.grlcu_group_destroy.argtypes = [vp]
     L.grlcu_group_run.argtypes = [vp, C.c_int64]
@@ -354,6 +355,12 @@ class Batch:
         st, act, ep = np.empty(self.S), C.c_double(), C.c_int32()
         self._chk(self.lib.grlcu_get_state(self.h, agent, _ptr(st, _dp), C.byref(act), C.byref(ep)))
         return st, act.value, ep.value
+
+    def layout_info(self):
+        """dict(tile_major, table_stride, inbox_words, shared_words): how the context stores its tables."""
+        tm, ts, iw, sw = C.c_int32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self._chk(self.lib.grlcu_layout_info(self.h, C.byref(tm), C.byref(ts), C.byref(iw), C.byref(sw)))
+        return dict(tile_major=bool(tm.value), table_stride=ts.value, inbox_words=iw.value, shared_words=sw.value)
 
     def launch_count(self):
         return self.lib.grlcu_launch_count(self.h)

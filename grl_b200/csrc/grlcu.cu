@@ -830,6 +830,16 @@ extern "C" int grlcu_run_kernel_time(grlcu_ctx *c, double *ms, int64_t *launches
   return 0;
 }
 
+extern "C" int grlcu_layout_info(grlcu_ctx *c, int32_t *tile_major, uint32_t *table_stride, uint32_t *inbox_words, uint32_t *shared_words)
+{
+  if (!c) return fail(GRLCU_ERR_ARG, "null context");
+  if (tile_major) *tile_major = c->geo ? 1 : 0;
+  if (table_stride) *table_stride = c->p.tstride;
+  if (inbox_words) *inbox_words = c->inbox_words;
+  if (shared_words) *shared_words = c->shared_words;
+  return 0;
+}
+
 extern "C" int64_t grlcu_launch_count(grlcu_ctx *c) { return c ? c->launches : -1; }
 extern "C" int grlcu_trace_capacity(grlcu_ctx *c) { return c ? c->p.trace_cap : -1; }
 
