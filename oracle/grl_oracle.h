@@ -28,14 +28,19 @@
  *   src/agents/td.cpp:50-81, src/agents/fixed.cpp:48-62
  *   src/experiments/online_learning.cpp:154-222
  *
- * PARITY PIN STATUS: the real reference cannot be compiled in the authoring
- * container (it needs Eigen 3, which is neither vendored nor installed), and
- * the reference ships no unit-level golden vectors for this path.  The oracle
- * is pinned against (a) an independent MurmurHash2 formulation for the tile
- * hash and (b) the reference's seeded learning curve
- * tests/template/pendulum-sarsa-tc-0.txt (see tests/test_oracle_golden.py for
- * how far that pin holds).  Everything else is "parity unpinned" in the sense
- * of the task statement; see DESIGN.md.
+ * PARITY PIN STATUS (details: DESIGN.md section 3).  The reference as a whole cannot be compiled in the authoring
+ * container (it needs Eigen 3, neither vendored nor installed).  The oracle is pinned by
+ *   (a) the reference's seeded learning curve tests/template/pendulum-sarsa-tc-0.txt, all 181 rows
+ *       (tests/test_oracle_golden.py): RK4, pendulum task, hash, Q read, samplers, SARSA(lambda) write, replacing trace;
+ *   (b) the reference's tests/template/cart_pole_balancing-pid-0.txt, all 10 rows (grl_oracle_pin.c,
+ *       tests/test_oracle_vs_ref.py): cart-pole equations of motion + RK4 over 5 states;
+ *   (c) the reference's OWN environment sources (pendulum.cpp, cart_pole.cpp, cart_double_pole.cpp) compiled from
+ *       /root/reference against stand-in headers into oracle/_ref/libgrlref_env.so: eom / start / actuate / observe /
+ *       evaluate bit-exact on 1e5 random inputs per function (tests/test_oracle_vs_ref.py);
+ *   (d) an independent byte-wise MurmurHash2 for the tile hash, Random123's known answers for Philox.
+ * PARITY UNPINNED: the summation order inside Eigen's Matrix3d::inverse() and 3x3 products (cart-double-pole; the
+ * stand-in shares the oracle's assumption), and the actor-critic agent (ac_step: the reference's only vector for it,
+ * tests/template/cart_double_pole-ac-tc-0.txt, was produced by an older predictor).
  */
 #ifndef GRL_ORACLE_H_
 #define GRL_ORACLE_H_
