@@ -162,7 +162,7 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
            "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update",
            "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor", "grlcu_probe_random_access",
-           "grlcu_layout_info", "grlcu_device_count", "grlcu_group_create", "grlcu_group_destroy", "grlcu_group_run", "grlcu_group_results"]
+           "grlcu_layout_info", "grlcu_project_noalloc", "grlcu_device_count", "grlcu_group_create", "grlcu_group_destroy", "grlcu_group_run", "grlcu_group_results"]
 
 _lib = None
 
@@ -184,6 +184,7 @@ def load(build=True):
     L.grlcu_reset.argtypes = [vp, C.c_int32]
     L.grlcu_set_hyper.argtypes = [vp, _dp, _dp, _dp]
     L.grlcu_project.argtypes = [vp, C.c_int64, _dp, _u32p, _u32p]
+    L.grlcu_project_noalloc.argtypes = [vp, C.c_int64, _dp, _u32p, _u32p]
     L.grlcu_model_step.argtypes = [vp, C.c_int64, _dp, _dp, _dp, _dp, _dp, _i32p]
     L.grlcu_run.argtypes = [vp, C.c_int64, C.c_int32]
     L.grlcu_sync.argtypes = [vp]
@@ -267,6 +268,14 @@ class Batch:
         n, T = x.shape[0], self.cfg.tilings
         h, i = np.empty((n, T), np.uint32), np.empty((n, T), np.uint32)
         self._chk(self.lib.grlcu_project(self.h, n, _ptr(x, _dp), _ptr(h, _u32p), _ptr(i, _u32p)))
+        return h, i
+
+    def project_noalloc(self, inputs):
+        """grlcu_project_noalloc: the same projection staged in the library's static device scratch (no allocation)."""
+        x = np.ascontiguousarray(inputs, dtype=np.float64)
+        n, T = x.shape[0], self.cfg.tilings
+        h, i = np.empty((n, T), np.uint32), np.empty((n, T), np.uint32)
+        self._chk(self.lib.grlcu_project_noalloc(self.h, n, _ptr(x, _dp), _ptr(h, _u32p), _ptr(i, _u32p)))
         return h, i
 
     def model_step(self, state, action):

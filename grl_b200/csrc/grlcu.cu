@@ -1264,3 +1264,74 @@ extern "C" int grlcu_group_results(grlcu_group *g, grlcu_results *res, double *c
   }
   return 0;
 }
+
+// ---- grlcu_project_noalloc (include/grlcu.h): the K2 projection without any allocation --------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  grlcu_project stages its inputs and
+// outputs in device scratch that it cudaMallocs and frees per call; this variant stages them in ONE file-scope device
+// array that every GPU loading the library holds until exit (768 KiB).  Layout of the array (offsets 256-byte aligned):
+//   [0, 256 KiB)        inputs   double   [GRLCU_NOALLOC_MAX_INPUTS][GRLCU_MAX_DIMS]  (n * dims used)
+//   [256, 512 KiB)      hashes   uint32_t [GRLCU_NOALLOC_MAX_INPUTS][16]
+//   [512, 768 KiB)      indices  uint32_t [GRLCU_NOALLOC_MAX_INPUTS][16]
+// Every call shares the array and it keeps the last call's contents.  Nothing in it has to start at zero: a call
+// overwrites the n * dims inputs it reads and the kernel writes every one of the n * T hashes and indices that are copied
+// out; words beyond those are never read.  Calls that overlap on one GPU (two streams, two host threads, two contexts on
+// the same device) RACE on the array: the caller serialises them.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[GRLCU_NOALLOC_MAX_INPUTS * (GRLCU_MAX_DIMS * 8 + 16 * 4 + 16 * 4)];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+// In host code `g_noalloc_scratch` is a host-side stand-in, NOT a device address: the address the kernel gets comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+unsigned char *g_noalloc_ptr[kNoAllocMaxDevices];
+bool g_noalloc_have[kNoAllocMaxDevices];
+
+int noalloc_scratch(int device, unsigned char **out)
+{
+  if (device < 0 || device >= kNoAllocMaxDevices) return fail(GRLCU_ERR_ARG, "grlcu_project_noalloc: device %d out of range", device);
+  if (!g_noalloc_have[device])
+  {
+    CU(cudaSetDevice(device));
+    void *ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr)
+      return fail(GRLCU_ERR_CUDA, "grlcu_project_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+    g_noalloc_ptr[device] = (unsigned char *)ptr;
+    g_noalloc_have[device] = true;
+  }
+  *out = g_noalloc_ptr[device];
+  return 0;
+}
+}  // namespace
+
+extern "C" int grlcu_project_noalloc(grlcu_ctx *c, int64_t n, const double *in, uint32_t *hash, uint32_t *index)
+{
+  if (!c || n < 0 || !in || !index) return fail(GRLCU_ERR_ARG, "grlcu_project_noalloc: bad arguments");
+  if (n > GRLCU_NOALLOC_MAX_INPUTS)
+    return fail(GRLCU_ERR_ARG, "grlcu_project_noalloc: %lld inputs exceed the static scratch of %d (GRLCU_NOALLOC_MAX_INPUTS): "
+                "split the batch or use grlcu_project", (long long)n, GRLCU_NOALLOC_MAX_INPUTS);
+  if (c->cfg.tilings != 16) return fail(GRLCU_ERR_UNSUPPORTED, "grlcu_project_noalloc: tilings %d (16 expected)", c->cfg.tilings);
+  if (n == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  unsigned char *base = nullptr;
+  if (int r = noalloc_scratch(c->device, &base)) return r;
+  const bool is_ac = c->cfg.algo == GRLCU_ALGO_AC;
+  const int dims = is_ac ? c->cfg.obs_dims : c->cfg.obs_dims + 1, T = 16;
+  double *d_in = (double *)base;
+  uint32_t *d_h = (uint32_t *)(base + (size_t)GRLCU_NOALLOC_MAX_INPUTS * GRLCU_MAX_DIMS * 8);
+  uint32_t *d_i = d_h + (size_t)GRLCU_NOALLOC_MAX_INPUTS * 16;
+  CU(cudaMemcpyAsync(d_in, in, sizeof(double) * n * dims, cudaMemcpyHostToDevice, c->stream));
+  const int grd = grid_for(n, 128);
+#define CALL(D) k_project<Dyn<D>::OBS + 1, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i)
+#define CALL_AC(D) k_project<Dyn<D>::OBS, 16><<<grd, 128, 0, c->stream>>>(c->p.proj, n, d_in, d_h, d_i)
+  if (is_ac) DISPATCH_DYN(c, CALL_AC);
+  else DISPATCH_SARSA(c, CALL);
+#undef CALL_AC
+#undef CALL
+  c->launches++;
+  CU(cudaGetLastError());
+  if (hash) CU(cudaMemcpyAsync(hash, d_h, sizeof(uint32_t) * n * T, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(index, d_i, sizeof(uint32_t) * n * T, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}

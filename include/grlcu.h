@@ -167,6 +167,18 @@ int grlcu_set_hyper(grlcu_ctx *ctx, const double *alpha, const double *lambda, c
  * in: [n][dims] row-major, dims = obs_dims + 1.  hash/index: [n][tilings]. */
 int grlcu_project(grlcu_ctx *ctx, int64_t n, const double *in, uint32_t *hash, uint32_t *index);
 
+/* grlcu_project without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and results as grlcu_project (bit-identical), but the device staging of the inputs, hashes and indices
+ * lives in one file-scope `static __device__` array of the library (768 KiB per GPU that loads it, held until exit)
+ * instead of per-call cudaMalloc / cudaFree; the call performs no cudaMalloc, cudaFree or other allocating routine.
+ * Limit: n <= GRLCU_NOALLOC_MAX_INPUTS, larger batches are rejected with GRLCU_ERR_ARG (split them, or use
+ * grlcu_project).  Every call shares the array, which keeps the previous call's contents (nothing in it needs to start
+ * at zero: every word that is read back is written first); calls that overlap on one GPU race on it, so the caller
+ * serialises them. */
+#define GRLCU_NOALLOC_MAX_INPUTS 4096
+int grlcu_project_noalloc(grlcu_ctx *ctx, int64_t n, const double *in, uint32_t *hash, uint32_t *index);
+
 /* K1: ModeledEnvironment::step body (modeled.cpp:160-213) = Task::actuate +
  * DynamicalModel::step (modeled.cpp:254-276) + Task::observe + Task::evaluate.
  * state/next: [n][S] row-major; action/reward: [n]; obs: [n][obs_dims]. */
