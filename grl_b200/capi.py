@@ -37,6 +37,7 @@ class Config(C.Structure):
         ("actor_resolution", C.c_double * MAX_DIMS), ("actor_wrapping", C.c_double * MAX_DIMS),
         ("target_epsilon", C.c_double),
         ("end_stop_penalty", C.c_int32), ("sampler", C.c_int32), ("softmax_tau", C.c_double),
+        ("safe", C.c_int32),
     ]
 
     def __init__(self, *a, **kw):
@@ -162,7 +163,7 @@ EXPORTS = ["grlcu_last_error", "grlcu_version", "grlcu_create", "grlcu_destroy",
            "grlcu_set_table", "grlcu_get_state", "grlcu_trace_capacity", "grlcu_launch_count",
            "grlcu_run_kernel_time", "grlcu_task_start", "grlcu_read", "grlcu_update",
            "grlcu_get_actor_table", "grlcu_set_actor_table", "grlcu_read_actor", "grlcu_update_actor", "grlcu_probe_random_access",
-           "grlcu_layout_info", "grlcu_project_noalloc", "grlcu_device_count", "grlcu_group_create", "grlcu_group_destroy", "grlcu_group_run", "grlcu_group_results"]
+           "grlcu_layout_info", "grlcu_get_pressure", "grlcu_project_noalloc", "grlcu_device_count", "grlcu_group_create", "grlcu_group_destroy", "grlcu_group_run", "grlcu_group_results"]
 
 _lib = None
 
@@ -184,6 +185,7 @@ def load(build=True):
     L.grlcu_reset.argtypes = [vp, C.c_int32]
     L.grlcu_set_hyper.argtypes = [vp, _dp, _dp, _dp]
     L.grlcu_project.argtypes = [vp, C.c_int64, _dp, _u32p, _u32p]
+    L.grlcu_get_pressure.argtypes = [vp, _u32p]
     L.grlcu_project_noalloc.argtypes = [vp, C.c_int64, _dp, _u32p, _u32p]
     L.grlcu_model_step.argtypes = [vp, C.c_int64, _dp, _dp, _dp, _dp, _dp, _i32p]
     L.grlcu_run.argtypes = [vp, C.c_int64, C.c_int32]
@@ -370,6 +372,12 @@ class Batch:
         tm, ts, iw, sw = C.c_int32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
         self._chk(self.lib.grlcu_layout_info(self.h, C.byref(tm), C.byref(ts), C.byref(iw), C.byref(sw)))
         return dict(tile_major=bool(tm.value), table_stride=ts.value, inbox_words=iw.value, shared_words=sw.value)
+
+    def pressure(self):
+        """safe > 0: per-agent maximum probe length in the claim table (TileCodingProjector::pressure_)."""
+        out = np.empty(self.n, np.uint32)
+        self._chk(self.lib.grlcu_get_pressure(self.h, _ptr(out, _u32p)))
+        return out
 
     def launch_count(self):
         return self.lib.grlcu_launch_count(self.h)

@@ -159,6 +159,9 @@ static int supported(const grlcu_config *cfg)
   if (cfg->memory < 1) return fail(GRLCU_ERR_ARG, "memory must be positive");
   if (cfg->integration_steps < 1) return fail(GRLCU_ERR_ARG, "integration_steps must be >= 1");
   if (cfg->end_stop_penalty != 0 && cfg->end_stop_penalty != 1) return fail(GRLCU_ERR_ARG, "end_stop_penalty must be 0 or 1");
+  if (cfg->safe < 0 || cfg->safe > 2) return fail(GRLCU_ERR_ARG, "projector/tile_coding:safe must be 0, 1 or 2");
+  if (cfg->safe > 0 && cfg->algo != GRLCU_ALGO_SARSA)
+    return fail(GRLCU_ERR_UNSUPPORTED, "safe > 0 (the collision-claim table) is instantiated for predictor/sarsa only");
   if (cfg->algo == GRLCU_ALGO_AC)
   {
     // cfg/cart_double_pole/ac.yaml, cfg/pendulum/ac_tc.yaml, cfg/cart_pole/ac_tc.yaml of the reference
@@ -292,6 +295,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   p.target_kind = cfg->algo == GRLCU_ALGO_Q ? 1 : cfg->algo == GRLCU_ALGO_EXPECTED_SARSA ? 2 : 0;
   p.target_epsilon = cfg->target_epsilon;
   p.softmax_tau = cfg->sampler == GRLCU_SAMPLER_SOFTMAX ? cfg->softmax_tau : 0.;
+  p.safe = cfg->safe;
+  if (p.safe > 0) { p.mode = 1; p.force_slow = 1; }     // claim table: the reference's literal sequential update, uncached
   p.trace_cap = trace_capacity_for(cfg->gamma * cfg->lambda, cfg->trace);
   if (p.trace_cap < 0 || p.trace_cap > 160)
   {
@@ -303,7 +308,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   // hash order, kept for A/B runs and as the other side of tests/test_gpu_cached.py)
   p.tstride = (uint32_t)cfg->memory;
   grlcu_host::Layout lay;
-  if (!(getenv("GRLCU_LAYOUT") && atoi(getenv("GRLCU_LAYOUT")) == 0))
+  if (!(getenv("GRLCU_LAYOUT") && atoi(getenv("GRLCU_LAYOUT")) == 0) && cfg->safe == 0)
     lay = grlcu_host::build_layout(*cfg, p.proj.scaling, p.proj.wrap);
   if (lay.enabled)
   {
@@ -346,6 +351,14 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     r = dalloc(c, &c->ac.actor, n * (size_t)cfg->memory);
     c->ac.sigma = cfg->sigma; c->ac.actor_alpha = cfg->actor_alpha;
     c->ac.action_min = cfg->action_min; c->ac.action_max = cfg->action_max;
+  }
+  if (!r && p.safe > 0)
+  {
+    r = dalloc(c, &p.claims, n * (size_t)cfg->memory);
+    if (!r) r = dalloc(c, &p.prev_hash, n * T);
+    if (!r) r = dalloc(c, &p.pressure, n);
+    if (!r && cudaMemset(p.pressure, 0, n * sizeof(uint32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
+    if (!r && cudaMemset(p.prev_hash, 0, n * T * sizeof(uint32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
   }
   if (!r) r = dalloc(c, &p.state, n * c->S);
   if (!r) r = dalloc(c, &p.action, n);
@@ -450,6 +463,8 @@ static int launch_reset(grlcu_ctx *c, int what)
       c->launches++;
     }
   }
+  if ((what & GRLCU_RESET_TABLES) && p.claims)       // TileCodingProjector::reconfigure(action=reset), tile_coding.cpp:82-89
+    CU(cudaMemsetAsync(p.claims, 0xFF, (size_t)p.n * c->cfg.memory * sizeof(int32_t), c->stream));
   if (what & GRLCU_RESET_AGENTS) { k_reset_agents<<<grd, blk, 0, c->stream>>>(p); c->launches++; c->traces_live = false; }
   if (what & GRLCU_RESET_STATS) { k_reset_stats<<<grd, blk, 0, c->stream>>>(p); c->launches++; }
   CU(cudaGetLastError());
@@ -787,9 +802,12 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
       else if (roomy) k_run_ac<D, 16, false, 4><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0); \
       else k_run_ac<D, 16, false, 7><<<grd, c->block, 0, c->stream>>>(c->p, c->ac, begin, end, n_steps, 0);      \
     } while (0)
+#define CALL_SAFE(D) k_run<D, 16, 3, false, 7, false, true><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0)
     if (c->cfg.algo == GRLCU_ALGO_AC) DISPATCH_DYN(c, CALL_AC);
+    else if (c->p.safe > 0) DISPATCH_DYN(c, CALL_SAFE);
     else if (c->geo) CALL_G(0, true);              // the tile-major layout is instantiated for the pendulum (grlcu_layout.h)
     else DISPATCH_SARSA(c, CALL);
+#undef CALL_SAFE
 #undef CALL_AC
 #undef CALL
 #undef CALL_G
@@ -837,6 +855,16 @@ extern "C" int grlcu_layout_info(grlcu_ctx *c, int32_t *tile_major, uint32_t *ta
   if (table_stride) *table_stride = c->p.tstride;
   if (inbox_words) *inbox_words = c->inbox_words;
   if (shared_words) *shared_words = c->shared_words;
+  return 0;
+}
+
+extern "C" int grlcu_get_pressure(grlcu_ctx *c, uint32_t *out)
+{
+  if (!c || !out) return fail(GRLCU_ERR_ARG, "grlcu_get_pressure: bad arguments");
+  if (!c->p.pressure) return fail(GRLCU_ERR_ARG, "grlcu_get_pressure: the context has no claim table (safe = 0)");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(out, c->p.pressure, sizeof(uint32_t) * c->p.n, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
 
@@ -1043,7 +1071,9 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
   const int blk = 64, grd = ((int)n + blk - 1) / blk;
 #define CALL(D) k_replay<D, 16, 3, false><<<grd, blk, 0, c->stream>>>(c->p, io)
 #define CALL_AC(D) k_replay_ac<D, 16><<<grd, blk, 0, c->stream>>>(c->p, c->ac, io)
+#define CALL_SAFE(D) k_replay<D, 16, 3, false, true><<<grd, blk, 0, c->stream>>>(c->p, io)
   if (is_ac) DISPATCH_DYN(c, CALL_AC);
+  else if (c->p.safe > 0) DISPATCH_DYN(c, CALL_SAFE);
   else if (c->geo) k_replay<0, 16, 3, true><<<grd, blk, 0, c->stream>>>(c->p, io);
   else DISPATCH_SARSA(c, CALL);
 #undef CALL_AC

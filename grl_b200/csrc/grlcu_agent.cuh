@@ -83,6 +83,11 @@ struct Params
   double   *total_reward, *last_return, *last_test_return, *return_sum;
   const double *alpha_a, *lambda_a, *epsilon_a;   // optional per-agent hyper-parameters
   const double *start_override;                    // optional [S][n] start states (run_host)
+  // projector/tile_coding safe > 0 (tile_coding.h:116-148): per-agent collision-claim table and what goes with it
+  int32_t  safe;              // 0 off, 1 claim on the predictor's projections, 2 claim on every projection
+  int32_t  *claims;           // [n][memory] TileCodingProjector::indices_ (-1 = free)
+  uint32_t *prev_hash;        // [T][n] tile hashes of (prev_obs, prev_action): the predictor projects them again, claiming
+  uint32_t *pressure;         // [n] largest number of probe steps a lookup took (pressure_)
 };
 
 // Replay buffers on the device (same meaning as grlcu_replay_in/out, SoA [field][agent])
@@ -213,6 +218,23 @@ __device__ __forceinline__ int sample_action(const double (&q)[A], const Draws &
   return mai;
 }
 
+// TileCodingProjector::getFeatureLocation with a claim table (tile_coding.h:116-148): linear probing from h % memory
+// until the entry is h or free; `indices_[ii] != h` compares the int32 entry with the unsigned hash, `!= -1` as int.
+__device__ __noinline__ uint32_t probe_location(int32_t *claims, uint32_t memory, uint32_t h, bool claim, uint32_t *pressure)
+{
+  uint32_t ii = h % memory, collisions = 0;
+  // (a full table makes the reference probe forever; here the walk stops after one lap so that a mis-sized table cannot
+  // hang the GPU -- the pressure counter then reads `memory`)
+  while ((uint32_t)claims[ii] != h && claims[ii] != -1 && collisions < memory)
+  {
+    ++collisions;
+    if (++ii >= memory) ii = 0;
+  }
+  if (collisions > *pressure) *pressure = collisions;
+  if (claim) claims[ii] = (int32_t)h;
+  return ii;
+}
+
 constexpr int kMaxBlock = 64;     // threads per block of the fused kernels (shared index stash is sized for it)
 
 // h % memory (tile_coding.h:118) without a division: mask for powers of two, else the exact
@@ -296,7 +318,10 @@ struct Agent
 // reference's hash and logical index h % memory of every word.
 // The gathers are issued in two groups (actions 0..A-2, then action A-1 together with the T entries of
 // the previous projection p) to bound the registers holding loads in flight.
-template <int DYN, int T, int A, bool GEO, typename Resolve>
+// SAFE (projector safe > 0): the location of a hash comes from the agent's claim table (probe_location; the policy's
+// multi-projection claims only with safe > 1, tile_coding.h:66-72) and the hashes are kept in the stash rows
+// [A*T, 2*A*T) for the predictor, which projects again, claiming (agent_core).
+template <int DYN, int T, int A, bool GEO, bool SAFE, typename Resolve>
 __device__ __forceinline__ void q_values(const Params &p, const double *tbl, const double (&obs)[Dyn<DYN>::OBS],
                                          uint32_t *sid, double (&q)[A], const uint32_t (&pidx)[T],
                                          double (&vp)[T], bool with_p, uint32_t *hash_out, uint32_t *index_out,
@@ -358,8 +383,9 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
           uint32_t g = (h * m) ^ p.kact[aa][j];
           g = (g * m) ^ p.kj[j];
           g ^= g >> 13; g *= m; g ^= g >> 15;
-          const uint32_t x = reduce_index(p, g);
           if (hash_out) hash_out[((size_t)aa * T + j) * n + a] = g;
+          if (SAFE) { sid[(A * T + aa * T + j) * kMaxBlock] = g; continue; }    // located below, in the reference's order
+          const uint32_t x = reduce_index(p, g);
           if (index_out) index_out[((size_t)aa * T + j) * n + a] = x;
           if (!GEO) sid[(aa * T + j) * kMaxBlock] = x;
           else
@@ -370,6 +396,19 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
           }
         }
       }
+    }
+  }
+  if (SAFE)
+  {
+    // getFeatureLocation in the reference's order -- action by action, tiling by tiling (q.cpp:94-107 projects the
+    // variants one after the other): with safe = 2 every lookup claims, so the order decides who gets which slot
+    int32_t *claims = p.claims + (size_t)a * p.proj.memory;
+#pragma unroll 1
+    for (int k = 0; k < A * T; ++k)
+    {
+      const uint32_t x = probe_location(claims, (uint32_t)p.proj.memory, sid[(A * T + k) * kMaxBlock], p.safe > 1, p.pressure + a);
+      sid[k * kMaxBlock] = x;
+      if (index_out) index_out[(size_t)k * n + a] = x;
     }
   }
   // Phase 2: the gathers, issued in two groups (actions 0..A-2, then action A-1 together with p's T words) to

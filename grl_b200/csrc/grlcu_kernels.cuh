@@ -142,7 +142,11 @@ template <int T> struct CacheResolve
 //   act   : there is a next action to choose (TDAgent::start / step; false for TDAgent::end, td.cpp:76-81)
 //   learn : there is a transition to learn from (TDAgent::step / end of a learning episode, td.cpp:63-81)
 // Returns the policy's own action choice (-1 when !act); commits `force` instead when force >= 0 (replay).
-template <int DYN, int T, int A, bool CACHED, bool GEO>
+// SAFE (projector safe > 0, uncached kernels only): the policy looks its locations up in the agent's claim table at act
+// time (claiming only with safe > 1); the predictor then projects (prev_obs, prev_action) and (obs, action) AGAIN, claiming
+// both (sarsa.cpp:102-108 through Projector::project(base, variant), tile_coding.h:62-65), and reads Q(s', a') and Q(p) at
+// those locations -- which can differ from the act-time ones once a claim lands on a probe path.
+template <int DYN, int T, int A, bool CACHED, bool GEO, bool SAFE = false>
 __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                           uint32_t *sid, int a,
                                           const double (&obs)[Dyn<DYN>::OBS], double reward, bool act, bool learn,
@@ -157,8 +161,8 @@ __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, co
   {
     // act on the new observation first (td.cpp:63-74), then update with (s,a,r,s',a')
     double q[A];
-    if (CACHED) q_values<DYN, T, A, GEO>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, index_out, p.n, a, CacheResolve<T>{c});
-    else q_values<DYN, T, A, GEO>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, index_out, p.n, a, NoResolve());
+    if (CACHED) q_values<DYN, T, A, GEO, false>(p, tbl, obs, sid, q, ag.pidx, vp, learn, hash_out, index_out, p.n, a, CacheResolve<T>{c});
+    else q_values<DYN, T, A, GEO, SAFE>(p, tbl, obs, sid, q, ag.pidx, vp, learn && !SAFE, hash_out, index_out, p.n, a, NoResolve());
     own = sample_action<A>(q, d, ag.epsilon, test, p.softmax_tau);
     ai = force >= 0 ? force : own;
     if (o_q)
@@ -168,8 +172,31 @@ __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, co
     }
     qn = bootstrap_value<A>(q, ai, p.target_kind, p.target_epsilon);
   }
-  else if (learn)
+  else if (learn && !SAFE)
   {
+#pragma unroll
+    for (int j = 0; j < T; ++j) vp[j] = ld_tbl(tbl + ag.pidx[j]);
+  }
+  if (SAFE && learn)
+  {
+    int32_t *claims = p.claims + (size_t)a * p.proj.memory;
+    const uint32_t mem = (uint32_t)p.proj.memory;
+    // p = projector_->project(prev_obs, prev_action): claims
+#pragma unroll 1
+    for (int j = 0; j < T; ++j) ag.pidx[j] = probe_location(claims, mem, p.prev_hash[(size_t)j * p.n + a], true, p.pressure + a);
+    if (act)
+    {
+      // read(projector_->project(obs, action)): claims, then the sequential sum / T of linear.cpp:147-151
+      double r = 0;
+#pragma unroll 1
+      for (int j = 0; j < T; ++j)
+      {
+        const uint32_t x = probe_location(claims, mem, sid[(A * T + ai * T + j) * kMaxBlock], true, p.pressure + a);
+        sid[(ai * T + j) * kMaxBlock] = x;
+        r += ld_tbl(tbl + x);
+      }
+      qn = r / T;
+    }
 #pragma unroll
     for (int j = 0; j < T; ++j) vp[j] = ld_tbl(tbl + ag.pidx[j]);
   }
@@ -182,13 +209,18 @@ __device__ __forceinline__ int agent_core(const Params &p, Agent<DYN, T> &ag, co
   {
     set_prev_projection<DYN, T>(ag, sid, ai);
     ag.action = p.actions[ai];
+    if (SAFE)
+    {
+#pragma unroll 1
+      for (int j = 0; j < T; ++j) p.prev_hash[(size_t)j * p.n + a] = sid[(A * T + ai * T + j) * kMaxBlock];
+    }
   }
   return own;
 }
 
 // Episode start (online_learning.cpp:160-178): observe the start state, TDAgent::start /
 // FixedAgent::start (trace clear + first act).  Used by the replay kernel; k_run inlines the same sequence.
-template <int DYN, int T, int A, bool CACHED, bool GEO>
+template <int DYN, int T, int A, bool CACHED, bool GEO, bool SAFE = false>
 __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                               uint32_t *sid, int a, const Draws &d, bool test, double *o_q, int *o_ai)
 {
@@ -205,20 +237,20 @@ __device__ __forceinline__ void episode_start(const Params &p, Agent<DYN, T> &ag
   ag.total_reward = 0;
   ag.flags = (ag.flags & 16) | 1 | (test ? 2 : 0);       // also clears bit2 (start override pending)
   double qp, target, delta; int swept;
-  const int ai = agent_core<DYN, T, A, CACHED, GEO>(p, ag, c, tbl, sid, a, obs, 0., true, false, test, d, -1, nullptr, nullptr, o_q,
+  const int ai = agent_core<DYN, T, A, CACHED, GEO, SAFE>(p, ag, c, tbl, sid, a, obs, 0., true, false, test, d, -1, nullptr, nullptr, o_q,
                                                     qp, target, delta, swept);
   if (o_ai) *o_ai = ai;
 }
 
 // The agent half of one step (TDAgent::step / end, td.cpp:63-81; FixedAgent for test episodes).
-template <int DYN, int T, int A, bool CACHED, bool GEO>
+template <int DYN, int T, int A, bool CACHED, bool GEO, bool SAFE = false>
 __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, const Cache<T> &c, double *tbl,
                                           uint32_t *sid, int a,
                                           const double (&obs)[Dyn<DYN>::OBS], double reward, int terminal, bool test,
                                           const Draws &d, int force, uint32_t *hash_out, uint32_t *index_out, double *o_q,
                                           double &qp, double &target, double &delta, int &swept)
 {
-  return agent_core<DYN, T, A, CACHED, GEO>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !test, test, d, force,
+  return agent_core<DYN, T, A, CACHED, GEO, SAFE>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !test, test, d, force,
                                             hash_out, index_out, o_q, qp, target, delta, swept);
 }
 
@@ -229,12 +261,12 @@ __device__ __forceinline__ int agent_half(const Params &p, Agent<DYN, T> &ag, co
 // so 14 warps means 4 warps on some of them and the kernel is bounded at 128 registers per thread
 // (MINB = 7).  Launches with at most 8 warps per SM (BASELINE configs[2], [3]: 32,768 agents) use the
 // MINB = 4 instantiation, which may use up to 255 registers and does not spill.
-template <int DYN, int T, int A, bool CACHED, int MINB, bool GEO>
+template <int DYN, int T, int A, bool CACHED, int MINB, bool GEO, bool SAFE = false>
 __global__ void __launch_bounds__(kMaxBlock, MINB)
 k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_close)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
-  __shared__ uint32_t s_idx[A * T][kMaxBlock];
+  __shared__ uint32_t s_idx[(SAFE ? 2 : 1) * A * T][kMaxBlock];     // slots of Q(s', .) [+ their hashes: safe > 0]
   const int a = agent_begin + blockIdx.x * blockDim.x + threadIdx.x;
   if (a >= agent_end) return;
   uint32_t *sid = &s_idx[0][threadIdx.x];
@@ -301,7 +333,7 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_close)
     double qp, target, delta; int swept;
     Draws d; d.u = 1.; d.r_explore = 0; d.r_tie = 0;
     if (terminal != 2) d = next_draws<DYN, T>(p, ag, a, gid, test);
-    agent_core<DYN, T, A, CACHED, GEO>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !starting && !test, test, d, -1,
+    agent_core<DYN, T, A, CACHED, GEO, SAFE>(p, ag, c, tbl, sid, a, obs, reward, terminal != 2, !starting && !test, test, d, -1,
                                        nullptr, nullptr, nullptr, qp, target, delta, swept);
     if (!starting)
     {
@@ -333,12 +365,12 @@ __global__ void k_cache_close(Params p)
 
 // Replay: one agent-step per agent with states, observations, rewards, draws (and optionally the
 // committed action) fed from outside; emits everything observable for comparison.
-template <int DYN, int T, int A, bool GEO>
+template <int DYN, int T, int A, bool GEO, bool SAFE = false>
 __global__ void __launch_bounds__(kMaxBlock)
 k_replay(Params p, ReplayIO io)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
-  __shared__ uint32_t s_idx[A * T][kMaxBlock];
+  __shared__ uint32_t s_idx[(SAFE ? 2 : 1) * A * T][kMaxBlock];
   const int a = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = p.n;
   if (a >= n) return;
@@ -354,7 +386,7 @@ k_replay(Params p, ReplayIO io)
     for (int i = 0; i < S; ++i) ag.x[i] = io.start_state[(size_t)i * n + a];
     Draws d; d.u = io.start_u[a]; d.r_explore = io.start_r_explore[a]; d.r_tie = io.start_r_tie[a];
     int ai;
-    episode_start<DYN, T, A, false, GEO>(p, ag, Cache<T>(), tbl, sid, a, d, test, io.o_start_q, &ai);
+    episode_start<DYN, T, A, false, GEO, SAFE>(p, ag, Cache<T>(), tbl, sid, a, d, test, io.o_start_q, &ai);
     if (io.o_start_action_index) io.o_start_action_index[a] = ai;
     p.episode_ctr[a] += 1;
   }
@@ -384,7 +416,7 @@ k_replay(Params p, ReplayIO io)
   double qp, target, delta; int swept;
   Draws d; d.u = io.u[a]; d.r_explore = io.r_explore[a]; d.r_tie = io.r_tie[a];
   const int force = (io.force_action && terminal != 2) ? io.force_action[a] : -1;
-  const int own = agent_half<DYN, T, A, false, GEO>(p, ag, Cache<T>(), tbl, sid, a, obs, reward, terminal, test, d, force,
+  const int own = agent_half<DYN, T, A, false, GEO, SAFE>(p, ag, Cache<T>(), tbl, sid, a, obs, reward, terminal, test, d, force,
                                              io.o_hash, io.o_index, io.o_q, qp, target, delta, swept);
   if (terminal != 2)
   {

@@ -115,7 +115,7 @@ void CudaTileCodingProjector::configure(Configuration &config)
   wrapping_ = config["wrapping"].v();
   if (tilings_ != 16) throw bad_param("projector/tile_coding/cuda:tilings");       // kernels instantiated for 16
   if (memory_ < 1) throw bad_param("projector/tile_coding/cuda:memory");
-  if (safe_ != 0) throw bad_param("projector/tile_coding/cuda:safe");             // collision claiming: not on this path
+  if (safe_ < 0 || safe_ > 2) throw bad_param("projector/tile_coding/cuda:safe");   // 1, 2: per-agent collision-claim table (SARSA only)
   if (resolution_.empty() || resolution_.size() > GRLCU_MAX_DIMS) throw bad_param("projector/tile_coding/cuda:resolution");
   if (wrapping_.empty()) wrapping_ = Vector(resolution_.size(), 0.);
   if (wrapping_.size() != resolution_.size()) throw bad_param("projector/tile_coding:wrapping");
@@ -134,6 +134,7 @@ void CudaTileCodingProjector::contribute(CudaPath *p) const
 {
   p->cfg.tilings = tilings_;
   p->cfg.memory = memory_;
+  p->cfg.safe = safe_;
   for (size_t i = 0; i < resolution_.size(); ++i) { p->cfg.resolution[i] = resolution_[i]; p->cfg.wrapping[i] = wrapping_[i]; }
   p->have_projector = true;
 }

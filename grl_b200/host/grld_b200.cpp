@@ -19,12 +19,12 @@ static void print_config_json(const grlcu_config &c, int agents)
          "\"randomization\": %.17g, \"tilings\": %d, \"memory\": %d, \"obs_dims\": %d, \"n_actions\": %d, "
          "\"resolution\": %s, \"wrapping\": %s, \"actions\": %s, \"alpha\": %.17g, \"gamma\": %.17g, \"lambda\": %.17g, "
          "\"epsilon\": %.17g, \"trace\": %d, \"test_interval\": %d, \"init_min\": %.17g, \"init_max\": %.17g, \"seed\": %llu, \"algo\": %d, "
-         "\"sigma\": %.17g, \"actor_alpha\": %.17g, \"action_min\": %.17g, \"action_max\": %.17g, \"actor_resolution\": %s, \"actor_wrapping\": %s, \"target_epsilon\": %.17g, \"end_stop_penalty\": %d, \"sampler\": %d, \"softmax_tau\": %.17g}\n",
+         "\"sigma\": %.17g, \"actor_alpha\": %.17g, \"action_min\": %.17g, \"action_max\": %.17g, \"actor_resolution\": %s, \"actor_wrapping\": %s, \"target_epsilon\": %.17g, \"end_stop_penalty\": %d, \"sampler\": %d, \"softmax_tau\": %.17g, \"safe\": %d}\n",
          agents, c.dynamics, c.integration_steps, c.control_step, c.timeout, c.randomization, c.tilings, c.memory, c.obs_dims,
          c.n_actions, vec(c.resolution, dims).c_str(), vec(c.wrapping, dims).c_str(), vec(c.actions, c.n_actions).c_str(),
          c.alpha, c.gamma, c.lambda, c.epsilon, c.trace, c.test_interval, c.init_min, c.init_max, (unsigned long long)c.seed, c.algo,
          c.sigma, c.actor_alpha, c.action_min, c.action_max, vec(c.actor_resolution, c.algo == GRLCU_ALGO_AC ? c.obs_dims : 0).c_str(),
-         vec(c.actor_wrapping, c.algo == GRLCU_ALGO_AC ? c.obs_dims : 0).c_str(), c.target_epsilon, c.end_stop_penalty, c.sampler, c.softmax_tau);
+         vec(c.actor_wrapping, c.algo == GRLCU_ALGO_AC ? c.obs_dims : 0).c_str(), c.target_epsilon, c.end_stop_penalty, c.sampler, c.softmax_tau, c.safe);
 }
 
 // -i: drive the one-agent role interfaces of the CUDA objects (Environment::start/step, Projector::project,

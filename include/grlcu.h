@@ -78,6 +78,9 @@ typedef struct grlcu_config
                                  `epsilon`) | GRLCU_SAMPLER_SOFTMAX (softmax.cpp:48-101, uses `softmax_tau`); test
                                  episodes always use sampler/greedy */
   double  softmax_tau;        /* sampler/softmax tau: temperature of the Boltzmann distribution (softmax.cpp:34) */
+  int32_t safe;               /* projector/tile_coding safe (tile_coding.cpp:35-43, tile_coding.h:116-148): 0 = plain hashing;
+                                 1 / 2 = collision-claim table (linear probing over int32 indices_[memory] per agent; claim on
+                                 the predictor's projections / on every projection).  SARSA only; runs the uncached kernels */
 } grlcu_config;
 
 typedef struct grlcu_ctx grlcu_ctx;
@@ -266,6 +269,10 @@ int grlcu_group_results(grlcu_group *group, grlcu_results *results, double *coll
  * shared_words = those of them whose index collides with an earlier tile's (they live in that tile's sector).
  * Any pointer may be NULL. */
 int grlcu_layout_info(grlcu_ctx *ctx, int32_t *tile_major, uint32_t *table_stride, uint32_t *inbox_words, uint32_t *shared_words);
+
+/* projector/tile_coding safe > 0: per agent, the largest number of probe steps a lookup in its claim table has taken
+ * (TileCodingProjector::pressure_, tile_coding.h:131-136: the reference warns above 7).  out: n_agents values. */
+int grlcu_get_pressure(grlcu_ctx *ctx, uint32_t *out);
 
 /* Trace capacity (entries) the context allocated per agent. */
 int grlcu_trace_capacity(grlcu_ctx *ctx);

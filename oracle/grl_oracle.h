@@ -99,6 +99,7 @@ typedef struct orc_config
   int32_t end_stop_penalty;   /* task/cart_pole/swingup: end_stop_penalty (cart_pole.h:75 default 1) */
   int32_t sampler;            /* ORC_SAMPLER_*: sampler/epsilon_greedy | sampler/softmax (learning policy) */
   double  softmax_tau;        /* sampler/softmax: tau */
+  int32_t safe;               /* projector/tile_coding: safe (0 off, 1 claim on write, 2 claim always; tile_coding.h:116-148) */
 } orc_config;
 
 /* Everything observable about one agent-step (one iteration of
@@ -156,6 +157,9 @@ void orc_scaling(const double *resolution, const double *wrapping, int dims, int
                  double *scaling, int32_t *iwrap);
 void orc_project(const double *resolution, const double *wrapping, int dims, int tilings,
                  int32_t memory, const double *in, uint32_t *hash, uint32_t *index);
+/* the tile hashes alone (createHashSum per tiling), before getFeatureLocation */
+void orc_project_hashes(const double *resolution, const double *wrapping, int dims, int tilings,
+                        const double *in, uint32_t *hash);
 void orc_eom(int dynamics, const double *x, double u, double *xd);
 void orc_rk4(int dynamics, double tau, int steps, const double *x, double u, double *next);
 int  orc_state_dims(int dynamics);
@@ -188,6 +192,8 @@ double *orc_actor_table(orc_agent *a);      /* memory doubles (AC only) */
 int orc_step(orc_agent *a, orc_record *rec);
 /* run n learning steps without recording (CPU baseline timing) */
 uint64_t orc_run(orc_agent *a, uint64_t n_steps);
+/* projector/tile_coding safe > 0: the largest number of probe steps any lookup of this agent took (pressure_, tile_coding.h:131-136) */
+uint64_t orc_pressure(const orc_agent *a);
 /* run n agent-steps, test-episode steps included (the count grlcu_run takes) */
 void orc_run_total(orc_agent *a, uint64_t n_steps);
 /* statistics */

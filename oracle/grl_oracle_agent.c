@@ -35,6 +35,8 @@ struct orc_agent
   double alpha, lambda, epsilon;      /* per-agent (sweep) */
   double *table;                      /* Q (SARSA) or V (AC critic) */
   double *actor;                      /* AC actor table */
+  int32_t *claims;                    /* safe > 0: TileCodingProjector::indices_ (tile_coding.cpp:51-56), -1 = free */
+  uint64_t pressure;                  /* TileCodingProjector::pressure_ */
   /* glibc mode streams (utils.h:84-137) */
   struct drand48_data randgen;        /* thread-local RandGen: table init + task start */
   struct drand48_data sampler;        /* EpsilonGreedySampler::rand_ */
@@ -314,9 +316,44 @@ static int sample(orc_agent *a, const double *q, int test, act_draws *d)
   return mai;
 }
 
+/* ---- TileCodingProjector::getFeatureLocation (tile_coding.h:116-148) ------ */
+static uint32_t feature_location(orc_agent *a, uint32_t h, int claim)
+{
+  const uint32_t memory = (uint32_t)a->c.memory;
+  uint32_t ii = h % memory;
+  if (a->claims)
+  {
+    uint64_t collisions = 0;
+    /* `indices_[ii] != h` compares the int32 entry with the unsigned hash (usual arithmetic conversions),
+     * `indices_[ii] != -1` is an int comparison */
+    while ((uint32_t)a->claims[ii] != h && a->claims[ii] != -1)
+    {
+      collisions++;
+      if (++ii >= memory) ii = 0;
+    }
+    if (collisions > a->pressure) a->pressure = collisions;
+    if (claim) a->claims[ii] = (int32_t)h;
+  }
+  return ii;
+}
+
+/* TileCodingProjector::_project(in, claim) (tile_coding.cpp:103-149) for this agent's projector */
+static void agent_project(orc_agent *a, const double *in, int dims, int claim, uint32_t *hash, uint32_t *idx)
+{
+  uint32_t h[ORC_MAX_TILINGS];
+  orc_project_hashes(a->c.resolution, a->c.wrapping, dims, a->c.tilings, in, h);
+  for (int j = 0; j < a->c.tilings; ++j)
+  {
+    if (hash) hash[j] = h[j];
+    idx[j] = feature_location(a, h[j], claim);
+  }
+}
+
+uint64_t orc_pressure(const orc_agent *a) { return a->pressure; }
+
 /* ---- QPolicy (q.cpp:94-107,129-155) ------------------------------------- */
 
-static void q_values(const orc_agent *a, const double *obs, uint32_t *hash, uint32_t *idx, double *q)
+static void q_values(orc_agent *a, const double *obs, uint32_t *hash, uint32_t *idx, double *q)
 {
   const orc_config *c = &a->c;
   double in[ORC_MAX_DIMS];
@@ -324,8 +361,8 @@ static void q_values(const orc_agent *a, const double *obs, uint32_t *hash, uint
   for (int aa = 0; aa < c->n_actions; ++aa)
   {
     in[c->obs_dims] = c->actions[aa];       /* extend(obs, variant) */
-    orc_project(c->resolution, c->wrapping, c->obs_dims + 1, c->tilings, c->memory, in,
-                hash ? hash + aa * c->tilings : NULL, idx + aa * c->tilings);
+    /* Projector::project(base, variants, out): claims only with safe > 1 (tile_coding.h:66-72) */
+    agent_project(a, in, c->obs_dims + 1, c->safe > 1, hash ? hash + aa * c->tilings : NULL, idx + aa * c->tilings);
     q[aa] = table_read(a->table, idx + aa * c->tilings, c->tilings, -DBL_MAX, DBL_MAX);
   }
 }
@@ -437,6 +474,11 @@ orc_agent *orc_create(const orc_config *c, uint64_t agent_id)
   if (c->algo == ORC_ALGO_AC)
     a->actor = (double *)malloc((size_t)c->memory * sizeof(double));
   trace_clear(&a->trace);
+  if (c->safe > 0)
+  {
+    a->claims = (int32_t *)malloc((size_t)c->memory * sizeof(int32_t));
+    for (int32_t ii = 0; ii < c->memory; ++ii) a->claims[ii] = -1;
+  }
 
   if (c->rng == ORC_RNG_GLIBC)
   {
@@ -472,7 +514,7 @@ orc_agent *orc_create(const orc_config *c, uint64_t agent_id)
 void orc_destroy(orc_agent *a)
 {
   if (!a) return;
-  free(a->table); free(a->actor); free(a);
+  free(a->table); free(a->actor); free(a->claims); free(a);
 }
 
 void orc_set_hyper(orc_agent *a, double alpha, double lambda, double epsilon)
@@ -506,6 +548,15 @@ void orc_get_state(const orc_agent *a, double *state, double *prev_obs, double *
 double orc_pending_action(const orc_agent *a) { return a->action; }
 
 static int ac_step(orc_agent *a, orc_record *rec);
+
+/* safe > 0: the predictor's own projection of (prev_obs, prev_action), claiming (sarsa.cpp:102) */
+static void reproject_prev(orc_agent *a)
+{
+  double in[ORC_MAX_DIMS];
+  for (int i = 0; i < a->c.obs_dims; ++i) in[i] = a->prev_obs[i];
+  in[a->c.obs_dims] = a->prev_action;
+  agent_project(a, in, a->c.obs_dims + 1, 1, NULL, a->prev_idx);
+}
 
 /* ---- one agent-step (online_learning.cpp:154-222) ------------------------ */
 int orc_step(orc_agent *a, orc_record *rec)
@@ -562,7 +613,11 @@ int orc_step(orc_agent *a, orc_record *rec)
   if (terminal == 2)
   {
     /* TDAgent::end (td.cpp:76-81): update without bootstrap; FixedAgent::end: nothing */
-    if (!a->test) sarsa_update(a, reward, NULL, NULL, rec);
+    if (!a->test)
+    {
+      if (c->safe > 0) reproject_prev(a);
+      sarsa_update(a, reward, NULL, NULL, rec);
+    }
   }
   else
   {
@@ -581,7 +636,20 @@ int orc_step(orc_agent *a, orc_record *rec)
       }
       rec->action_index = ai;
     }
-    if (!a->test) sarsa_update(a, reward, idx + ai * T, q, rec);
+    if (!a->test)
+    {
+      if (c->safe > 0)
+      {
+        /* SARSAPredictor::criticize (sarsa.cpp:102-108) projects (prev_obs, prev_action) and then (obs, action) itself,
+         * through Projector::project(base, variant) -> project(in): BOTH claim their locations (tile_coding.h:62-65) */
+        double in[ORC_MAX_DIMS];
+        reproject_prev(a);
+        for (int i = 0; i < c->obs_dims; ++i) in[i] = obs[i];
+        in[c->obs_dims] = action;
+        agent_project(a, in, c->obs_dims + 1, 1, NULL, idx + ai * T);
+      }
+      sarsa_update(a, reward, idx + ai * T, q, rec);
+    }
     memcpy(a->prev_obs, obs, sizeof(obs));
     a->prev_action = action;
     memcpy(a->prev_idx, idx + ai * T, (size_t)T * sizeof(uint32_t));

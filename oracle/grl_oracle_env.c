@@ -100,6 +100,13 @@ void orc_project(const double *resolution, const double *wrapping, int dims, int
   }
 }
 
+void orc_project_hashes(const double *resolution, const double *wrapping, int dims, int tilings,
+                        const double *in, uint32_t *hash)
+{
+  uint32_t index[ORC_MAX_TILINGS];
+  orc_project(resolution, wrapping, dims, tilings, 1, in, hash, index);
+}
+
 int orc_state_dims(int dynamics)
 {
   return dynamics == ORC_DYN_PENDULUM ? 3 : dynamics == ORC_DYN_CART_POLE ? 5 : 7;

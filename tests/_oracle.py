@@ -37,6 +37,7 @@ class Config(C.Structure):
         ("actor_resolution", C.c_double * MAX_DIMS), ("actor_wrapping", C.c_double * MAX_DIMS),
         ("target_epsilon", C.c_double),
         ("end_stop_penalty", C.c_int32), ("sampler", C.c_int32), ("softmax_tau", C.c_double),
+        ("safe", C.c_int32),
     ]
 
     def __init__(self, *a, **kw):

@@ -340,3 +340,57 @@ def test_run_host_start_states_apply_to_the_next_episode_an_agent_begins(G):
         assert np.allclose(st3[:, 2], 0.03) and np.all(np.abs(st3[:, 0] + 2.0) < 0.2)
     finally:
         b.close()
+
+
+@pytest.mark.parametrize("safe,mem,steps", [(1, 8209, 300), (2, 16411, 300), (1, 65536, 320)])
+def test_replay_collision_claim_table(G, orc, safe, mem, steps):
+    """projector/tile_coding `safe` > 0 (tile_coding.h:116-148): per-agent claim table with linear probing; the policy's
+    multi-projection claims only with safe = 2, the predictor's own projections of (s, a) and (s', a') always do, so a
+    location can move between the act-time read and the update.  Indices, actions, traces, Q-values and tables bit-exact in
+    replay, and the pressure counter (longest probe walk) equal.  Table sizes leave free slots for every claim."""
+    kw = dict(randomization=1.0, test_interval=3, safe=safe)
+    _replay(G, G.pendulum_config, O.pendulum_config, n=32, steps=steps, mem=mem, **kw)
+    # pressure: run a second, shorter pair by hand to read both counters
+    cfg, oc = G.pendulum_config(memory=mem, **kw), O.pendulum_config(memory=mem, **kw)
+    b, ob = G.Batch(cfg, 16), O.OracleBatch(oc, 16)
+    try:
+        for t in range(120):
+            d = ob.step()
+            inp = dict(d)
+            inp["force_action"] = np.maximum(d["action_index"], 0).astype(np.int32)
+            b.replay_step(inp, want_trace=False)
+        orc.orc_pressure.restype = C.c_uint64
+        orc.orc_pressure.argtypes = [C.c_void_p]
+        want = np.array([orc.orc_pressure(a) for a in ob.agents], dtype=np.uint32)
+        assert np.array_equal(b.pressure(), want)
+    finally:
+        b.close(); ob.close()
+
+
+def test_collision_claim_table_free_running_and_limits(G, orc):
+    """The fused kernel with a claim table against the free-running oracle, agent by agent; safe is SARSA-only."""
+    kw = dict(memory=65536, randomization=1.0, test_interval=4, safe=1, epsilon=0.2)
+    cfg, oc = G.pendulum_config(**kw), O.pendulum_config(**kw)
+    n, steps = 128, 260
+    orc.orc_run_total.restype = None
+    orc.orc_run_total.argtypes = [C.c_void_p, C.c_uint64]
+    b = G.Batch(cfg, n, first_agent_id=77)
+    try:
+        b.run(100); b.run(steps - 100)
+        res = b.results()
+        for i in range(n):
+            a = orc.orc_create(C.byref(oc), 77 + i)
+            orc.orc_run_total(a, steps)
+            s, e, w, lr = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_double()
+            orc.orc_stats(a, C.byref(s), C.byref(e), C.byref(w), C.byref(lr), None)
+            t = np.ctypeslib.as_array(orc.orc_table(a), shape=(cfg.memory,))
+            assert (int(res["steps"][i]), int(res["episodes"][i]), int(res["swept"][i])) == (s.value, e.value, w.value), i
+            assert abs(res["last_return"][i] - lr.value) <= RTOL * abs(lr.value), i
+            assert np.allclose(b.get_table(i), t, rtol=RTOL, atol=0), i
+            orc.orc_destroy(a)
+    finally:
+        b.close()
+    with pytest.raises(G.GrlcuError):
+        G.Batch(G.pendulum_config(memory=4096, safe=1, algo=O.ALGO_Q), 2)
+    with pytest.raises(G.GrlcuError):
+        G.Batch(G.pendulum_config(memory=4096, safe=3), 2)

@@ -582,3 +582,15 @@ def test_grld_on_two_gpus_equals_one_gpu(grld, tmp_path):
     assert strip(str(tmp_path / "one") + "-0.txt") == strip(str(tmp_path / "two") + "-0.txt")
     assert open(str(tmp_path / "one") + "-0-cells.txt").read() == open(str(tmp_path / "two") + "-0-cells.txt").read()
     assert "NCCL all-gather" in outs["two"] and "NCCL all-gather" not in outs["one"]
+
+
+def test_safe_parameter_reaches_the_c_abi(grld, tmp_path):
+    """projector/tile_coding `safe` (tile_coding.cpp:35-43): 0, 1, 2 accepted and handed to the C ABI; 3 is illegal."""
+    base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
+    for v, ok in ((0, True), (1, True), (2, True), (3, False)):
+        p = tmp_path / ("safe%d.yaml" % v)
+        p.write_text(base.replace("        tilings: 16\n", "        tilings: 16\n        safe: %d\n" % v))
+        rc, out, err = check(grld, str(p))
+        assert (rc == 0) == ok, (v, err)
+        if ok:
+            assert json.loads(out)["safe"] == v
