@@ -344,11 +344,13 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     if (!r && cudaMemset(p.geo.mismatch, 0, sizeof(int32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
     if (!r) r = dalloc(c, &c->d_stage, (size_t)cfg->memory);
   }
+  if (is_ac) p.tstride = 2u * (uint32_t)cfg->memory;      // interleaved {critic, actor} pairs (grlcu_ac.cuh)
   if (!r) r = dalloc(c, &p.table, n * (size_t)p.tstride);
   memset(&c->ac, 0, sizeof(c->ac));
   if (!r && is_ac)
   {
-    r = dalloc(c, &c->ac.actor, n * (size_t)cfg->memory);
+    c->ac.actor = p.table + 1;
+    r = dalloc(c, &c->d_stage, (size_t)cfg->memory);
     c->ac.sigma = cfg->sigma; c->ac.actor_alpha = cfg->actor_alpha;
     c->ac.action_min = cfg->action_min; c->ac.action_max = cfg->action_max;
   }
@@ -449,19 +451,16 @@ static int launch_reset(grlcu_ctx *c, int what)
   if (what & GRLCU_RESET_TABLES)
   {
     const int64_t work = ((int64_t)c->cfg.memory + 1) / 2 * p.n;
-    if (c->geo)
+    if (c->ac.actor)
+      k_table_init_pairs<<<grid_for((int64_t)c->cfg.memory * p.n, 256, 148 * 32), 256, 0, c->stream>>>(
+          p.table, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max);
+    else if (c->geo)
       k_table_init_phys<<<grid_for((int64_t)p.tstride * p.n, 256, 148 * 32), 256, 0, c->stream>>>(
           p.table, p.n, p.tstride, p.geo.iperm, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_TABLE);
     else
       k_table_init<<<grid_for(work, 256, 148 * 32), 256, 0, c->stream>>>(
           p.table, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_TABLE);
     c->launches++;
-    if (c->ac.actor)
-    {
-      k_table_init<<<grid_for(work, 256, 148 * 32), 256, 0, c->stream>>>(
-          c->ac.actor, p.n, c->cfg.memory, p.first_id, p.seed, c->cfg.init_min, c->cfg.init_max, STREAM_ACTOR_TABLE);
-      c->launches++;
-    }
   }
   if ((what & GRLCU_RESET_TABLES) && p.claims)       // TileCodingProjector::reconfigure(action=reset), tile_coding.cpp:82-89
     CU(cudaMemsetAsync(p.claims, 0xFF, (size_t)p.n * c->cfg.memory * sizeof(int32_t), c->stream));
@@ -654,26 +653,26 @@ extern "C" int grlcu_task_start(grlcu_ctx *c, int64_t n, int32_t test, const dou
 // [lo, hi]: the representation's output_min / output_max (+-DBL_MAX when unset, linear.cpp:88-98); the read is
 // clamped to it (linear.cpp:179-180) and, with limit = 1, so is every updated weight (linear.cpp:207-211)
 // perm: logical index -> physical slot (struct Geo), or NULL
-__global__ void k_table_read(const double *tbl, const uint32_t *perm, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
+__global__ void k_table_read(const double *tbl, const uint32_t *perm, int shift, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
                              double *value, int *bad)
 {
   double r = 0;
   for (int i = 0; i < n_idx; ++i)
   {
     if (idx[i] >= memory) { *bad = 1; return; }
-    r += tbl[perm ? perm[idx[i]] : idx[i]];
+    r += tbl[perm ? perm[idx[i]] : idx[i] << shift];
   }
   *value = fmin(fmax(r / n_idx, lo), hi);
 }
 
-__global__ void k_table_update(double *tbl, const uint32_t *perm, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
+__global__ void k_table_update(double *tbl, const uint32_t *perm, int shift, int n_idx, const uint64_t *idx, uint64_t memory, double lo, double hi,
                                double delta, int *bad)
 {
   for (int i = 0; i < n_idx; ++i)
   {
     if (idx[i] == ~0ull) continue;                    // IndexProjection::invalid_index()
     if (idx[i] >= memory) { *bad = 1; return; }
-    const uint64_t s = perm ? perm[idx[i]] : idx[i];
+    const uint64_t s = perm ? perm[idx[i]] : idx[i] << shift;
     tbl[s] = fmin(fmax(tbl[s] + delta, lo), hi);
   }
 }
@@ -692,10 +691,11 @@ static int table_view(grlcu_ctx *c, bool actor, int32_t agent, int32_t n_idx, co
   CU(cudaMemcpyAsync(d_i, idx, sizeof(uint64_t) * n_idx, cudaMemcpyHostToDevice, c->stream));
   CU(cudaMemsetAsync(d_bad, 0, sizeof(int), c->stream));
   double *tbl = (actor ? c->ac.actor : c->p.table) + (size_t)agent * c->p.tstride;
+  const int shift = c->ac.actor ? 1 : 0;          // actor-critic: pair x at doubles [2x, 2x + 1]
   const double lo = actor ? c->ac.action_min : -DBL_MAX, hi = actor ? c->ac.action_max : DBL_MAX;
   const uint32_t *perm = c->geo ? c->p.geo.perm : nullptr;
-  if (value) k_table_read<<<1, 1, 0, c->stream>>>(tbl, perm, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, d_v, d_bad);
-  else k_table_update<<<1, 1, 0, c->stream>>>(tbl, perm, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, delta, d_bad);
+  if (value) k_table_read<<<1, 1, 0, c->stream>>>(tbl, perm, shift, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, d_v, d_bad);
+  else k_table_update<<<1, 1, 0, c->stream>>>(tbl, perm, shift, n_idx, d_i, (uint64_t)c->cfg.memory, lo, hi, delta, d_bad);
   c->launches++;
   CU(cudaGetLastError());
   int bad = 0;
@@ -941,7 +941,14 @@ extern "C" int grlcu_get_table(grlcu_ctx *c, int32_t agent, double *out)
   CU(cudaSetDevice(c->device));
   if (int r = ensure_plain(c)) return r;
   const double *src = c->p.table + (size_t)agent * c->p.tstride;
-  if (c->geo)
+  if (c->ac.actor)
+  {
+    k_table_gather_pairs<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(src, c->cfg.memory, c->d_stage);
+    c->launches++;
+    CU(cudaGetLastError());
+    src = c->d_stage;
+  }
+  else if (c->geo)
   {
     // physical (tile-major) -> the reference's logical order
     k_table_gather<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(src, c->p.geo.perm, c->cfg.memory, c->d_stage);
@@ -969,7 +976,14 @@ extern "C" int grlcu_set_table(grlcu_ctx *c, int32_t agent, const double *in)
       return fail(GRLCU_ERR_ARG, "grlcu_set_table: entry %d holds the NaN pattern 0x%08X........ that the kernels reserve", x, kSentinelHi);
   }
   double *dst = c->p.table + (size_t)agent * c->p.tstride;
-  if (c->geo)
+  if (c->ac.actor)
+  {
+    CU(cudaMemcpyAsync(c->d_stage, in, sizeof(double) * c->cfg.memory, cudaMemcpyHostToDevice, c->stream));
+    k_table_scatter_pairs<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(dst, c->cfg.memory, c->d_stage);
+    c->launches++;
+    CU(cudaGetLastError());
+  }
+  else if (c->geo)
   {
     CU(cudaMemcpyAsync(c->d_stage, in, sizeof(double) * c->cfg.memory, cudaMemcpyHostToDevice, c->stream));
     k_table_scatter<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(dst, c->p.geo.perm, c->cfg.memory, c->d_stage);
@@ -987,8 +1001,10 @@ extern "C" int grlcu_get_actor_table(grlcu_ctx *c, int32_t agent, double *out)
   if (!c || !out || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_get_actor_table: bad arguments");
   if (!c->ac.actor) return fail(GRLCU_ERR_ARG, "grlcu_get_actor_table: not an actor-critic context");
   CU(cudaSetDevice(c->device));
-  CU(cudaMemcpyAsync(out, c->ac.actor + (size_t)agent * c->cfg.memory, sizeof(double) * c->cfg.memory,
-                     cudaMemcpyDeviceToHost, c->stream));
+  k_table_gather_pairs<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(c->ac.actor + (size_t)agent * c->p.tstride, c->cfg.memory, c->d_stage);
+  c->launches++;
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out, c->d_stage, sizeof(double) * c->cfg.memory, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -998,8 +1014,10 @@ extern "C" int grlcu_set_actor_table(grlcu_ctx *c, int32_t agent, const double *
   if (!c || !in || agent < 0 || agent >= c->p.n) return fail(GRLCU_ERR_ARG, "grlcu_set_actor_table: bad arguments");
   if (!c->ac.actor) return fail(GRLCU_ERR_ARG, "grlcu_set_actor_table: not an actor-critic context");
   CU(cudaSetDevice(c->device));
-  CU(cudaMemcpyAsync(c->ac.actor + (size_t)agent * c->cfg.memory, in, sizeof(double) * c->cfg.memory,
-                     cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->d_stage, in, sizeof(double) * c->cfg.memory, cudaMemcpyHostToDevice, c->stream));
+  k_table_scatter_pairs<<<grid_for(c->cfg.memory, 256), 256, 0, c->stream>>>(c->ac.actor + (size_t)agent * c->p.tstride, c->cfg.memory, c->d_stage);
+  c->launches++;
+  CU(cudaGetLastError());
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }

@@ -11,6 +11,12 @@
 // indices addresses both per-agent tables.  The critic update is sarsa_update() (grlcu_agent.cuh) verbatim.
 // The actor table is clamped to [action_min, action_max] on every write (linear.cpp:207-211, limit = 1)
 // and on every read (linear.cpp:179-180).
+//
+// Physical layout: because one index x addresses both tables and the agent always reads (and writes) the critic's and the
+// actor's word of an index together, the two tables of an agent are INTERLEAVED: pair x = {critic[x], actor[x]} at doubles
+// [2x, 2x + 1] of one array (`critic` = base, `actor` = base + 1, physical slot = 2x).  One 16-byte request fetches both
+// (ld_tbl2), and the actor store and the critic's directory sentinel of an index dirty ONE sector.  The logical index x
+// (replay, grlcu_get_table / get_actor_table, checkpoints) is slot >> 1; the trace ring and prev_idx hold slots.
 #pragma once
 #include "grlcu_agent.cuh"
 #include "grlcu_cached.cuh"
@@ -36,7 +42,7 @@ __device__ __forceinline__ void project_obs(const Params &p, const double (&obs)
   {
     const uint32_t h = tile_hash_of<OBS, T>(p.proj, q, j);
     if (hash_out) hash_out[(size_t)j * stride] = h;
-    sid[j * kMaxBlock] = reduce_index(p, h);
+    sid[j * kMaxBlock] = reduce_index(p, h) * 2u;       // physical slot of the {critic, actor} pair
   }
 }
 
@@ -122,8 +128,8 @@ __device__ __forceinline__ void ac_core(const Params &p, const ACParams &ac, Age
 #pragma unroll
     for (int j = 0; j < T; ++j)
     {
-      const uint32_t x = sid[j * kMaxBlock];
-      wa[j] = ld_tbl(actor + x); wc[j] = ld_tbl(critic + x);
+      const double2 w = ld_tbl2(critic + sid[j * kMaxBlock]);     // {critic, actor} of one index: one request
+      wc[j] = w.x; wa[j] = w.y;
     }
 #pragma unroll
     for (int j = 0; j < T; ++j) { pi += wa[j]; vnext += CACHED ? resolve<T>(c, wc[j]) : wc[j]; }
@@ -149,7 +155,7 @@ __device__ __forceinline__ void ac_core(const Params &p, const ACParams &ac, Age
   {
     double ua[T], vp[T];
 #pragma unroll
-    for (int j = 0; j < T; ++j) { ua[j] = ld_tbl(actor + ag.pidx[j]); vp[j] = ld_tbl(critic + ag.pidx[j]); }
+    for (int j = 0; j < T; ++j) { const double2 w = ld_tbl2(critic + ag.pidx[j]); vp[j] = w.x; ua[j] = w.y; }
     ac_update<DYN, T, CACHED>(p, ac, ag, c, critic, actor, a, reward, act, vnext, ua, vp, o.u, qp, target, delta, swept);
   }
   if (act)
@@ -161,7 +167,7 @@ __device__ __forceinline__ void ac_core(const Params &p, const ACParams &ac, Age
     if (index_out)
     {
 #pragma unroll
-      for (int j = 0; j < T; ++j) index_out[(size_t)j * p.n] = ag.pidx[j];
+      for (int j = 0; j < T; ++j) index_out[(size_t)j * p.n] = ag.pidx[j] >> 1;     // logical index
     }
     o.pi = pi; o.vnext = vnext; o.action = action;
   }
@@ -181,7 +187,7 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
   Agent<DYN, T> ag;
   ag.load(p, a);
   double *critic = p.table + (size_t)a * p.tstride;
-  double *actor = ac.actor + (size_t)a * p.tstride;
+  double *actor = critic + 1;                  // interleaved pairs
   const uint64_t gid = (uint64_t)(p.first_id + a);
   Cache<T> c;
   c.bind(p, a);
@@ -266,7 +272,7 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
   Agent<DYN, T> ag;
   ag.load(p, a);
   double *critic = p.table + (size_t)a * p.tstride;
-  double *actor = ac.actor + (size_t)a * p.tstride;
+  double *actor = critic + 1;                  // interleaved pairs
   const uint64_t gid = (uint64_t)(p.first_id + a);
   const bool test = io.test[a] != 0;
   ACOut o;
@@ -327,8 +333,11 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
     {
       const int pos = ring_pos(ag.head, k, p.trace_cap);
       for (int j = 0; j < T; ++j)
-        io.o_trace_index[((size_t)k * T + j) * n + a] =
-            k < ag.len ? p.trace_idx[((size_t)pos * T + j) * n + a] : kInvalidIndex;
+      {
+        uint32_t x = k < ag.len ? p.trace_idx[((size_t)pos * T + j) * n + a] : kInvalidIndex;
+        if (x != kInvalidIndex) x >>= 1;           // the ring holds physical slots
+        io.o_trace_index[((size_t)k * T + j) * n + a] = x;
+      }
     }
   if (!test) ag.dsteps++;
   if (terminal) ag.episode_end(p, a, test);

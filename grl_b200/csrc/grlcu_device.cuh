@@ -27,6 +27,14 @@ __device__ __forceinline__ double ld_tbl(const double *p)
   asm volatile("ld.global.L2::64B.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
   return v;
 }
+// two adjacent table words with one 16-byte request (the actor-critic's interleaved {critic, actor} pairs)
+__device__ __forceinline__ double2 ld_tbl2(const double *p)
+{
+  double2 v;
+  asm volatile("ld.global.L2::64B.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+  return v;
+}
+
 // ---- Philox4x32-10 (Salmon et al., SC'11) -------------------------------------------------
 struct Philox4 { uint32_t w[4]; };
 

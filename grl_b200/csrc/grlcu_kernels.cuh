@@ -51,6 +51,35 @@ __global__ void k_table_init_phys(double *table, int32_t n, uint32_t tstride, co
   }
 }
 
+// Actor-critic: the interleaved {critic, actor} pairs of every agent (grlcu_ac.cuh): pair x = doubles [2x, 2x + 1] of the
+// agent's row; critic values from Philox stream STREAM_TABLE, actor values from STREAM_ACTOR_TABLE, each exactly what
+// k_table_init gives entry x (half x & 1 of counter x / 2).  One thread per pair, 16-byte coalesced stores.
+__global__ void k_table_init_pairs(double *table, int32_t n, int32_t memory, int64_t first_id, uint64_t seed,
+                                   double init_min, double init_max)
+{
+  const int64_t total = (int64_t)memory * n;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x)
+  {
+    const int64_t a = t / memory;
+    const uint32_t x = (uint32_t)(t - a * memory);
+    const Philox4 wc = philox_for(seed, (uint64_t)(first_id + a), STREAM_TABLE, (uint64_t)(x >> 1));
+    const Philox4 wa = philox_for(seed, (uint64_t)(first_id + a), STREAM_ACTOR_TABLE, (uint64_t)(x >> 1));
+    const double vc = init_min + ((x & 1u) ? u53(wc.w[2], wc.w[3]) : u53(wc.w[0], wc.w[1])) * (init_max - init_min);
+    const double va = init_min + ((x & 1u) ? u53(wa.w[2], wa.w[3]) : u53(wa.w[0], wa.w[1])) * (init_max - init_min);
+    *reinterpret_cast<double2 *>(table + 2 * t) = make_double2(vc, va);
+  }
+}
+
+// strided copies of one table out of / into an agent's interleaved pairs (tbl = row base, + 1 for the actor)
+__global__ void k_table_gather_pairs(const double *tbl, int32_t memory, double *out)
+{
+  for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < memory; x += gridDim.x * blockDim.x) out[x] = tbl[2 * (size_t)x];
+}
+__global__ void k_table_scatter_pairs(double *tbl, int32_t memory, const double *in)
+{
+  for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < memory; x += gridDim.x * blockDim.x) tbl[2 * (size_t)x] = in[x];
+}
+
 // logical <-> physical copies of one agent's table (grlcu_get_table / grlcu_set_table under the tile-major layout)
 __global__ void k_table_gather(const double *tbl, const uint32_t *perm, int32_t memory, double *out)
 {
