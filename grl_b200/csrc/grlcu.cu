@@ -15,6 +15,8 @@
 #include <cstring>
 #include <new>
 #include <vector>
+#include <algorithm>
+#include <numeric>
 
 using namespace grlcu;
 
@@ -47,6 +49,7 @@ struct grlcu_ctx
   int S, OBS;
   std::vector<void *> allocs;
   double *d_alpha, *d_lambda, *d_epsilon, *d_start;
+  uint32_t *d_chunk_map;      // launch order of the 32-agent chunks (per-agent lambda), see grlcu_set_hyper
   int64_t launches;
   int sm_count;
   bool geo;                   // tile-major physical table layout in use (struct Geo)
@@ -233,6 +236,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   c->S = cfg->dynamics == GRLCU_DYN_PENDULUM ? 3 : cfg->dynamics == GRLCU_DYN_CART_POLE ? 5 : 7;
   c->OBS = cfg->obs_dims;
   c->d_alpha = c->d_lambda = c->d_epsilon = c->d_start = nullptr;
+  c->d_chunk_map = nullptr;
   c->launches = 0;
   c->ev_ms = 0; c->ev_n = 0; c->traces_live = false;
   c->geo = false; c->inbox_words = c->shared_words = 0; c->d_stage = nullptr;
@@ -521,6 +525,22 @@ extern "C" int grlcu_set_hyper(grlcu_ctx *c, const double *alpha, const double *
   if (int r = upload_opt(c, &c->d_alpha, alpha)) return r;
   if (int r = upload_opt(c, &c->d_lambda, lambda)) return r;
   if (int r = upload_opt(c, &c->d_epsilon, epsilon)) return r;
+  if (lambda && c->cfg.algo != GRLCU_ALGO_AC && c->p.n % 32 == 0 && !getenv("GRLCU_NO_CHUNK_MAP"))
+  {
+    // A warp sweeps as long as its longest trace, and a cohort launch lasts as long as its slowest warp: order the 32-agent
+    // chunks by (their largest) lambda so that the cohorts of grlcu_run hold traces of similar length and can use the
+    // 255-register instantiation (one launch of everything needs the 128-register one and spills).
+    const int chunks = c->p.n / 32;
+    std::vector<double> key(chunks, 0.);
+    for (int i = 0; i < c->p.n; ++i) key[i / 32] = std::max(key[i / 32], lambda[i]);
+    std::vector<uint32_t> order(chunks);
+    std::iota(order.begin(), order.end(), 0u);
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return key[a] < key[b]; });
+    if (!c->d_chunk_map) if (int r = dalloc(c, &c->d_chunk_map, (size_t)chunks)) return r;
+    CU(cudaMemcpyAsync(c->d_chunk_map, order.data(), sizeof(uint32_t) * chunks, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));       // (order is a local)
+    c->p.chunk_map = c->d_chunk_map;
+  }
   CU(cudaStreamSynchronize(c->stream));
   c->p.alpha_a = c->d_alpha; c->p.lambda_a = c->d_lambda; c->p.epsilon_a = c->d_epsilon;
   return 0;
@@ -775,9 +795,10 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
   // ~0.5 KB per thread; two launches of half the agents at up to 255 registers are faster (profiles/r02_residency.txt:
   // 5.76e8 against 4.38e8 agent-steps/s for the same 32,768 agents).  So, unless the caller chose a cohort size, the
   // agents run in the fewest equal cohorts that fit 8 warps per SM.  Agents are independent: the order cannot matter.
-  // (per-agent lambda: trace lengths differ from warp to warp, and one launch lets the hardware backfill blocks as the
-  // short-trace warps finish: measured 3.75e8 all at once against 3.27e8 in four cohorts on the sweep workload)
-  if (cohort == n && (int)c->p.cblock < n && !c->p.lambda_a && !getenv("GRLCU_MINB7")) cohort = (int)c->p.cblock;
+  // (per-agent lambda: trace lengths differ from warp to warp; cohorts in agent-id order lose to one launch that backfills
+  // blocks as the short-trace warps finish (3.27e8 against 3.97e8 on the sweep workload), cohorts in lambda order
+  // (chunk_map, grlcu_set_hyper) win: 4.23e8 against 4.07e8, profiles/r02_sweep_lambda_sorted_cohorts.txt)
+  if (cohort == n && (int)c->p.cblock < n && (!c->p.lambda_a || c->p.chunk_map) && !getenv("GRLCU_MINB7")) cohort = (int)c->p.cblock;
   for (int begin = 0; begin < n; begin += cohort)
   {
     const int end = begin + cohort < n ? begin + cohort : n;

@@ -83,6 +83,9 @@ struct Params
   double   *total_reward, *last_return, *last_test_return, *return_sum;
   const double *alpha_a, *lambda_a, *epsilon_a;   // optional per-agent hyper-parameters
   const double *start_override;                    // optional [S][n] start states (run_host)
+  // Per-agent lambda: launch order of the 32-agent chunks, sorted by lambda (chunk_map[k] = chunk that thread-chunk k of a
+  // launch runs), so that a cohort launch holds agents with traces of similar length; NULL = identity
+  const uint32_t *chunk_map;
   // projector/tile_coding safe > 0 (tile_coding.h:116-148): per-agent collision-claim table and what goes with it
   int32_t  safe;              // 0 off, 1 claim on the predictor's projections, 2 claim on every projection
   int32_t  *claims;           // [n][memory] TileCodingProjector::indices_ (-1 = free)

@@ -296,8 +296,10 @@ k_run(Params p, int agent_begin, int agent_end, int64_t n_steps, int do_close)
 {
   constexpr int S = Dyn<DYN>::S, OBS = Dyn<DYN>::OBS;
   __shared__ uint32_t s_idx[(SAFE ? 2 : 1) * A * T][kMaxBlock];     // slots of Q(s', .) [+ their hashes: safe > 0]
-  const int a = agent_begin + blockIdx.x * blockDim.x + threadIdx.x;
-  if (a >= agent_end) return;
+  const int slot_in_launch = agent_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot_in_launch >= agent_end) return;
+  // (agents are independent: which thread runs which agent cannot matter; chunk_map orders the launches by lambda)
+  const int a = p.chunk_map ? (int)(__ldg(p.chunk_map + (slot_in_launch >> 5)) * 32u) + (slot_in_launch & 31) : slot_in_launch;
   uint32_t *sid = &s_idx[0][threadIdx.x];
   Agent<DYN, T> ag;
   ag.load(p, a);
