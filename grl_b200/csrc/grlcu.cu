@@ -49,6 +49,7 @@ struct grlcu_ctx
   int S, OBS;
   std::vector<void *> allocs;
   double *d_alpha, *d_lambda, *d_epsilon, *d_start;
+  bool warned_slow;
   uint32_t *d_chunk_map;      // launch order of the 32-agent chunks (per-agent lambda), see grlcu_set_hyper
   int64_t launches;
   int sm_count;
@@ -191,7 +192,11 @@ static int supported(const grlcu_config *cfg)
   // cfg/pendulum/sarsa_tc.yaml, cfg/cart_pole/sarsa.yaml, cfg/cart_double_pole/sarsa.yaml of the reference
   if (cfg->dynamics != GRLCU_DYN_PENDULUM && cfg->dynamics != GRLCU_DYN_CART_POLE && cfg->dynamics != GRLCU_DYN_CART_DOUBLE_POLE)
     return fail(GRLCU_ERR_UNSUPPORTED, "dynamics %d not instantiated for SARSA", cfg->dynamics);
-  if (cfg->n_actions != 3) return fail(GRLCU_ERR_UNSUPPORTED, "n_actions %d: kernels are instantiated for 3", cfg->n_actions);
+  // discretizer/uniform with one action dimension (uniform.cpp:126-151): 3 actions run every kernel (value cache, tile-major
+  // layout); 2, 4 and 5 are instantiated for the uncached kernels only
+  if (cfg->n_actions < 2 || cfg->n_actions > 5)
+    return fail(GRLCU_ERR_UNSUPPORTED, "n_actions %d: kernels are instantiated for 2..5 actions (one action dimension)", cfg->n_actions);
+  if (cfg->n_actions != 3 && cfg->safe > 0) return fail(GRLCU_ERR_UNSUPPORTED, "safe > 0 is instantiated for 3 actions");
   const int obs = cfg->dynamics == GRLCU_DYN_PENDULUM ? 2 : cfg->dynamics == GRLCU_DYN_CART_POLE ? 4 : 6;
   if (cfg->obs_dims != obs) return fail(GRLCU_ERR_ARG, "obs_dims %d does not match dynamics (%d)", cfg->obs_dims, obs);
   return 0;
@@ -236,7 +241,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   c->S = cfg->dynamics == GRLCU_DYN_PENDULUM ? 3 : cfg->dynamics == GRLCU_DYN_CART_POLE ? 5 : 7;
   c->OBS = cfg->obs_dims;
   c->d_alpha = c->d_lambda = c->d_epsilon = c->d_start = nullptr;
-  c->d_chunk_map = nullptr;
+  c->d_chunk_map = nullptr; c->warned_slow = false;
   c->launches = 0;
   c->ev_ms = 0; c->ev_n = 0; c->traces_live = false;
   c->geo = false; c->inbox_words = c->shared_words = 0; c->d_stage = nullptr;
@@ -789,7 +794,15 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
   c->traces_live = true;
   // the trace value cache applies to the replacing trace (unique owner slot per index); it stays live between
   // launches, agent by agent (values return to the tables lazily, see ensure_plain), unless GRLCU_EAGER_CLOSE is set
-  const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64;
+  const bool cached = c->p.mode == 0 && !c->p.force_slow && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap <= 64 &&
+                      (c->cfg.algo == GRLCU_ALGO_AC || c->cfg.n_actions == 3);
+  if (!cached && c->p.mode == 0 && c->p.trace_kind == GRLCU_TRACE_REPLACING && c->p.trace_cap > 64 && !c->warned_slow)
+  {
+    // (the fast update paths carry a 64-bit per-entry duplicate mask)
+    fprintf(stderr, "libgrlcu: gamma*lambda = %g needs a %d-entry trace (> 64): this context runs the sequential update path, "
+            "about 3x slower than the cached one\n", c->cfg.gamma * c->cfg.lambda, c->p.trace_cap);
+    c->warned_slow = true;
+  }
   const int do_close = getenv("GRLCU_EAGER_CLOSE") ? 1 : 0;
   // Register budget: a launch with more than 8 warps per SM gets the 128-register instantiation, which spills
   // ~0.5 KB per thread; two launches of half the agents at up to 255 registers are faster (profiles/r02_residency.txt:
@@ -826,6 +839,18 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
 #define CALL_SAFE(D) k_run<D, 16, 3, false, 7, false, true><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0)
     if (c->cfg.algo == GRLCU_ALGO_AC) DISPATCH_DYN(c, CALL_AC);
     else if (c->p.safe > 0) DISPATCH_DYN(c, CALL_SAFE);
+    else if (c->cfg.n_actions != 3)
+    {
+#define CALL_A2(D) k_run<D, 16, 2, false, 7, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0)
+#define CALL_A4(D) k_run<D, 16, 4, false, 7, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0)
+#define CALL_A5(D) k_run<D, 16, 5, false, 7, false><<<grd, c->block, 0, c->stream>>>(c->p, begin, end, n_steps, 0)
+      if (c->cfg.n_actions == 2) DISPATCH_DYN(c, CALL_A2);
+      else if (c->cfg.n_actions == 4) DISPATCH_DYN(c, CALL_A4);
+      else DISPATCH_DYN(c, CALL_A5);
+#undef CALL_A2
+#undef CALL_A4
+#undef CALL_A5
+    }
     else if (c->geo) CALL_G(0, true);              // the tile-major layout is instantiated for the pendulum (grlcu_layout.h)
     else DISPATCH_SARSA(c, CALL);
 #undef CALL_SAFE
@@ -1113,6 +1138,18 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
 #define CALL_SAFE(D) k_replay<D, 16, 3, false, true><<<grd, blk, 0, c->stream>>>(c->p, io)
   if (is_ac) DISPATCH_DYN(c, CALL_AC);
   else if (c->p.safe > 0) DISPATCH_DYN(c, CALL_SAFE);
+  else if (c->cfg.n_actions != 3)
+  {
+#define CALL_A2(D) k_replay<D, 16, 2, false><<<grd, blk, 0, c->stream>>>(c->p, io)
+#define CALL_A4(D) k_replay<D, 16, 4, false><<<grd, blk, 0, c->stream>>>(c->p, io)
+#define CALL_A5(D) k_replay<D, 16, 5, false><<<grd, blk, 0, c->stream>>>(c->p, io)
+    if (c->cfg.n_actions == 2) DISPATCH_DYN(c, CALL_A2);
+    else if (c->cfg.n_actions == 4) DISPATCH_DYN(c, CALL_A4);
+    else DISPATCH_DYN(c, CALL_A5);
+#undef CALL_A2
+#undef CALL_A4
+#undef CALL_A5
+  }
   else if (c->geo) k_replay<0, 16, 3, true><<<grd, blk, 0, c->stream>>>(c->p, io);
   else DISPATCH_SARSA(c, CALL);
 #undef CALL_AC

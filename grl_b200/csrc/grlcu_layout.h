@@ -51,7 +51,7 @@ inline Layout build_layout(const grlcu_config &cfg, const double *scaling, const
   Layout L;
   const int T = cfg.tilings, OBS = cfg.obs_dims, A = cfg.n_actions, ia = OBS;
   double lo[GRLCU_MAX_DIMS], hi[GRLCU_MAX_DIMS];
-  if (cfg.algo == GRLCU_ALGO_AC || T != 16 || A < 1 || A > 4 || (cfg.memory & 3) || !task_box(cfg, lo, hi)) return L;
+  if (cfg.algo == GRLCU_ALGO_AC || T != 16 || A != 3 || (cfg.memory & 3) || !task_box(cfg, lo, hi)) return L;
   if (wrap[ia] != 0) return L;
   uint64_t ncells = 1;
   for (int i = 0; i < OBS; ++i)

@@ -30,9 +30,10 @@ extern "C" {
 #endif
 
 /* Array capacities of grlcu_config.  What the kernels are INSTANTIATED for is narrower and checked by grlcu_create
- * (GRLCU_ERR_UNSUPPORTED otherwise): tilings = 16, one action dimension with n_actions = 3 (every tile-coded configuration
- * the reference ships for these three tasks: cfg/pendulum, cfg/cart_pole, cfg/cart_double_pole), obs_dims = 2 / 4 / 6 as
- * the dynamics dictate. */
+ * (GRLCU_ERR_UNSUPPORTED otherwise): tilings = 16; one action dimension with n_actions = 3 for every kernel (every
+ * tile-coded configuration the reference ships for these three tasks: cfg/pendulum, cfg/cart_pole, cfg/cart_double_pole),
+ * n_actions = 2, 4 or 5 on the uncached kernels (discretizer/uniform with other `steps`); obs_dims = 2 / 4 / 6 as the
+ * dynamics dictate. */
 #define GRLCU_MAX_DIMS 8
 #define GRLCU_MAX_ACTIONS 8
 #define GRLCU_MAX_STATE 7
@@ -58,7 +59,7 @@ typedef struct grlcu_config
   int32_t tilings;            /* projector/tile_coding tilings (tile_coding.cpp:35-43); instantiated: 16 */
   int32_t memory;             /* projector/tile_coding memory = table entries PER AGENT */
   int32_t obs_dims;           /* task observation_dims */
-  int32_t n_actions;          /* discretizer/uniform: number of discrete actions; instantiated: 3 (0 for GRLCU_ALGO_AC) */
+  int32_t n_actions;          /* discretizer/uniform: number of discrete actions; instantiated: 2..5 (0 for GRLCU_ALGO_AC) */
   double  resolution[GRLCU_MAX_DIMS];   /* projector resolution (obs dims then action) */
   double  wrapping[GRLCU_MAX_DIMS];     /* projector wrapping */
   double  actions[GRLCU_MAX_ACTIONS];   /* discretizer values (uniform.cpp:60-94) */

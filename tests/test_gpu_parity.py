@@ -394,3 +394,42 @@ def test_collision_claim_table_free_running_and_limits(G, orc):
         G.Batch(G.pendulum_config(memory=4096, safe=1, algo=O.ALGO_Q), 2)
     with pytest.raises(G.GrlcuError):
         G.Batch(G.pendulum_config(memory=4096, safe=3), 2)
+
+
+@pytest.mark.parametrize("which,A", [(0, 2), (0, 5), (1, 4)])
+def test_replay_other_action_counts(G, orc, which, A):
+    """discretizer/uniform with `steps` other than 3 (uniform.cpp:60-94: min + k (max - min) / (steps - 1)): 2, 4 and 5
+    actions run the uncached kernels; replay bit-exact, and the fused kernel per agent against the free-running oracle."""
+    name, gcfg, ocfg, mem = _cfgs(G)[which]
+    amax = (3.0, 15.0)[which]
+    acts = [-amax + k * (2 * amax) / (A - 1) for k in range(A)] + [0.0] * (8 - A)
+    def mk(f):
+        def g(**kw):
+            c = f(**kw)
+            c.n_actions = A
+            for i, v in enumerate(acts):
+                c.actions[i] = v
+            return c
+        return g
+    _replay(G, mk(gcfg), mk(ocfg), n=32, steps=260, mem=16384, randomization=1.0, test_interval=3, epsilon=0.2)
+    cfg = mk(gcfg)(memory=16384, randomization=1.0, test_interval=-1)
+    oc = mk(ocfg)(memory=16384, randomization=1.0, test_interval=-1)
+    orc.orc_run_total.restype = None
+    orc.orc_run_total.argtypes = [C.c_void_p, C.c_uint64]
+    b = G.Batch(cfg, 64, first_agent_id=9)
+    try:
+        b.run(150)
+        res = b.results()
+        for i in range(64):
+            a = orc.orc_create(C.byref(oc), 9 + i)
+            orc.orc_run_total(a, 150)
+            s, e, w, lr = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_double()
+            orc.orc_stats(a, C.byref(s), C.byref(e), C.byref(w), C.byref(lr), None)
+            assert (int(res["steps"][i]), int(res["episodes"][i]), int(res["swept"][i])) == (s.value, e.value, w.value), i
+            assert np.allclose(b.get_table(i), np.ctypeslib.as_array(orc.orc_table(a), shape=(16384,)), rtol=RTOL, atol=0), i
+            orc.orc_destroy(a)
+    finally:
+        b.close()
+    with pytest.raises(G.GrlcuError):
+        c = gcfg(memory=1024); c.n_actions = 7
+        G.Batch(c, 2)
