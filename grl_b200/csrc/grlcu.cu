@@ -217,6 +217,48 @@ static int trace_capacity_for(double e, int kind)
 static int launch_reset(grlcu_ctx *c, int what);
 static int ensure_plain(grlcu_ctx *c);
 
+// ---- pilot run for the visit-ordered table layout (grlcu_layout.h: build_layout_from_visits) --------------------------
+// Which groups of tiles the agents of this configuration actually visit is found by running a few of them: a small
+// context in the raw layout whose projections are logged (Geo::pilot_keys).  All agents of a context are statistically
+// alike (same task, same hyper-parameters), so a few hundred predict the rest; a group the pilot never saw merely is not
+// co-located.  The pilot's agents are thrown away; the real agents start from scratch.
+static thread_local int g_in_pilot = 0;
+
+static int run_pilot(const grlcu_config *cfg, int64_t first_agent_id, int device, void *stream, std::vector<uint64_t> *keys)
+{
+  const size_t budget = (size_t)2 << 30;                          // device memory the pilot's tables may take
+  int agents = (int)std::min<size_t>(256, budget / ((size_t)cfg->memory * sizeof(double)));
+  if (agents < 32) return 0;
+  const int steps = 600;
+  const uint32_t cap = (uint32_t)agents * (steps + 16) * (uint32_t)cfg->tilings;
+  grlcu_ctx *pc = nullptr;
+  g_in_pilot = 1;
+  int r = grlcu_create(cfg, agents, first_agent_id, device, stream, &pc);
+  g_in_pilot = 0;
+  if (r) return r;
+  uint64_t *d_keys = nullptr;
+  uint32_t *d_count = nullptr;
+  r = dalloc(pc, &d_keys, (size_t)cap);
+  if (!r) r = dalloc(pc, &d_count, 1);
+  if (!r && cudaMemsetAsync(d_count, 0, sizeof(uint32_t), pc->stream) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
+  if (!r)
+  {
+    pc->p.geo.pilot_keys = d_keys; pc->p.geo.pilot_count = d_count; pc->p.geo.pilot_cap = cap;
+    r = grlcu_run(pc, steps, 0);
+  }
+  uint32_t count = 0;
+  if (!r && cudaMemcpyAsync(&count, d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, pc->stream) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "pilot: copy failed");
+  if (!r && cudaStreamSynchronize(pc->stream) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "pilot run failed: %s", cudaGetErrorString(cudaGetLastError()));
+  if (!r)
+  {
+    keys->resize(std::min(count, cap));
+    if (!keys->empty() && cudaMemcpy(keys->data(), d_keys, keys->size() * sizeof(uint64_t), cudaMemcpyDeviceToHost) != cudaSuccess)
+      r = fail(GRLCU_ERR_CUDA, "pilot: copy failed");
+  }
+  grlcu_destroy(pc);
+  return r;
+}
+
 extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t first_agent_id,
                             int32_t device, void *stream, grlcu_ctx **out)
 {
@@ -326,6 +368,23 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     p.geo.enabled = 1;
     for (int i = 0; i < cfg->obs_dims; ++i) { p.geo.kn[i] = lay.kn[i]; p.geo.koff[i] = lay.koff[i]; p.geo.wrapped[i] = lay.wrapped[i]; }
   }
+  else if (!g_in_pilot && !(getenv("GRLCU_LAYOUT") && atoi(getenv("GRLCU_LAYOUT")) == 0) && cfg->safe == 0 && !is_ac &&
+           cfg->n_actions == 3 && cfg->tilings == 16 && (cfg->memory & 3) == 0 && cfg->memory >= 4096 && cfg->memory <= (1 << 20) &&
+           n_agents >= 64)
+  {
+    // the task's tiles do not fit the table (or it has no box): visit-ordered layout from a pilot run.  A failing pilot
+    // only costs the layout.
+    std::vector<uint64_t> keys;
+    if (run_pilot(cfg, first_agent_id, device, stream, &keys) == 0)
+      lay = grlcu_host::build_layout_from_visits(*cfg, keys, p.kact, p.kj);
+    CU(cudaSetDevice(device));
+    if (lay.enabled)
+    {
+      c->geo = true; c->inbox_words = lay.inbox_words; c->shared_words = lay.shared_words;
+      p.tstride = lay.tstride;
+      p.geo.enabled = 2;
+    }
+  }
 
   const size_t n = (size_t)n_agents, T = (size_t)cfg->tilings;
   if (n * T * (size_t)p.trace_cap >= (1ull << 31))
@@ -347,8 +406,8 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     };
     if (!r) r = up(&p.geo.perm, lay.perm);
     if (!r) r = up(&p.geo.iperm, lay.iperm);
-    if (!r) r = up(&p.geo.slotmap, lay.slotmap);
-    if (!r) r = up(&p.geo.gflags, lay.gflags);
+    if (!r && p.geo.enabled == 1) r = up(&p.geo.slotmap, lay.slotmap);
+    if (!r && p.geo.enabled == 1) r = up(&p.geo.gflags, lay.gflags);
     if (!r) r = dalloc(c, &p.geo.mismatch, 1);
     if (!r && cudaMemset(p.geo.mismatch, 0, sizeof(int32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
     if (!r) r = dalloc(c, &c->d_stage, (size_t)cfg->memory);
@@ -851,7 +910,9 @@ extern "C" int grlcu_run(grlcu_ctx *c, int64_t n_steps, int32_t cohort)
 #undef CALL_A4
 #undef CALL_A5
     }
-    else if (c->geo) CALL_G(0, true);              // the tile-major layout is instantiated for the pendulum (grlcu_layout.h)
+#define CALL_GEO(D) CALL_G(D, true)
+    else if (c->geo) DISPATCH_DYN(c, CALL_GEO);    // tile-major (pendulum: from tile coordinates) or visit-ordered (perm only)
+#undef CALL_GEO
     else DISPATCH_SARSA(c, CALL);
 #undef CALL_SAFE
 #undef CALL_AC
@@ -897,7 +958,7 @@ extern "C" int grlcu_run_kernel_time(grlcu_ctx *c, double *ms, int64_t *launches
 extern "C" int grlcu_layout_info(grlcu_ctx *c, int32_t *tile_major, uint32_t *table_stride, uint32_t *inbox_words, uint32_t *shared_words)
 {
   if (!c) return fail(GRLCU_ERR_ARG, "null context");
-  if (tile_major) *tile_major = c->geo ? 1 : 0;
+  if (tile_major) *tile_major = c->geo ? c->p.geo.enabled : 0;     // 1: from tile coordinates, 2: visit-ordered (perm only)
   if (table_stride) *table_stride = c->p.tstride;
   if (inbox_words) *inbox_words = c->inbox_words;
   if (shared_words) *shared_words = c->shared_words;
@@ -1150,7 +1211,9 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
 #undef CALL_A4
 #undef CALL_A5
   }
-  else if (c->geo) k_replay<0, 16, 3, true><<<grd, blk, 0, c->stream>>>(c->p, io);
+#define CALL_GEO(D) k_replay<D, 16, 3, true><<<grd, blk, 0, c->stream>>>(c->p, io)
+  else if (c->geo) DISPATCH_DYN(c, CALL_GEO);
+#undef CALL_GEO
   else DISPATCH_SARSA(c, CALL);
 #undef CALL_AC
 #undef CALL

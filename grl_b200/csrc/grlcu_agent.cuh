@@ -31,7 +31,7 @@ namespace grlcu {
 // its own group's sector; the MurmurHash2 path + perm[] serve observations outside the box.
 struct Geo
 {
-  int32_t  enabled;
+  int32_t  enabled;             // 1: slots from tile coordinates inside the box (perm[] outside); 2: perm[] only (visit-ordered layout)
   int32_t  kn[kMaxDims];        // coarse cells per observation dimension
   int32_t  koff[kMaxDims];      // k + koff in [0, kn) inside the box (unwrapped dimensions)
   int32_t  wrapped[kMaxDims];   // dimension wraps (wrap = kn * T): k mod kn
@@ -40,6 +40,11 @@ struct Geo
   const uint32_t *slotmap;      // [ncells * T * 4] physical slot of every in-box tile word
   const uint32_t *gflags;       // 4 bits per (cell, tiling) group: bit a = action a's word is in the group's own sector
   int32_t  *mismatch;           // replay kernels: geometric slot != perm[hash index] seen (must stay 0)
+  // pilot run of grlcu_create (visit-ordered layout): every projected group is logged as (hash state after the
+  // observation coordinates) << 8 | tiling
+  uint64_t *pilot_keys;
+  uint32_t *pilot_count;
+  uint32_t  pilot_cap;
 };
 
 struct Params
@@ -343,7 +348,7 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
     {
       bool inbox = false;
       uint32_t group = 0;
-      if (GEO)
+      if (GEO && p.geo.enabled == 1)
       {
         // coarse tile coordinate of tiling j in dimension i: c_i = b + T*k with b = j(1+2i) mod T (tile_coding.cpp:122-131)
         inbox = true;
@@ -379,6 +384,11 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
           int32_t c = qz[i] - safe_mod(qz[i] - j * (1 + 2 * i), T);
           if (p.proj.wrap[i] != 0) c = safe_mod(c, p.proj.wrap[i]);
           h = (h * m) ^ murmur_mix((uint32_t)c);
+        }
+        if (!GEO && p.geo.pilot_keys)
+        {
+          const uint32_t at = atomicAdd(p.geo.pilot_count, 1u);
+          if (at < p.geo.pilot_cap) p.geo.pilot_keys[at] = ((uint64_t)h << 8) | (uint32_t)j;
         }
 #pragma unroll
         for (int aa = 0; aa < A; ++aa)

@@ -6,6 +6,8 @@
 #include <stdint.h>
 #include <math.h>
 #include <vector>
+#include <algorithm>
+#include <utility>
 #include "../../include/grlcu.h"
 
 namespace grlcu_host {
@@ -126,6 +128,71 @@ inline Layout build_layout(const grlcu_config &cfg, const double *scaling, const
       while (L.iperm[next] != UNSET) ++next;
       L.perm[x] = next; L.iperm[next] = x;
     }
+  L.enabled = true;
+  return L;
+}
+
+// Visit-ordered layout for tasks whose tiles do not fit the table (the hash really compresses: cart-pole, cart-double-pole).
+// `keys`: the groups a pilot run projected ((hash state after the observation coordinates) << 8 | tiling), with
+// repetitions.  Groups are ranked by visit count; the A action words of the most visited groups get consecutive slots
+// padded to a sector, exactly as in build_layout, until a quarter of the table's entries have become group bases; a word
+// whose index is already placed shares that slot; everything else fills the holes.  The kernel finds a slot through
+// perm[] alone (Geo.enabled = 2), so an unranked group costs nothing but its co-location.
+// kact / kj: the pre-mixed action and tiling words of Params (grlcu_create).
+inline Layout build_layout_from_visits(const grlcu_config &cfg, std::vector<uint64_t> &keys,
+                                       const uint32_t (*kact)[16], const uint32_t *kj)
+{
+  Layout L;
+  const int A = cfg.n_actions;
+  if (keys.empty() || A != 3 || cfg.tilings != 16 || (cfg.memory & 3)) return L;
+  std::sort(keys.begin(), keys.end());
+  std::vector<std::pair<uint32_t, uint64_t>> ranked;          // (visits, key)
+  for (size_t i = 0; i < keys.size();)
+  {
+    size_t e = i;
+    while (e < keys.size() && keys[e] == keys[i]) ++e;
+    ranked.push_back(std::make_pair((uint32_t)(e - i), keys[i]));
+    i = e;
+  }
+  std::sort(ranked.begin(), ranked.end(), [](const std::pair<uint32_t, uint64_t> &a, const std::pair<uint32_t, uint64_t> &b)
+            { return a.first != b.first ? a.first > b.first : a.second < b.second; });
+  const uint32_t mem = (uint32_t)cfg.memory, max_groups = mem / 4;
+  const uint32_t UNSET = 0xFFFFFFFFu, m = 0x5bd1e995u;
+  L.perm.assign(mem, UNSET);
+  L.iperm.assign(mem, UNSET);
+  uint32_t groups = 0;
+  for (size_t r = 0; r < ranked.size() && groups < max_groups; ++r)
+  {
+    const uint32_t h = (uint32_t)(ranked[r].second >> 8);
+    const int j = (int)(ranked[r].second & 255u);
+    uint32_t x[3];
+    bool any_free = false;
+    for (int aa = 0; aa < A; ++aa)
+    {
+      uint32_t g = (h * m) ^ kact[aa][j];
+      g = (g * m) ^ kj[j];
+      g ^= g >> 13; g *= m; g ^= g >> 15;
+      x[aa] = g % mem;
+      any_free |= L.perm[x[aa]] == UNSET;
+    }
+    if (!any_free) { L.inbox_words += A; L.shared_words += A; continue; }
+    const uint32_t base = groups++ * 4;
+    for (int aa = 0; aa < A; ++aa)
+    {
+      ++L.inbox_words;
+      if (L.perm[x[aa]] == UNSET) { L.perm[x[aa]] = base + aa; L.iperm[base + aa] = x[aa]; }
+      else ++L.shared_words;
+    }
+  }
+  uint32_t next = 0;
+  for (uint32_t xx = 0; xx < mem; ++xx)
+    if (L.perm[xx] == UNSET)
+    {
+      while (L.iperm[next] != UNSET) ++next;
+      L.perm[xx] = next; L.iperm[next] = xx;
+    }
+  L.tstride = mem;
+  L.ncells = groups;
   L.enabled = true;
   return L;
 }
