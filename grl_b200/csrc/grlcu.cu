@@ -230,7 +230,7 @@ static int run_pilot(const grlcu_config *cfg, int64_t first_agent_id, int device
   int agents = (int)std::min<size_t>(256, budget / ((size_t)cfg->memory * sizeof(double)));
   if (agents < 32) return 0;
   const int steps = 600;
-  const uint32_t cap = (uint32_t)agents * (steps + 16) * (uint32_t)cfg->tilings;
+  const uint32_t cap = (uint32_t)(steps + 16) * (uint32_t)cfg->tilings;      // keys per agent
   grlcu_ctx *pc = nullptr;
   g_in_pilot = 1;
   int r = grlcu_create(cfg, agents, first_agent_id, device, stream, &pc);
@@ -238,22 +238,29 @@ static int run_pilot(const grlcu_config *cfg, int64_t first_agent_id, int device
   if (r) return r;
   uint64_t *d_keys = nullptr;
   uint32_t *d_count = nullptr;
-  r = dalloc(pc, &d_keys, (size_t)cap);
-  if (!r) r = dalloc(pc, &d_count, 1);
-  if (!r && cudaMemsetAsync(d_count, 0, sizeof(uint32_t), pc->stream) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
+  r = dalloc(pc, &d_keys, (size_t)cap * agents);
+  if (!r) r = dalloc(pc, &d_count, (size_t)agents);
+  if (!r && cudaMemsetAsync(d_count, 0, sizeof(uint32_t) * agents, pc->stream) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
   if (!r)
   {
     pc->p.geo.pilot_keys = d_keys; pc->p.geo.pilot_count = d_count; pc->p.geo.pilot_cap = cap;
     r = grlcu_run(pc, steps, 0);
   }
-  uint32_t count = 0;
-  if (!r && cudaMemcpyAsync(&count, d_count, sizeof(uint32_t), cudaMemcpyDeviceToHost, pc->stream) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "pilot: copy failed");
+  std::vector<uint32_t> counts(agents, 0);
+  std::vector<uint64_t> all;
   if (!r && cudaStreamSynchronize(pc->stream) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "pilot run failed: %s", cudaGetErrorString(cudaGetLastError()));
+  if (!r && cudaMemcpy(counts.data(), d_count, sizeof(uint32_t) * agents, cudaMemcpyDeviceToHost) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "pilot: copy failed");
   if (!r)
   {
-    keys->resize(std::min(count, cap));
-    if (!keys->empty() && cudaMemcpy(keys->data(), d_keys, keys->size() * sizeof(uint64_t), cudaMemcpyDeviceToHost) != cudaSuccess)
-      r = fail(GRLCU_ERR_CUDA, "pilot: copy failed");
+    all.resize((size_t)cap * agents);
+    if (cudaMemcpy(all.data(), d_keys, all.size() * sizeof(uint64_t), cudaMemcpyDeviceToHost) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "pilot: copy failed");
+  }
+  if (!r)
+  {
+    // agent after agent, each in its own projection order
+    keys->clear();
+    for (int a = 0; a < agents; ++a)
+      keys->insert(keys->end(), all.begin() + (size_t)a * cap, all.begin() + (size_t)a * cap + std::min(counts[a], cap));
   }
   grlcu_destroy(pc);
   return r;

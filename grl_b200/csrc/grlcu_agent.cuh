@@ -42,8 +42,8 @@ struct Geo
   int32_t  *mismatch;           // replay kernels: geometric slot != perm[hash index] seen (must stay 0)
   // pilot run of grlcu_create (visit-ordered layout): every projected group is logged as (hash state after the
   // observation coordinates) << 8 | tiling
-  uint64_t *pilot_keys;
-  uint32_t *pilot_count;
+  uint64_t *pilot_keys;         // [n][pilot_cap]
+  uint32_t *pilot_count;        // [n]
   uint32_t  pilot_cap;
 };
 
@@ -387,8 +387,9 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
         }
         if (!GEO && p.geo.pilot_keys)
         {
-          const uint32_t at = atomicAdd(p.geo.pilot_count, 1u);
-          if (at < p.geo.pilot_cap) p.geo.pilot_keys[at] = ((uint64_t)h << 8) | (uint32_t)j;
+          // one stream per agent, in the order the agent projects them (pilot_cap keys per agent)
+          const uint32_t at = p.geo.pilot_count[a]++;
+          if (at < p.geo.pilot_cap) p.geo.pilot_keys[(size_t)a * p.geo.pilot_cap + at] = ((uint64_t)h << 8) | (uint32_t)j;
         }
 #pragma unroll
         for (int aa = 0; aa < A; ++aa)

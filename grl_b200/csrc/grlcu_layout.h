@@ -139,32 +139,45 @@ inline Layout build_layout(const grlcu_config &cfg, const double *scaling, const
 // whose index is already placed shares that slot; everything else fills the holes.  The kernel finds a slot through
 // perm[] alone (Geo.enabled = 2), so an unranked group costs nothing but its co-location.
 // kact / kj: the pre-mixed action and tiling words of Params (grlcu_create).
-inline Layout build_layout_from_visits(const grlcu_config &cfg, std::vector<uint64_t> &keys,
+inline Layout build_layout_from_visits(const grlcu_config &cfg, const std::vector<uint64_t> &keys,
                                        const uint32_t (*kact)[16], const uint32_t *kj)
 {
   Layout L;
   const int A = cfg.n_actions;
   if (keys.empty() || A != 3 || cfg.tilings != 16 || (cfg.memory & 3)) return L;
-  std::sort(keys.begin(), keys.end());
+  // visits per group, and the rank below which a group gets a sector of its own
+  std::vector<uint64_t> sorted(keys);
+  std::sort(sorted.begin(), sorted.end());
   std::vector<std::pair<uint32_t, uint64_t>> ranked;          // (visits, key)
-  for (size_t i = 0; i < keys.size();)
+  for (size_t i = 0; i < sorted.size();)
   {
     size_t e = i;
-    while (e < keys.size() && keys[e] == keys[i]) ++e;
-    ranked.push_back(std::make_pair((uint32_t)(e - i), keys[i]));
+    while (e < sorted.size() && sorted[e] == sorted[i]) ++e;
+    ranked.push_back(std::make_pair((uint32_t)(e - i), sorted[i]));
     i = e;
   }
   std::sort(ranked.begin(), ranked.end(), [](const std::pair<uint32_t, uint64_t> &a, const std::pair<uint32_t, uint64_t> &b)
             { return a.first != b.first ? a.first > b.first : a.second < b.second; });
   const uint32_t mem = (uint32_t)cfg.memory, max_groups = mem / 4;
+  if (ranked.size() > max_groups) ranked.resize(max_groups);
+  std::vector<uint64_t> chosen(ranked.size());
+  for (size_t i = 0; i < ranked.size(); ++i) chosen[i] = ranked[i].second;
+  std::sort(chosen.begin(), chosen.end());
+  std::vector<char> placed(chosen.size(), 0);
   const uint32_t UNSET = 0xFFFFFFFFu, m = 0x5bd1e995u;
   L.perm.assign(mem, UNSET);
   L.iperm.assign(mem, UNSET);
   uint32_t groups = 0;
-  for (size_t r = 0; r < ranked.size() && groups < max_groups; ++r)
+  // Sectors are handed out in FIRST-VISIT order along the pilot agents' own trajectories (`keys` is agent after agent, each
+  // in projection order): the 16 groups of one observation are discovered together and a trajectory moves continuously,
+  // so groups that are read together end up in neighbouring sectors (64-byte fetches and L2 lines get shared).
+  for (size_t r = 0; r < keys.size(); ++r)
   {
-    const uint32_t h = (uint32_t)(ranked[r].second >> 8);
-    const int j = (int)(ranked[r].second & 255u);
+    const size_t at = std::lower_bound(chosen.begin(), chosen.end(), keys[r]) - chosen.begin();
+    if (at >= chosen.size() || chosen[at] != keys[r] || placed[at]) continue;
+    placed[at] = 1;
+    const uint32_t h = (uint32_t)(keys[r] >> 8);
+    const int j = (int)(keys[r] & 255u);
     uint32_t x[3];
     bool any_free = false;
     for (int aa = 0; aa < A; ++aa)
