@@ -392,8 +392,8 @@ def ours(args):
                                          if traffic and kern_ms > 0 and traffic_current else None,
                          "peak_source": peak_src, "random_access": random_access,
                          "bytes_per_agent_step": B, "V_mean": V,
-                         "table_layout": dict(layout, note="tile-major: the 3 action words of one tile share a 32-byte sector, "
-                                              "slot computed from tile coordinates (DESIGN.md section 4); else the reference's raw hash order"),
+                         "table_layout": dict(layout, note="tile-major / visit-ordered: the 3 action words of one tile share a 32-byte sector "
+                                              "(DESIGN.md section 4); inbox_words = tile words ranked, shared_words = those sharing an earlier slot"),
                          "kernel": "grlcu::k_run_ac" if args.workload in AC_WORKLOADS else "grlcu::k_run",
                          "kernel_ms_per_launch": kern_ms / max(kern_launches, 1),
                          "kernel_ms_per_pass": kern_ms / max(args.steps, 1),

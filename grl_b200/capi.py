@@ -371,7 +371,8 @@ class Batch:
         """dict(tile_major, table_stride, inbox_words, shared_words): how the context stores its tables."""
         tm, ts, iw, sw = C.c_int32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
         self._chk(self.lib.grlcu_layout_info(self.h, C.byref(tm), C.byref(ts), C.byref(iw), C.byref(sw)))
-        return dict(tile_major=bool(tm.value), table_stride=ts.value, inbox_words=iw.value, shared_words=sw.value)
+        kind = {0: "raw hash order", 1: "tile-major (slots from tile coordinates)", 2: "visit-ordered (pilot run, perm lookup)"}[tm.value]
+        return dict(tile_major=bool(tm.value), kind=kind, table_stride=ts.value, inbox_words=iw.value, shared_words=sw.value)
 
     def pressure(self):
         """safe > 0: per-agent maximum probe length in the claim table (TileCodingProjector::pressure_)."""

@@ -366,8 +366,14 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   // hash order, kept for A/B runs and as the other side of tests/test_gpu_cached.py)
   p.tstride = (uint32_t)cfg->memory;
   grlcu_host::Layout lay;
-  if (!(getenv("GRLCU_LAYOUT") && atoi(getenv("GRLCU_LAYOUT")) == 0) && cfg->safe == 0)
+  const int layout_env = getenv("GRLCU_LAYOUT") ? atoi(getenv("GRLCU_LAYOUT")) : 1;     // 0 raw, 2 visit-ordered even where tile-major applies
+  if (layout_env == 1 && cfg->safe == 0 && !g_in_pilot)      // (the pilot runs in the raw layout)
     lay = grlcu_host::build_layout(*cfg, p.proj.scaling, p.proj.wrap);
+  const bool pilot_ok = !g_in_pilot && layout_env != 0 && cfg->safe == 0 && !is_ac && cfg->n_actions == 3 && cfg->tilings == 16 &&
+                        (cfg->memory & 3) == 0 && cfg->memory >= 4096 && cfg->memory <= (1 << 20) && n_agents >= 64;
+  // a box that fills more than half the table leaves many tiles without a home (sweep: 30 % of the words share a slot):
+  // ranking by actual visits does better there (4.47e8 against 4.22e8), profiles/r02_visit_ordered_vs_tile_major.txt
+  if (lay.enabled && pilot_ok && (size_t)lay.inbox_words * 2 > (size_t)cfg->memory) lay = grlcu_host::Layout();
   if (lay.enabled)
   {
     c->geo = true; c->inbox_words = lay.inbox_words; c->shared_words = lay.shared_words;
@@ -375,9 +381,7 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     p.geo.enabled = 1;
     for (int i = 0; i < cfg->obs_dims; ++i) { p.geo.kn[i] = lay.kn[i]; p.geo.koff[i] = lay.koff[i]; p.geo.wrapped[i] = lay.wrapped[i]; }
   }
-  else if (!g_in_pilot && !(getenv("GRLCU_LAYOUT") && atoi(getenv("GRLCU_LAYOUT")) == 0) && cfg->safe == 0 && !is_ac &&
-           cfg->n_actions == 3 && cfg->tilings == 16 && (cfg->memory & 3) == 0 && cfg->memory >= 4096 && cfg->memory <= (1 << 20) &&
-           n_agents >= 64)
+  else if (pilot_ok)
   {
     // the task's tiles do not fit the table (or it has no box): visit-ordered layout from a pilot run.  A failing pilot
     // only costs the layout.
@@ -390,6 +394,14 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
       c->geo = true; c->inbox_words = lay.inbox_words; c->shared_words = lay.shared_words;
       p.tstride = lay.tstride;
       p.geo.enabled = 2;
+    }
+    else if (layout_env == 1 && (lay = grlcu_host::build_layout(*cfg, p.proj.scaling, p.proj.wrap)).enabled)
+    {
+      // (the pilot failed: tile-major after all, where it applies)
+      c->geo = true; c->inbox_words = lay.inbox_words; c->shared_words = lay.shared_words;
+      p.tstride = lay.tstride;
+      p.geo.enabled = 1;
+      for (int i = 0; i < cfg->obs_dims; ++i) { p.geo.kn[i] = lay.kn[i]; p.geo.koff[i] = lay.koff[i]; p.geo.wrapped[i] = lay.wrapped[i]; }
     }
   }
 

@@ -267,7 +267,8 @@ int grlcu_group_run(grlcu_group *group, int64_t n_steps);
  * collective_ms (may be NULL): device time of the all-gather alone, CUDA events on the first context's stream. */
 int grlcu_group_results(grlcu_group *group, grlcu_results *results, double *collective_ms);
 
-/* How the context stores its tables (measurement aid, replaces nothing in the reference): tile_major = 1 when the
+/* How the context stores its tables (measurement aid, replaces nothing in the reference): tile_major = 1 (slots from tile
+ * coordinates) or 2 (visit-ordered from a pilot run) when the
  * tile-major physical layout is in use (the action words of one tile share a 32-byte sector and the
  * kernel computes the slot from the tile coordinates; logical indices, grlcu_get_table / grlcu_set_table and checkpoints
  * are unaffected), table_stride = doubles per agent, inbox_words = tile words of the task's observation box,
