@@ -229,7 +229,7 @@ static int run_pilot(const grlcu_config *cfg, int64_t first_agent_id, int device
   const size_t budget = (size_t)2 << 30;                          // device memory the pilot's tables may take
   int agents = (int)std::min<size_t>(256, budget / ((size_t)cfg->memory * sizeof(double)));
   if (agents < 32) return 0;
-  const int steps = 600;
+  const int steps = getenv("GRLCU_PILOT_STEPS") ? std::max(100, atoi(getenv("GRLCU_PILOT_STEPS"))) : 600;
   const uint32_t cap = (uint32_t)(steps + 16) * (uint32_t)cfg->tilings;      // keys per agent
   grlcu_ctx *pc = nullptr;
   g_in_pilot = 1;
