@@ -32,6 +32,7 @@ void OnlineLearningExperiment::request(ConfigurationRequest *config)
   config->push_back(CRP("save_every", "Save policy to 'output' at the end of event", save_every_));
   // new on the batched path
   config->push_back(CRP("agents", "Independent agents learning side by side on the GPU (per run)", agents_, CRP::Configuration, 1));
+  config->push_back(CRP("checkpoint_agents", "Agents whose tables load_file reads and save_every writes (0: all; agent k's file is '<name>-agent<k>.dat', agent 0's has the reference's own name)", checkpoint_agents_, CRP::Configuration, 0));
   config->push_back(CRP("steps_per_launch", "Agent-steps per agent between two reports", steps_per_launch_, CRP::Configuration, 1));
   // Several GPUs of one box (what MultiExperiment's instances on threads are to the reference, experiments/multi.cpp:44-75):
   // the agents are sharded over `devices` in contiguous ranges of global agent ids, one context per device, and the
@@ -60,6 +61,8 @@ void OnlineLearningExperiment::configure(Configuration &config)
   output_ = config["output"].str(); load_file_ = config["load_file"].str(); save_every_ = config["save_every"].str();
   agents_ = config["agents"]; steps_per_launch_ = config["steps_per_launch"]; device_ = config["device"];
   devices_ = config["devices"].v();
+  checkpoint_agents_ = config["checkpoint_agents"];
+  if (checkpoint_agents_ < 0) throw bad_param("experiment/online_learning:checkpoint_agents");
   for (double d : devices_) if (d < 0 || d != floor(d)) throw bad_param("experiment/online_learning:devices");
   if (!devices_.empty() && agents_ % (int)devices_.size()) throw bad_param("experiment/online_learning:{agents,devices}");
   sweep_alpha_ = config["sweep_alpha"].v(); sweep_lambda_ = config["sweep_lambda"].v(); sweep_epsilon_ = config["sweep_epsilon"].v();
@@ -276,7 +279,7 @@ std::vector<double> OnlineLearningExperiment::run()
       for (size_t at = load_file.find("$run"); at != std::string::npos; at = load_file.find("$run", at))
         load_file.replace(at, 4, std::to_string(rr));
       loadconfig.set("file", load_file);
-      loadconfig.set("agents", agents_);
+      loadconfig.set("agents", checkpoint_agents_ ? std::min(agents_, checkpoint_agents_) : agents_);
       for (Representation *r : checkpoint_reps_) r->reconfigure(loadconfig);
     }
     auto start = std::chrono::steady_clock::now();
@@ -334,7 +337,7 @@ std::vector<double> OnlineLearningExperiment::run()
         Configuration saveconfig;
         saveconfig.set("action", "save");
         saveconfig.set("file", soss.str());
-        saveconfig.set("agents", agents_);
+        saveconfig.set("agents", checkpoint_agents_ ? std::min(agents_, checkpoint_agents_) : agents_);
         for (Representation *r : checkpoint_reps_) r->reconfigure(saveconfig);
       }
       ++report;
@@ -347,7 +350,7 @@ std::vector<double> OnlineLearningExperiment::run()
       Configuration saveconfig;
       saveconfig.set("action", "save");
       saveconfig.set("file", oss.str());
-      saveconfig.set("agents", agents_);
+      saveconfig.set("agents", checkpoint_agents_ ? std::min(agents_, checkpoint_agents_) : agents_);
       for (Representation *r : checkpoint_reps_) r->reconfigure(saveconfig);
     }
     if (ofs.is_open())

@@ -343,7 +343,7 @@ class OnlineLearningExperiment : public Experiment
   private:
     void assemble();
     int runs_ = 1, run_offset_ = 0, trials_ = 0, steps_ = 0, rate_ = 0, test_interval_ = -1, test_trials_ = 1;
-    int agents_ = 1, steps_per_launch_ = 100, device_ = -1;
+    int agents_ = 1, steps_per_launch_ = 100, device_ = -1, checkpoint_agents_ = 0;
     Vector devices_;                                       // CUDA devices the agents are sharded over (empty: see configure)
     std::string output_, load_file_, save_every_ = "never";
     Environment *environment_ = nullptr; Agent *agent_ = nullptr, *test_agent_ = nullptr;
