@@ -155,7 +155,8 @@ template <> struct Dyn<1>
     // cart_pole.cpp:66: theta = state[end_stop_], dtheta = state[3-2*end_stop_]; with end_stop_ = 1 both are state[1]
     // (the reference uses the pole angle where the angular velocity belongs; reproduced as is)
     double theta = x[1], dtheta = x[3 - 2 * 1];
-    double costheta = cos(theta), sintheta = sin(theta);
+    double costheta, sintheta;
+    sincos(theta, &sintheta, &costheta);        // one range reduction for both (the dynamics' bar is 1e-9 against glibc)
     double temp = (u + pole_mass_length * dtheta * dtheta * sintheta) / total_mass;
     double thetaacc = (g * sintheta - costheta * temp) /
                       (length * ((4. / 3.) - mass_pole * costheta * costheta / total_mass));
@@ -193,8 +194,8 @@ template <> struct Dyn<2>
                  h4 = m1 * l1 * l1 + m2 * L1 * L1 + J1, h5 = m2 * l2 * L1, h6 = m2 * l2 * l2 + J2,
                  h7 = m1 * l1 * g_ + m2 * L1 * g_, h8 = m2 * l2 * g_;
     double qd[3] = { x[3], x[4], x[5] };
-    double c1 = cos(x[1]), c2 = cos(x[2]), s1 = sin(x[1]), s2 = sin(x[2]),
-           c12 = cos(x[1] - x[2]), s12 = sin(x[1] - x[2]);
+    double c1, c2, s1, s2, c12, s12;
+    sincos(x[1], &s1, &c1); sincos(x[2], &s2, &c2); sincos(x[1] - x[2], &s12, &c12);
     double M[3][3] = { { h1, h2 * c1, h3 * c2 }, { h2 * c1, h4, h5 * c12 }, { h3 * c2, h5 * c12, h6 } };
     double C[3][3] = { { 0, -h2 * qd[1] * s1, -h3 * qd[2] * s2 }, { 0, 0, h5 * qd[2] * s12 },
                        { 0, -h5 * qd[1] * s12, 0 } };
