@@ -433,3 +433,18 @@ def test_replay_other_action_counts(G, orc, which, A):
     with pytest.raises(G.GrlcuError):
         c = gcfg(memory=1024); c.n_actions = 7
         G.Batch(c, 2)
+
+
+def test_replay_visit_ordered_layout(G, orc):
+    """Contexts of 64 agents or more whose tiles do not fit the table get the visit-ordered physical layout (a pilot run
+    inside grlcu_create): replay parity -- logical indices, traces, Q-values, tables -- must not notice."""
+    b = G.Batch(G.cart_pole_config(memory=65536, randomization=1.0), 64)
+    try:
+        info = b.layout_info()
+        assert info["kind"].startswith("visit-ordered") and info["inbox_words"] > 0, info
+    finally:
+        b.close()
+    _replay(G, G.cart_pole_config, O.cart_pole_config, n=64, steps=220, mem=65536, randomization=1.0, test_interval=3, epsilon=0.3)
+    _replay(G, G.cart_double_pole_config, O.cart_double_pole_config, n=64, steps=120, mem=131072, test_interval=-1, epsilon=0.2)
+    # the pendulum with a table that its box fills more than half: visit-ordered as well
+    _replay(G, G.pendulum_config, O.pendulum_config, n=64, steps=220, mem=32768, randomization=1.0, test_interval=2)
