@@ -449,9 +449,12 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
     if (!r && cudaMemset(p.pressure, 0, n * sizeof(uint32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
     if (!r && cudaMemset(p.prev_hash, 0, n * T * sizeof(uint32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
   }
+  if (!r) r = dalloc(c, &p.oob, 1);
+  if (!r && cudaMemset(p.oob, 0, sizeof(int32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
   if (!r) r = dalloc(c, &p.state, n * c->S);
   if (!r) r = dalloc(c, &p.action, n);
   if (!r) r = dalloc(c, &p.prev_idx, n * T);
+  if (!r && cudaMemset(p.prev_idx, 0, n * T * sizeof(uint32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
   if (!r) r = dalloc(c, &p.trace_idx, n * T * (size_t)p.trace_cap);
   if (!r) r = dalloc(c, &p.trace_len, n);
   if (!r) r = dalloc(c, &p.trace_head, n);
@@ -1249,9 +1252,11 @@ extern "C" int grlcu_replay_step(grlcu_ctx *c, const grlcu_replay_in *in, grlcu_
   DOWN(o_swept, swept, int32_t, n); DOWN(o_trace_len, trace_len, int32_t, n);
   DOWN(o_trace_index, trace_index, uint32_t, cap * T * n);
 #undef DOWN
-  int32_t mismatch = 0;
+  int32_t mismatch = 0, oob = 0;
   if (c->geo) CU(cudaMemcpyAsync(&mismatch, c->p.geo.mismatch, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(&oob, c->p.oob, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
   CU(cudaStreamSynchronize(c->stream));
+  if (oob) return fail(GRLCU_ERR_CUDA, "grlcu_replay_step: a physical table slot beyond the agent's row (%u doubles) was computed", c->p.tstride);
   if (mismatch)
     return fail(GRLCU_ERR_CUDA, "grlcu_replay_step: a tile's geometric slot differs from perm[hash index] (layout bug)");
   return 0;

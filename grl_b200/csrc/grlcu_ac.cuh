@@ -319,6 +319,7 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
   ac_core<DYN, T, false>(p, ac, ag, Cache<T>(), critic, actor, sid, a, gid, obs, reward, terminal != 2, !test, test,
                          true, io.u[a], io.o_hash ? io.o_hash + a : nullptr, io.o_index ? io.o_index + a : nullptr, o,
                          noise, qp, target, delta, swept);
+  for (int j = 0; j < T; ++j) if (ag.pidx[j] + 1u >= p.tstride + 0u && terminal != 2) *p.oob = 1;     // pair {critic, actor} inside the row
   if (io.o_q)
   {
     io.o_q[a] = o.pi; io.o_q[(size_t)n + a] = o.vnext; io.o_q[(size_t)2 * n + a] = o.u; io.o_q[(size_t)3 * n + a] = o.action;

@@ -91,6 +91,7 @@ struct Params
   // Per-agent lambda: launch order of the 32-agent chunks, sorted by lambda (chunk_map[k] = chunk that thread-chunk k of a
   // launch runs), so that a cohort launch holds agents with traces of similar length; NULL = identity
   const uint32_t *chunk_map;
+  int32_t  *oob;              // replay kernels: a physical slot beyond the agent's table row was seen (must stay 0)
   // projector/tile_coding safe > 0 (tile_coding.h:116-148): per-agent collision-claim table and what goes with it
   int32_t  safe;              // 0 off, 1 claim on the predictor's projections, 2 claim on every projection
   int32_t  *claims;           // [n][memory] TileCodingProjector::indices_ (-1 = free)

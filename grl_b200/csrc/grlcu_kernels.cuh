@@ -452,7 +452,10 @@ k_replay(Params p, ReplayIO io)
   if (terminal != 2)
   {
     if (test) p.test_act_ctr[a] += 1; else ag.act_ctr++;
+    // bounds check of every physical slot this step used (compute-sanitizer is not available on the pool)
+    for (int k = 0; k < A * T; ++k) if (sid[k * kMaxBlock] >= p.tstride) *p.oob = 1;
   }
+  for (int j = 0; j < T; ++j) if (ag.pidx[j] >= p.tstride) *p.oob = 1;
   if (io.o_action_index) io.o_action_index[a] = own;
   if (io.o_q_prev) io.o_q_prev[a] = qp;
   if (io.o_target) io.o_target[a] = target;
