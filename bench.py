@@ -88,6 +88,26 @@ def table_bytes_per_step(workload, V):
     return (768 if workload in AC_WORKLOADS else 640) + 16 * V
 
 
+def committed_traffic(workload, agents, memory, agent_steps_per_launch):
+    """DRAM traffic of one launch of the run kernel, from the committed `ncu --set full` capture of this exact workload
+    (profiles/traffic.json, written by tools/update_traffic.py): (bytes per launch, capture file, sha of the kernel
+    sources the capture was taken from, whether that is the current tree).  Per launch, like `roofline.achieved`: the
+    capture's bytes per agent-step x the agent-steps of one launch of THIS run (equal to the capture's own
+    dram_bytes_per_launch when the launches hold the same agents).  A cross-reference, not a measurement of the run
+    that prints it: it is only turned into `traffic_frac` when the kernel sources are byte-identical."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get("%s:%d:%d" % (workload, agents, memory))
+    except (OSError, ValueError) as exc:
+        sys.stderr.write("bench: profiles/traffic.json not usable (%s)\n" % exc)
+        return None, None, None, False
+    if not t:
+        return None, None, None, False
+    tree = t.get("kernel_sources_sha")
+    return (t["dram_bytes_per_agent_step"] * agent_steps_per_launch, t["capture"], tree,
+            tree == kernel_sources_sha())
+
+
 def kernel_sources_sha():
     """sha1 over the CUDA sources of libgrlcu.so: ties a committed ncu capture to the tree it was taken from."""
     import hashlib
@@ -325,19 +345,8 @@ def ours(args):
         B = table_bytes_per_step(args.workload, V)
         per_gpu_steps = steps_all / world
         achieved = per_gpu_steps * B / (kern_ms * 1e-3) / 1e9 if kern_ms > 0 else 0.0
-        # DRAM traffic of one launch, from the committed ncu capture of this exact workload (if there is one)
-        # (a cross-reference, not a measurement of this run: it is only turned into a fraction when the kernel
-        # sources are byte-identical to the ones the capture was taken from)
-        traffic, traffic_src, traffic_tree, traffic_current = None, None, None, False
-        try:
-            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                t = json.load(f).get("%s:%d:%d" % (args.workload, args.agents, args.memory))
-            if t:
-                traffic, traffic_src = t["dram_bytes_per_pass"], t["capture"]
-                traffic_tree = t.get("kernel_sources_sha")
-                traffic_current = traffic_tree == kernel_sources_sha()
-        except Exception:
-            pass
+        traffic, traffic_src, traffic_tree, traffic_current = committed_traffic(
+            args.workload, args.agents, args.memory, per_gpu_steps / max(kern_launches, 1))
         # What actually bounds the path: every table access is a hash-random 8-byte word.  Ceilings measured on
         # this GPU type (profiles/random_access_ceilings.json); accesses counted on the device.
         random_access = None
@@ -388,7 +397,7 @@ def ours(args):
                          # sector-granular figure: the DRAM bytes the hardware moved per launch (ncu capture)
                          # over this run's measured launch time, as a fraction of the same peak
                          "traffic_tree": traffic_tree, "traffic_is_of_this_tree": traffic_current,
-                         "traffic_frac": (traffic / (kern_ms / max(args.steps, 1) * 1e-3) / 1e9 / peak)
+                         "traffic_frac": (traffic / (kern_ms / max(kern_launches, 1) * 1e-3) / 1e9 / peak)
                                          if traffic and kern_ms > 0 and traffic_current else None,
                          "peak_source": peak_src, "random_access": random_access,
                          "bytes_per_agent_step": B, "V_mean": V,
