@@ -455,14 +455,14 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
   if (!r) r = dalloc(c, &p.action, n);
   if (!r) r = dalloc(c, &p.prev_idx, n * T);
   if (!r && cudaMemset(p.prev_idx, 0, n * T * sizeof(uint32_t)) != cudaSuccess) r = fail(GRLCU_ERR_CUDA, "cudaMemset failed");
-  if (!r) r = dalloc(c, &p.trace_idx, n * T * (size_t)p.trace_cap);
+  if (!r) r = dalloc(c, &p.trace_idx, warp_rows_agents(n) * T * (size_t)p.trace_cap);     // blocked by warp (warp_rows)
   if (!r) r = dalloc(c, &p.trace_len, n);
   if (!r) r = dalloc(c, &p.trace_head, n);
   if (!r) r = dalloc(c, &p.total_decay, n);
   if (!r) r = dalloc(c, &p.flags, n);
   if (!r) r = dalloc(c, &p.dupmask, n);
   {
-    // one contiguous block of cache_val per launch cohort (see grlcu_run): [blocks][cap*T][cblock]
+    // cblock: agents per launch cohort (see grlcu_run); cache_val itself is blocked by warp (grlcu_cached.cuh)
     const int roomy_cap = c->sm_count * 8 * 32 / c->block * c->block;
     p.cblock = (uint32_t)n_agents;
     if (n_agents > roomy_cap)
@@ -470,10 +470,9 @@ extern "C" int grlcu_create(const grlcu_config *cfg, int32_t n_agents, int64_t f
       const int parts = (n_agents + roomy_cap - 1) / roomy_cap;
       p.cblock = (uint32_t)(((n_agents + parts - 1) / parts + c->block - 1) / c->block * c->block);
     }
-    const size_t blocks = (n + p.cblock - 1) / p.cblock;
-    if (!r) r = dalloc(c, &p.cache_val, blocks * p.cblock * T * (size_t)p.trace_cap);
+    if (!r) r = dalloc(c, &p.cache_val, warp_rows_agents(n) * T * (size_t)p.trace_cap);      // [n / 32][cap*T][32]
   }
-  if (!r) r = dalloc(c, &p.cache_mask, n * (size_t)p.trace_cap);
+  if (!r) r = dalloc(c, &p.cache_mask, warp_rows_agents(n) * (size_t)p.trace_cap);
   if (!r) r = dalloc(c, &p.act_ctr, n);
   if (!r) r = dalloc(c, &p.test_act_ctr, n);
   if (!r) r = dalloc(c, &p.episode_ctr, n);

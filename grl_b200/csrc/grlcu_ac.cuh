@@ -335,7 +335,7 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
       const int pos = ring_pos(ag.head, k, p.trace_cap);
       for (int j = 0; j < T; ++j)
       {
-        uint32_t x = k < ag.len ? p.trace_idx[((size_t)pos * T + j) * n + a] : kInvalidIndex;
+        uint32_t x = k < ag.len ? warp_rows(p.trace_idx, a, (size_t)p.trace_cap * T)[(pos * T + j) * kLanes] : kInvalidIndex;
         if (x != kInvalidIndex) x >>= 1;           // the ring holds physical slots
         io.o_trace_index[((size_t)k * T + j) * n + a] = x;
       }

@@ -79,8 +79,8 @@ struct Params
   int32_t  target_kind;       // bootstrap value: 0 Q(s',a') (SARSA), 1 max_a Q(s',a) (Q-learning), 2 policy value (expected SARSA)
   double   target_epsilon;    // expected SARSA: target policy's epsilon (< 0: greedy sampler)
   double   softmax_tau;       // > 0: the learning policy's sampler is sampler/softmax with this temperature
-  double   *cache_val;        // [n / cblock][cap*T][cblock] cached trace weights (grlcu_cached.cuh): one contiguous block per cohort
-  uint32_t cblock;            // agents per block of cache_val (= the launch cohort, so that a cohort's cache is one address range)
+  double   *cache_val;        // [n / 32][cap*T][32] cached trace weights, blocked by warp (grlcu_cached.cuh)
+  uint32_t cblock;            // agents per launch cohort (grlcu_run)
   uint32_t *cache_mask;       // [cap][n] valid bits per trace entry
   uint64_t *act_ctr, *test_act_ctr, *episode_ctr, *tt, *ss, *swept;
   uint64_t *tblw;             // random 8-byte table stores issued (roofline accounting)
@@ -539,17 +539,28 @@ __device__ __forceinline__ void set_prev_projection(Agent<DYN, T> &ag, const uin
   ag.flags = (ag.flags & ~8) | (has_duplicates<T>(ag.pidx) ? 8 : 0);
 }
 
+// Per-agent rows of the trace arrays (trace_idx, cache_val, cache_mask) are blocked by warp: row r of agent a lives at
+// base[(a / 32) * rows * 32 + r * 32 + a % 32].  A warp still reads one row as one contiguous segment, but the distance
+// between an agent's rows is a compile-time constant (immediate offsets instead of a multiply-add per access) and the
+// rows of one ring entry are contiguous in DRAM.
+constexpr uint32_t kLanes = 32;
+template <typename X>
+__device__ __forceinline__ X *warp_rows(X *base, int a, size_t rows)
+{
+  return base + (size_t)((uint32_t)a >> 5) * rows * kLanes + ((uint32_t)a & 31u);
+}
+__host__ __device__ inline size_t warp_rows_agents(size_t n) { return (n + 31) / 32 * 32; }   // agents to allocate for
+
 // EnumeratedTrace::add tail (trace.h:226-233 / 253-260): push p, total_decay *= decay, pop while
 // total_decay < dc.  The ring only moves its head; popped entries are simply no longer counted.
 template <int DYN, int T>
 __device__ __forceinline__ void trace_push(const Params &p, Agent<DYN, T> &ag, uint32_t *tr, double e, double dc)
 {
   const int cap = p.trace_cap;
-  const size_t n = (size_t)p.n;
   ag.head = ag.head + 1 == cap ? 0 : ag.head + 1;
-  uint32_t *dst = tr + (size_t)ag.head * T * n;
+  uint32_t *dst = tr + (size_t)ag.head * T * kLanes;
 #pragma unroll
-  for (int j = 0; j < T; ++j) dst[j * n] = ag.pidx[j];
+  for (int j = 0; j < T; ++j) dst[j * kLanes] = ag.pidx[j];
   ag.len++;
   ag.dupmask = (ag.dupmask << 1) | ((ag.flags & 8) ? 1ull : 0ull);
   ag.total_decay *= e;
@@ -576,8 +587,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
                                              double &o_qp, double &o_target, double &o_delta, int &o_swept)
 {
   const int cap = p.trace_cap;
-  const size_t n = (size_t)p.n;
-  uint32_t *tr = p.trace_idx + a;               // element (pos, j) at tr[((size_t)pos*T + j)*n]
+  uint32_t *tr = warp_rows(p.trace_idx, a, (size_t)cap * T);   // element (pos, j) at tr[(pos*T + j)*kLanes]
   double target = reward;
   if (bootstrap) target += p.gamma * q_next;    // pow(gamma, 1)
   double qp = 0;
@@ -618,14 +628,14 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
       double weight = 1.;
       for (int k = 0; k < ag.len; ++k)
       {
-        uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * n;
+        uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * kLanes;
         const bool sw = weight > 0.001;           // representation.h:81
         const double inc = weight * ad * e;
         weight *= e;
         uint32_t ix[T];
         double v[T];
 #pragma unroll
-        for (int j = 0; j < T; ++j) ix[j] = ent[j * n];
+        for (int j = 0; j < T; ++j) ix[j] = ent[j * kLanes];
 #pragma unroll
         for (int j = 0; j < T; ++j)
           if (sw && ix[j] != kInvalidIndex) v[j] = ld_tbl(tbl + ix[j]);
@@ -655,7 +665,7 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
 #pragma unroll
               for (int jj = 0; jj < T; ++jj) hit |= (x == ag.pidx[jj]);
             }
-            if (hit) ent[j * n] = kInvalidIndex;                // ssub (projection.h:93-104)
+            if (hit) ent[j * kLanes] = kInvalidIndex;                // ssub (projection.h:93-104)
           }
         }
       }
@@ -672,11 +682,11 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
       double weight = 1.;
       for (int k = 0; k < ag.len && weight > 0.001; ++k)
       {
-        const uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * n;
+        const uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * kLanes;
         const double inc = weight * ad * e;
         for (int j = 0; j < T; ++j)
         {
-          uint32_t ix = ent[j * n];
+          uint32_t ix = ent[j * kLanes];
           if (ix != kInvalidIndex) { tbl[ix] = ld_tbl(tbl + ix) + inc; ++swept; }
         }
         weight *= e;
@@ -686,14 +696,14 @@ __device__ __forceinline__ void sarsa_update(const Params &p, Agent<DYN, T> &ag,
       if (p.trace_kind == 1)
         for (int k = 0; k < ag.len; ++k)
         {
-          uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * n;
+          uint32_t *ent = tr + (size_t)ring_pos(ag.head, k, cap) * T * kLanes;
           for (int j = 0; j < T; ++j)
           {
-            uint32_t ix = ent[j * n];
+            uint32_t ix = ent[j * kLanes];
             bool hit = false;
 #pragma unroll
             for (int jj = 0; jj < T; ++jj) hit |= (ix == ag.pidx[jj]);
-            if (hit) ent[j * n] = kInvalidIndex;
+            if (hit) ent[j * kLanes] = kInvalidIndex;
           }
         }
       trace_push<DYN, T>(p, ag, tr, e, dc);

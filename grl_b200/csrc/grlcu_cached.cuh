@@ -33,24 +33,26 @@ __device__ __forceinline__ bool is_sentinel(double v) { return __double2hiint(v)
 __device__ __forceinline__ int sentinel_slot(double v) { return __double2loint(v); }
 __device__ __forceinline__ double make_sentinel(int slot) { return __hiloint2double(kSentinelHi, slot); }
 
-// Cache geometry: slot = pos*T + j (pos = ring position); cv[slot*n + a]; vmask[pos*n + a] bit j = valid.
+// Cache geometry: slot = pos*T + j (pos = ring position); cv[(a/32)*cap*T*32 + slot*32 + a%32]; vmask[(a/32)*cap*32 + pos*32 + a%32] bit j = valid.
 template <int T>
 struct Cache
 {
-  double   *cv;      // + a
-  uint32_t *vmask;   // + a
-  uint32_t *ring;    // trace_idx + a
-  uint32_t  n;       // element indices fit 32 bits: trace_cap * T * n < 2^31 is checked by grlcu_create
-  uint32_t  cn;      // stride of cv (agents per cache block)
+  double   *cv;
+  uint32_t *vmask;
+  uint32_t *ring;    // trace_idx
+  // all three arrays are blocked by warp (warp_rows, grlcu_agent.cuh): the 16 slots of a ring entry are 256 bytes apart
+  // in cv and 128 in ring -- compile-time strides: one base address per entry and immediate offsets instead of a
+  // multiply-add per access (the address arithmetic of val() was a fifth of the instructions the pendulum kernel
+  // executed, profiles/r02_ncu_pendulum.txt), and what a warp streams per entry is contiguous in DRAM
   __device__ __forceinline__ void bind(const Params &p, int a)
   {
-    const uint32_t blk = (uint32_t)a / p.cblock;
-    cv = p.cache_val + (size_t)blk * ((size_t)p.trace_cap * T) * p.cblock + ((uint32_t)a - blk * p.cblock);
-    vmask = p.cache_mask + a; ring = p.trace_idx + a; n = (uint32_t)p.n; cn = p.cblock;
+    cv = warp_rows(p.cache_val, a, (size_t)p.trace_cap * T);
+    vmask = warp_rows(p.cache_mask, a, (size_t)p.trace_cap);
+    ring = warp_rows(p.trace_idx, a, (size_t)p.trace_cap * T);
   }
-  __device__ __forceinline__ double &val(int slot) const { return cv[(uint32_t)slot * cn]; }
-  __device__ __forceinline__ uint32_t &mask(int pos) const { return vmask[(uint32_t)pos * n]; }
-  __device__ __forceinline__ uint32_t &idx(int pos, int j) const { return ring[(uint32_t)(pos * T + j) * n]; }
+  __device__ __forceinline__ double &val(int slot) const { return cv[(uint32_t)slot * kLanes]; }
+  __device__ __forceinline__ uint32_t &mask(int pos) const { return vmask[(uint32_t)pos * kLanes]; }
+  __device__ __forceinline__ uint32_t &idx(int pos, int j) const { return ring[(uint32_t)(pos * T + j) * kLanes]; }
 };
 
 // 4 bits per slot jj of ring entry `pos`: how many alias slots of the entry duplicate the (valid) slot jj

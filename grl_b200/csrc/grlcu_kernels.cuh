@@ -469,7 +469,7 @@ k_replay(Params p, ReplayIO io)
       for (int j = 0; j < T; ++j)
       {
         // the ring holds physical slots; the reference's trace holds the logical indices
-        uint32_t x = k < ag.len ? p.trace_idx[((size_t)pos * T + j) * n + a] : kInvalidIndex;
+        uint32_t x = k < ag.len ? warp_rows(p.trace_idx, a, (size_t)p.trace_cap * T)[(pos * T + j) * kLanes] : kInvalidIndex;
         if (GEO && x != kInvalidIndex) x = __ldg(p.geo.iperm + x);
         io.o_trace_index[((size_t)k * T + j) * n + a] = x;
       }
