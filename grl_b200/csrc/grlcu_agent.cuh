@@ -227,6 +227,15 @@ __device__ __forceinline__ int sample_action(const double (&q)[A], const Draws &
   return mai;
 }
 
+// 4-byte global -> shared copy that occupies no register and does not stall the issuing thread (LDGSTS); a thread
+// sees its own copies after stash_wait().  Used for table-layout lookups whose only consumer is the slot stash.
+__device__ __forceinline__ void stash_async(uint32_t *smem_dst, const uint32_t *src)
+{
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(src) : "memory");
+}
+__device__ __forceinline__ void stash_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // TileCodingProjector::getFeatureLocation with a claim table (tile_coding.h:116-148): linear probing from h % memory
 // until the entry is h or free; `indices_[ii] != h` compares the int32 entry with the unsigned hash, `!= -1` as int.
 __device__ __noinline__ uint32_t probe_location(int32_t *claims, uint32_t memory, uint32_t h, bool claim, uint32_t *pressure)
@@ -367,14 +376,12 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
       }
       if (GEO && inbox)
       {
-        const uint32_t own = (__ldg(p.geo.gflags + (group >> 3)) >> ((group & 7u) * 4u)) & 15u;
+        // slotmap[home] is home itself for a word that owns its slot and the earlier tile's slot for one that collided
+        // (grlcu_layout.h).  The lookups go global -> shared asynchronously (no register, no wait): all A*T of a step are
+        // in flight together and awaited once after the loop, where the rolled loop used to wait for a flag word and
+        // then for the collided words' entries tiling by tiling (19 % of the stall samples, profiles/r02_ncu_pendulum.txt)
 #pragma unroll
-        for (int aa = 0; aa < A; ++aa)
-        {
-          uint32_t slot = group * 4u + aa;
-          if (!((own >> aa) & 1u)) slot = __ldg(p.geo.slotmap + slot);     // collided with an earlier tile: shares its slot
-          sid[(aa * T + j) * kMaxBlock] = slot;
-        }
+        for (int aa = 0; aa < A; ++aa) stash_async(&sid[(aa * T + j) * kMaxBlock], p.geo.slotmap + group * 4u + aa);
       }
       if (!GEO || !inbox || hash_out || index_out)
       {
@@ -405,14 +412,18 @@ __device__ __forceinline__ void q_values(const Params &p, const double *tbl, con
           if (!GEO) sid[(aa * T + j) * kMaxBlock] = x;
           else
           {
-            const uint32_t slot = __ldg(p.geo.perm + x);
-            if (!inbox) sid[(aa * T + j) * kMaxBlock] = slot;
-            else if (slot != sid[(aa * T + j) * kMaxBlock]) *p.geo.mismatch = 1;   // replay only: must never happen
+            if (!inbox) stash_async(&sid[(aa * T + j) * kMaxBlock], p.geo.perm + x);       // awaited after the loop
+            else
+            {
+              stash_wait();                                                              // replay only
+              if (__ldg(p.geo.perm + x) != sid[(aa * T + j) * kMaxBlock]) *p.geo.mismatch = 1;   // must never happen
+            }
           }
         }
       }
     }
   }
+  if (GEO) stash_wait();
   if (SAFE)
   {
     // getFeatureLocation in the reference's order -- action by action, tiling by tiling (q.cpp:94-107 projects the

@@ -59,17 +59,18 @@ struct Cache
 template <int T>
 __device__ __noinline__ uint64_t alias_counts(const Cache<T> &c, int pos, uint32_t m)
 {
+  // all loads first: rolled, every iteration waited for its own ring word (15 round trips in a row for the warp)
+  uint32_t x[T];
+#pragma unroll
+  for (int j = 1; j < T; ++j) x[j] = c.idx(pos, j);
   uint64_t counts = 0;
-#pragma unroll 1
+#pragma unroll
   for (int j = 1; j < T; ++j)
-  {
-    const uint32_t x = c.idx(pos, j);
-    if (!((m >> j) & 1u) && x != kInvalidIndex && (x & kAliasBit))
+    if (!((m >> j) & 1u) && x[j] != kInvalidIndex && (x[j] & kAliasBit))
     {
-      const int jj = (int)(x & 15u);
+      const int jj = (int)(x[j] & 15u);
       if ((m >> jj) & 1u) counts += 1ull << (4 * jj);
     }
-  }
   return counts;
 }
 

@@ -80,7 +80,7 @@ def main():
             agg[loc][k] += v
             tot[k] += v
     print("totals:", {k: t for k, t in zip(keys, tot)})
-    for sortkey in (0, 2):
+    for sortkey in (0, 1, 2):
         print("\n== top lines by %s" % keys[sortkey])
         print("%-28s" % "file:line" + "".join("%14s" % k[-13:] for k in keys))
         for loc, v in sorted(agg.items(), key=lambda kv: -kv[1][sortkey])[:top]:
