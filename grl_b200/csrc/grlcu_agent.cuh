@@ -25,10 +25,11 @@ namespace grlcu {
 //     coordinates k_i of every observation dimension), tiling by tiling, action by action; the A action words of one
 //     (cell, tiling) group get consecutive slots, padded to one 32-byte sector: slot = ((cell * T) + j) * 4 + a;
 //   * a word whose index x was already placed by an earlier tile (a hash collision) simply shares that earlier slot
-//     (slotmap[] names it, its bit in gflags[] is clear): semantics unchanged by construction;
+//     (slotmap[] names it; slotmap[] of a word that owns its slot is that slot): semantics unchanged by construction;
 //   * indices no tile of the box maps to fill the holes and the tail.
-// The fused kernel computes the slot from the tile coordinates (no hash, no lookup) for every word that lives in
-// its own group's sector; the MurmurHash2 path + perm[] serve observations outside the box.
+// The fused kernel computes the group from the tile coordinates (no hash) and takes the slots of its A words from
+// slotmap[] with asynchronous global -> shared copies (stash_async); the MurmurHash2 path + perm[] serve observations
+// outside the box.
 struct Geo
 {
   int32_t  enabled;             // 1: slots from tile coordinates inside the box (perm[] outside); 2: perm[] only (visit-ordered layout)
@@ -38,7 +39,7 @@ struct Geo
   const uint32_t *perm;         // [memory] logical index -> physical slot
   const uint32_t *iperm;        // [tstride] physical slot -> logical index (kInvalidIndex: padding)
   const uint32_t *slotmap;      // [ncells * T * 4] physical slot of every in-box tile word
-  const uint32_t *gflags;       // 4 bits per (cell, tiling) group: bit a = action a's word is in the group's own sector
+  const uint32_t *gflags;       // 4 bits per (cell, tiling) group: bit a = action a's word is in the group's own sector (layout statistics; the kernels read slotmap[] only)
   int32_t  *mismatch;           // replay kernels: geometric slot != perm[hash index] seen (must stay 0)
   // pilot run of grlcu_create (visit-ordered layout): every projected group is logged as (hash state after the
   // observation coordinates) << 8 | tiling

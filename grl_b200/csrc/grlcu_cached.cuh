@@ -298,8 +298,11 @@ __device__ __forceinline__ void sarsa_update_cached(const Params &p, Agent<DYN, 
   for (int j = 0; j < T; ++j)
     if (((owner >> j) & 1u) && sp[j] >= 0)
     {
+      // a reduction, not a read-modify-write: nothing waits for it (the load of each of these used to be a round trip of
+      // its own, one after the other, because the compiler cannot tell whether two of them hit the same word); the
+      // thread's own later loads and stores of the word are ordered after it (same thread, same address)
       const int pos = sp[j] / T, jj = sp[j] - pos * T;
-      c.mask(pos) &= ~(1u << jj);
+      atomicAnd(&c.mask(pos), ~(1u << jj));
     }
   if (e < dc) cache_clear<DYN, T>(p, ag, c, tbl);                      // trace.h:220-221
   // push; then pop while total_decay < 0.01 (flushing what leaves)
