@@ -6,7 +6,7 @@
 //   state      double  [S][n]               environment state
 //   action     double  [n]                  action to apply at the next step
 //   prev_idx   uint32  [T][n]               projection of (prev_obs, prev_action)
-//   trace_idx  uint32  [cap][T][n]          enumerated trace ring (0xFFFFFFFF = invalidated)
+//   trace_idx  uint32  [n/32][cap*T][32]    enumerated trace ring (0xFFFFFFFF = invalidated), blocked by warp (warp_rows)
 //   trace_len/head int [n], total_decay double [n]
 //   counters / returns [n]
 // Citations: /root/reference/base.
@@ -82,7 +82,7 @@ struct Params
   double   softmax_tau;       // > 0: the learning policy's sampler is sampler/softmax with this temperature
   double   *cache_val;        // [n / 32][cap*T][32] cached trace weights, blocked by warp (grlcu_cached.cuh)
   uint32_t cblock;            // agents per launch cohort (grlcu_run)
-  uint32_t *cache_mask;       // [cap][n] valid bits per trace entry
+  uint32_t *cache_mask;       // [n/32][cap][32] valid bits per trace entry, blocked by warp
   uint64_t *act_ctr, *test_act_ctr, *episode_ctr, *tt, *ss, *swept;
   uint64_t *tblw;             // random 8-byte table stores issued (roofline accounting)
   uint32_t *episodes;
