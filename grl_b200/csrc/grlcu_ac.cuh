@@ -220,12 +220,10 @@ k_run_ac(Params p, ACParams ac, int agent_begin, int agent_end, int64_t n_steps,
       }
       int term0;
       observe<DYN>(ag.x, p.timeout, obs, term0, p.end_stop_penalty);
-      if (!test)
-      {
-        // TDAgent::start -> finalize -> trace clear
-        if (CACHED) cache_clear<DYN, T>(p, ag, c, critic);
-        else { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
-      }
+      // TDAgent::start -> predictor_->finalize() is ActionACPredictor::finalize() (ac.cpp:170-173): the empty
+      // Predictor::finalize() and nothing else -- it does not reach the critic, so the critic's eligibility trace is NOT
+      // cleared between episodes (TDPredictor::finalize, td.cpp:93-99, only runs on the experiment's reset at the start of
+      // a run = grlcu_reset).  The reference's own ac.cpp / td.cpp, compiled, say so (tests/test_oracle_vs_ref_agent.py).
       ag.total_reward = 0;
       ag.flags = (ag.flags & 16) | 1 | (test ? 2 : 0);
     }
@@ -286,7 +284,7 @@ k_replay_ac(Params p, ACParams ac, ReplayIO io)
     double obs0[OBS];
     int term0;
     observe<DYN>(ag.x, p.timeout, obs0, term0, p.end_stop_penalty);
-    if (!test) { ag.len = 0; ag.total_decay = 1.; ag.dupmask = 0; }
+    // (no trace clear: ActionACPredictor::finalize does not reach the critic, see k_run_ac)
     ag.total_reward = 0;
     ag.flags = (ag.flags & 16) | 1 | (test ? 2 : 0);
     ac_core<DYN, T, false>(p, ac, ag, Cache<T>(), critic, actor, sid, a, gid, obs0, 0., true, false, test, true,

@@ -37,10 +37,17 @@
  *   (c) the reference's OWN environment sources (pendulum.cpp, cart_pole.cpp, cart_double_pole.cpp) compiled from
  *       /root/reference against stand-in headers into oracle/_ref/libgrlref_env.so: eom / start / actuate / observe /
  *       evaluate bit-exact on 1e5 random inputs per function (tests/test_oracle_vs_ref.py);
- *   (d) an independent byte-wise MurmurHash2 for the tile hash, Random123's known answers for Philox.
+ *   (d) an independent byte-wise MurmurHash2 for the tile hash, Random123's known answers for Philox;
+ *   (e) the reference's OWN agent-side sources (tile_coding.cpp, linear.cpp, enumerated.cpp, uniform.cpp, greedy.cpp, q.cpp,
+ *       action.cpp, predictor.cpp, sarsa.cpp, td.cpp, ac.cpp, agents/td.cpp, agents/fixed.cpp) compiled from /root/reference with
+ *       the reference's own headers into oracle/_ref/libgrlref_agent.so (stand-ins: Eigen, one YAML type) and fed this oracle's
+ *       observations: every action and the final weight tables bit-exact over thousands of steps for the SARSA agent
+ *       (pendulum, cart-pole; replacing / accumulating / no trace; test episodes; hash collisions) and for the actor-critic
+ *       agent on all three dynamics (tests/test_oracle_vs_ref_agent.py).  That run corrected ac_step: the reference does not
+ *       clear the critic's trace between episodes.
  * PARITY UNPINNED: the summation order inside Eigen's Matrix3d::inverse() and 3x3 products (cart-double-pole; the
- * stand-in shares the oracle's assumption), and the actor-critic agent (ac_step: the reference's only vector for it,
- * tests/template/cart_double_pole-ac-tc-0.txt, was produced by an older predictor).
+ * stand-in shares the oracle's assumption); DynamicalModel::step for the 7-state system and the experiment loop of
+ * online_learning.cpp are pinned only through (a) and (b).
  */
 #ifndef GRL_ORACLE_H_
 #define GRL_ORACLE_H_

@@ -782,8 +782,12 @@ static int ac_step(orc_agent *a, orc_record *rec)
                a->tt % (uint64_t)(c->test_interval + 1) == (uint64_t)c->test_interval);
     double r = task_start(a, a->test, a->state);
     orc_observe(c, a->state, obs, &terminal);
-    if (!a->test)
-      trace_clear(&a->trace);                         /* TDAgent::start -> predictor finalize -> critic trace */
+    /* TDAgent::start -> predictor_->finalize() is ActionACPredictor::finalize() here, which only calls the empty
+     * Predictor::finalize() (ac.cpp:170-173, predictor.cpp:100-102): it does NOT reach the critic, so the critic's
+     * eligibility trace is NOT cleared between episodes -- it keeps decaying across the episode boundary and the first
+     * updates of an episode still move weights of the previous one.  (TDPredictor::finalize, td.cpp:93-99, runs only on
+     * the experiment's `reset` at the start of a run.)  Found by compiling the reference's own ac.cpp / td.cpp against
+     * this file (tests/test_oracle_vs_ref_agent.py); until then the oracle cleared the trace here. */
     a->action = ac_act(a, obs, a->test, 1, ahash, aidx, &pi, &noise);
     orc_project(c->resolution, c->wrapping, c->obs_dims, T, c->memory, obs, chash, cidx);
     memcpy(a->prev_obs, obs, sizeof(obs));

@@ -1,0 +1,157 @@
+"""The oracle's agent half against the reference's OWN agent-side sources, bit for bit (no GPU).
+
+oracle/_ref/libgrlref_agent.so (oracle/Makefile, target `ref`; built here, where /root/reference exists) holds the
+reference's tile_coding.cpp, linear.cpp, enumerated.cpp, uniform.cpp, greedy.cpp, q.cpp, action.cpp, predictor.cpp,
+sarsa.cpp, td.cpp, ac.cpp, agents/td.cpp and agents/fixed.cpp compiled with the reference's own headers; only Eigen
+(absent here) and one YAML type are stand-ins (oracle/ref_shim_eigen/).  oracle/ref_agent.cpp wires the objects the way
+grld does for cfg/pendulum/sarsa_tc.yaml and cfg/cart_double_pole/ac.yaml.
+
+Method: the oracle runs free in its glibc RNG mode (srand48(seed); per-object drand48_r streams seeded from lrand48() in
+grld's construction order, utils.h:84-137) and records every step; then srand48(seed) again, the reference objects are
+built and fed the SAME observations, rewards and terminal flags; they draw their own random numbers.  Compared: every
+action (episode starts included), and the weight tables at the end -- equality of the final tables means every read,
+target, TD error, write, trace sweep and trace update along the way was the same.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import _oracle as O
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "libgrlref_agent.so")
+
+pytestmark = pytest.mark.skipif(not os.path.exists(LIB),
+                                reason="oracle/_ref/libgrlref_agent.so is built where /root/reference exists (make -C oracle ref)")
+
+
+@pytest.fixture(scope="module")
+def ref():
+    L = C.CDLL(LIB)
+    dp = C.POINTER(C.c_double)
+    L.refag_prepare.restype = None
+    L.refag_create.restype = C.c_void_p
+    L.refag_create.argtypes = [C.POINTER(O.Config)]
+    L.refag_destroy.argtypes = [C.c_void_p]
+    L.refag_start.argtypes = [C.c_void_p, C.c_int, dp, dp]
+    L.refag_step.argtypes = [C.c_void_p, C.c_int, dp, C.c_double, C.c_int, dp]
+    L.refag_table.argtypes = [C.c_void_p, C.c_int, dp]
+    L.refag_project.argtypes = [C.c_void_p, C.c_int, dp, C.c_int, C.POINTER(C.c_uint32)]
+    L.refag_prepare()
+    return L
+
+
+def _bits(x):
+    return np.asarray(x, dtype=np.float64).view(np.uint64)
+
+
+def _run_both(ref, cfg, seed, steps):
+    L = O.lib()
+    ac = cfg.algo == O.ALGO_AC
+    cfg.rng = O.RNG_GLIBC
+    # 1. the oracle, free-running, recorded
+    L.orc_glibc_seed(seed)
+    a = L.orc_create(C.byref(cfg), 0)
+    recs = []
+    for _ in range(steps):
+        r = O.Record()
+        L.orc_step(a, C.byref(r))
+        recs.append(r)
+    table = np.ctypeslib.as_array(L.orc_table(a), shape=(cfg.memory,)).copy()
+    actor = np.ctypeslib.as_array(L.orc_actor_table(a), shape=(cfg.memory,)).copy() if ac else None
+    L.orc_destroy(a)
+
+    # 2. the reference's objects on the oracle's observations
+    L.orc_glibc_seed(seed)
+    h = ref.refag_create(C.byref(cfg))
+    assert h, "the reference's configure() threw"
+    OBS = cfg.obs_dims
+    act = C.c_double()
+    n_actions_checked = n_starts = n_ends = n_test = 0
+    for k, r in enumerate(recs):
+        if r.started:
+            obs0 = (C.c_double * O.MAX_DIMS)()
+            term = C.c_int32()
+            L.orc_observe(C.byref(cfg), r.start_state, obs0, C.byref(term))
+            assert ref.refag_start(h, r.test, obs0, C.byref(act)) == 0
+            want = r.start_q[3] if ac else cfg.actions[r.start_action_index]
+            assert _bits(act.value) == _bits(want), "start action at step %d: %r vs %r" % (k, act.value, want)
+            n_starts += 1
+        assert _bits(r.action) == _bits(act.value) or r.started, "step %d applies another action than the reference chose" % k
+        obs = (C.c_double * O.MAX_DIMS)(*r.obs)
+        assert ref.refag_step(h, r.test, obs, r.reward, r.terminal, C.byref(act)) == 0
+        n_test += r.test
+        if r.terminal == 2:
+            n_ends += 1
+            continue
+        want = r.q[3] if ac else cfg.actions[r.action_index]
+        assert _bits(act.value) == _bits(want), "action at step %d: %r vs %r" % (k, act.value, want)
+        n_actions_checked += 1
+    out = np.empty(cfg.memory)
+    assert ref.refag_table(h, 0, out.ctypes.data_as(C.POINTER(C.c_double))) == cfg.memory
+    assert np.array_equal(_bits(out), _bits(table)), "%d entries of the %s table differ" % (
+        int((_bits(out) != _bits(table)).sum()), "critic" if ac else "Q")
+    if ac:
+        assert ref.refag_table(h, 1, out.ctypes.data_as(C.POINTER(C.c_double))) == cfg.memory
+        assert np.array_equal(_bits(out), _bits(actor)), "%d entries of the actor table differ" % int((_bits(out) != _bits(actor)).sum())
+    ref.refag_destroy(h)
+    return dict(actions=n_actions_checked, starts=n_starts, absorbing_ends=n_ends, test_steps=n_test,
+                changed=int((table != table[0]).sum()))
+
+
+@pytest.mark.parametrize("seed", [1, 7])
+def test_pendulum_sarsa_agent_equals_the_reference_sources(ref, seed):
+    # cfg/pendulum/sarsa_tc.yaml: epsilon-greedy Q policy, SARSA(lambda) with the replacing trace, greedy test episodes
+    cfg = O.pendulum_config(memory=65536, test_interval=3, randomization=1.0)
+    s = _run_both(ref, cfg, seed, 4000)
+    assert s["actions"] > 3900 and s["starts"] >= 40 and s["test_steps"] > 500
+
+
+def test_pendulum_sarsa_small_table_collisions_and_accumulating_trace(ref):
+    cfg = O.pendulum_config(memory=257, test_interval=-1, randomization=1.0)
+    _run_both(ref, cfg, 3, 1500)
+    cfg = O.pendulum_config(memory=4096, test_interval=-1, randomization=1.0, trace=O.TRACE_ACCUMULATING)
+    _run_both(ref, cfg, 3, 1500)
+    cfg = O.pendulum_config(memory=4096, test_interval=-1, randomization=1.0, trace=O.TRACE_NONE)
+    _run_both(ref, cfg, 3, 800)
+
+
+def test_cart_pole_sarsa_agent_equals_the_reference_sources(ref):
+    # absorbing end-stops: Agent::end with an empty action (sarsa.cpp:104-109)
+    cfg = O.cart_pole_config(memory=262144, test_interval=5, randomization=1.0)
+    s = _run_both(ref, cfg, 2, 4000)
+    assert s["absorbing_ends"] >= 1
+
+
+@pytest.mark.parametrize("which", ["cart_double_pole", "pendulum", "cart_pole"])
+def test_actor_critic_agent_equals_the_reference_sources(ref, which):
+    # cfg/cart_double_pole/ac.yaml (and its pendulum / cart-pole siblings): policy/parameterized/action with Gaussian
+    # exploration drawn from the thread's RandGen (Box-Muller, utils.h:120-125), predictor/ac/action around
+    # predictor/critic/td with a replacing trace -- the path the reference's golden vector no longer pins
+    cfg = {"cart_double_pole": O.cart_double_pole_ac_config, "pendulum": O.pendulum_ac_config,
+           "cart_pole": O.cart_pole_ac_config}[which](test_interval=4)
+    s = _run_both(ref, cfg, 5, 3000)
+    assert s["actions"] > 2000 and s["starts"] >= 10
+
+
+def test_projector_alone_equals_the_reference_sources(ref):
+    # TileCodingProjector::project incl. wrapping and negative coordinates, against orc_project
+    L = O.lib()
+    cfg = O.pendulum_config(memory=65536)
+    cfg.rng = O.RNG_GLIBC
+    L.orc_glibc_seed(11)
+    h = ref.refag_create(C.byref(cfg))
+    rng = np.random.default_rng(0)
+    dims, T = cfg.obs_dims + 1, cfg.tilings
+    res = (C.c_double * dims)(*[cfg.resolution[i] for i in range(dims)])
+    wrp = (C.c_double * dims)(*[cfg.wrapping[i] for i in range(dims)])
+    hs, want, got = (C.c_uint32 * T)(), (C.c_uint32 * T)(), (C.c_uint32 * T)()
+    for _ in range(2000):
+        x = [rng.uniform(-7, 14), rng.uniform(-60, 60), rng.choice([-3.0, 0.0, 3.0])]
+        v = (C.c_double * dims)(*x)
+        L.orc_project(res, wrp, dims, T, cfg.memory, v, hs, want)
+        assert ref.refag_project(h, 0, v, dims, got) == T
+        assert list(got) == list(want), x
+    ref.refag_destroy(h)
