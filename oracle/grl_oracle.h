@@ -43,11 +43,13 @@
  *       the reference's own headers into oracle/_ref/libgrlref_agent.so (stand-ins: Eigen, one YAML type) and fed this oracle's
  *       observations: every action and the final weight tables bit-exact over thousands of steps for the SARSA agent
  *       (pendulum, cart-pole; replacing / accumulating / no trace; test episodes; hash collisions) and for the actor-critic
- *       agent on all three dynamics (tests/test_oracle_vs_ref_agent.py).  That run corrected ac_step: the reference does not
- *       clear the critic's trace between episodes.
+ *       agent on all three dynamics; likewise Q-learning, expected SARSA, sampler/softmax, the safe = 1|2 claim table, and
+ *       DynamicalModel::step of the reference's own modeled.cpp for the 3-, 5- and 7-state systems against orc_rk4
+ *       (tests/test_oracle_vs_ref_agent.py).  That run corrected ac_step: the reference does not clear the critic's trace
+ *       between episodes.
  * PARITY UNPINNED: the summation order inside Eigen's Matrix3d::inverse() and 3x3 products (cart-double-pole; the
- * stand-in shares the oracle's assumption); DynamicalModel::step for the 7-state system and the experiment loop of
- * online_learning.cpp are pinned only through (a) and (b).
+ * stand-in shares the oracle's assumption); the sequencing of ModeledEnvironment::step and of the experiment loop of
+ * online_learning.cpp is pinned only through (a) and (b).
  */
 #ifndef GRL_ORACLE_H_
 #define GRL_ORACLE_H_

@@ -3,7 +3,7 @@
  * oracle/Makefile (target `ref_agent`) compiles, from where they lie under /root/reference/base/src,
  *   projectors/tile_coding.cpp  representations/linear.cpp  traces/enumerated.cpp  discretizers/uniform.cpp
  *   samplers/greedy.cpp  policies/q.cpp  policies/action.cpp  predictor.cpp  predictors/sarsa.cpp  predictors/td.cpp
- *   predictors/ac.cpp  agents/td.cpp  agents/fixed.cpp
+ *   predictors/ac.cpp  agents/td.cpp  agents/fixed.cpp  environments/modeled.cpp  environments/{pendulum,cart_pole,cart_double_pole}.cpp
  * with the reference's own headers (vector.h, configurable.h, configuration.h, utils.h, trace.h, ...) and links them with
  * this file into oracle/_ref/libgrlref_agent.so.  The only stand-ins are Eigen (oracle/ref_shim_eigen/Eigen/Dense: the
  * library is absent here) and the YAML node type one declaration names; this file supplies the handful of globals that
@@ -26,13 +26,18 @@
 #include <grl/trace.h>
 #include <grl/discretizers/uniform.h>
 #include <grl/samplers/greedy.h>
+#include <grl/samplers/softmax.h>
 #include <grl/policies/q.h>
 #include <grl/policies/action.h>
 #include <grl/predictors/sarsa.h>
+#include <grl/predictors/advantage.h>
 #include <grl/predictors/td.h>
 #include <grl/predictors/ac.h>
 #include <grl/agents/td.h>
 #include <grl/agents/fixed.h>
+#include <grl/environments/pendulum.h>
+#include <grl/environments/cart_pole.h>
+#include <grl/environments/cart_double_pole.h>
 
 extern "C" {
 #include "grl_oracle.h"
@@ -69,8 +74,13 @@ struct RefAgent
   UniformDiscretizer disc;
   EpsilonGreedySampler sampler;
   GreedySampler test_sampler;
-  QPolicy policy, test_policy;
+  SoftmaxSampler softmax;
+  GreedySampler target_greedy;                 /* expected SARSA: the target policy's sampler */
+  EpsilonGreedySampler target_egreedy;
+  QPolicy policy, test_policy, target_policy;
   SARSAPredictor sarsa;
+  QPredictor qlearning;
+  ExpectedSARSAPredictor expected_sarsa;
   /* actor-critic */
   TileCodingProjector actor_proj;
   LinearRepresentation actor_repr;
@@ -180,17 +190,31 @@ extern "C" {
  * lrand48()).  Call once BEFORE seeding, so that every refag_create below starts from the same place. */
 void refag_prepare(void) { (void)RandGen::instance(); }
 
-/* The caller has done refag_prepare() once and srand48(seed) (orc_glibc_seed) just now.  In grld the thread's RandGen is
+/* The caller has done refag_prepare() once; srand48(seed) happens inside (see below).  In grld the thread's RandGen is
  * born inside the first representation's reset(): Rand() does srand48_r(lrand48()) (utils.h:90-93).  The instance of this
  * thread already exists, so it is re-seeded here the way a new one would be -- same call, same place in the lrand48()
  * sequence (nothing before the first representation draws).  Returns NULL and prints the reference's exception on failure. */
-void *refag_create(const orc_config *c)
+void *refag_create(const orc_config *c, long seed)
 {
   RefAgent *a = new RefAgent();
   a->c = *c;
   a->ac = c->algo == ORC_ALGO_AC;
   try
   {
+    /* expected SARSA's target policy owns a sampler whose Rand() consumes an lrand48() at construction but which never
+     * draws (ValuePolicy::value uses its distribution(), q.cpp).  The oracle does not model that object's stream, so it
+     * is built before the seed: the seeded sequence then starts where the oracle's does. */
+    Sampler *target_sampler = NULL;
+    if (c->algo == ORC_ALGO_EXPECTED_SARSA)
+    {
+      Configuration cfg;
+      cfg.set("epsilon", VectorConstructor(c->target_epsilon < 0 ? 0. : c->target_epsilon));
+      cfg.set("decay_rate", 1.0);
+      cfg.set("decay_min", 0.0);
+      if (c->target_epsilon < 0) { a->target_greedy.configure(cfg); target_sampler = &a->target_greedy; }
+      else { a->target_egreedy.configure(cfg); target_sampler = &a->target_egreedy; }
+    }
+    srand48(seed);
     RandGen::instance()->init(lrand48());
     if (!a->ac)
     {
@@ -205,19 +229,59 @@ void *refag_create(const orc_config *c)
         cfg.set("steps", VectorConstructor((double)c->n_actions));
         a->disc.configure(cfg);
       }
+      Sampler *learning_sampler;
+      if (c->sampler == ORC_SAMPLER_SOFTMAX)
+      {
+        Configuration cfg;
+        cfg.set("tau", c->softmax_tau);
+        a->softmax.configure(cfg);                              /* owns no Rand: draws from the thread's RandGen */
+        learning_sampler = &a->softmax;
+      }
+      else
       {
         Configuration cfg;
         cfg.set("epsilon", VectorConstructor(c->epsilon));
         cfg.set("decay_rate", 1.0);
         cfg.set("decay_min", 0.0);
         a->sampler.configure(cfg);                              /* new Rand(): lrand48() #2 */
+        learning_sampler = &a->sampler;
       }
-      configure_q_policy(a->policy, &a->disc, &a->proj, &a->repr, &a->sampler);
-      configure_critic(a->sarsa, *c, &a->proj, &a->repr, a->trace);
+      configure_q_policy(a->policy, &a->disc, &a->proj, &a->repr, learning_sampler);
+      Predictor *predictor;
+      if (c->algo == ORC_ALGO_Q)
+      {
+        Configuration cfg;
+        cfg.set("importer", ""); cfg.set("exporter", "");
+        cfg.set("discretizer", (void *)static_cast<Configurable *>(&a->disc));
+        cfg.set("projector", (void *)static_cast<Configurable *>(&a->proj));
+        cfg.set("representation", (void *)static_cast<Configurable *>(&a->repr));
+        if (a->trace) cfg.set("trace", (void *)static_cast<Configurable *>(a->trace)); else cfg.set("trace", "");
+        cfg.set("alpha", c->alpha); cfg.set("gamma", c->gamma); cfg.set("lambda", c->lambda);
+        a->qlearning.configure(cfg);
+        predictor = &a->qlearning;
+      }
+      else if (c->algo == ORC_ALGO_EXPECTED_SARSA)
+      {
+        configure_q_policy(a->target_policy, &a->disc, &a->proj, &a->repr, target_sampler);
+        Configuration cfg;
+        cfg.set("importer", ""); cfg.set("exporter", "");
+        cfg.set("projector", (void *)static_cast<Configurable *>(&a->proj));
+        cfg.set("representation", (void *)static_cast<Configurable *>(&a->repr));
+        cfg.set("policy", (void *)static_cast<Configurable *>(&a->target_policy));
+        if (a->trace) cfg.set("trace", (void *)static_cast<Configurable *>(a->trace)); else cfg.set("trace", "");
+        cfg.set("alpha", c->alpha); cfg.set("gamma", c->gamma); cfg.set("lambda", c->lambda);
+        a->expected_sarsa.configure(cfg);
+        predictor = &a->expected_sarsa;
+      }
+      else
+      {
+        configure_critic(a->sarsa, *c, &a->proj, &a->repr, a->trace);
+        predictor = &a->sarsa;
+      }
       {
         Configuration cfg;
         cfg.set("policy", (void *)static_cast<Configurable *>(&a->policy));
-        cfg.set("predictor", (void *)static_cast<Configurable *>(&a->sarsa));
+        cfg.set("predictor", (void *)static_cast<Configurable *>(predictor));
         a->agent.configure(cfg);
       }
       { Configuration cfg; a->test_sampler.configure(cfg); }  /* new Rand(): lrand48() #3 */
@@ -318,6 +382,37 @@ int refag_project(void *h, int actor, const double *in, int dims, uint32_t *inde
   if (!ip) return -1;
   for (size_t i = 0; i < ip->indices.size(); ++i) index[i] = (uint32_t)ip->indices[i];
   return (int)ip->indices.size();
+}
+
+/* DynamicalModel::step (modeled.cpp:254-276: RK4 over the dynamics' eom) of the reference's own modeled.cpp around its own
+ * dynamics classes: dyn 0 pendulum (3 states), 1 cart-pole (5), 2 cart-double-pole (7).  Returns tau, or -1. */
+double refag_model_step(int dyn, double control_step, int integration_steps, const double *state, double actuation, double *next)
+{
+  try
+  {
+    static PendulumDynamics pd; static CartPoleDynamics cpd; static CartDoublePoleDynamics cdpd;
+    static bool configured = false;
+    if (!configured)
+    {
+      Configuration cfg;
+      cfg.set("end_stop", 1);                         /* dynamics/cart_pole default (cart_pole.h:52) */
+      pd.configure(cfg); cpd.configure(cfg); cdpd.configure(cfg);
+      configured = true;
+    }
+    Dynamics *d = dyn == 0 ? (Dynamics *)&pd : dyn == 1 ? (Dynamics *)&cpd : (Dynamics *)&cdpd;
+    const int S = dyn == 0 ? 3 : dyn == 1 ? 5 : 7;
+    DynamicalModel model;
+    Configuration cfg;
+    cfg.set("dynamics", (void *)static_cast<Configurable *>(d));
+    cfg.set("control_step", control_step);
+    cfg.set("integration_steps", integration_steps);
+    model.configure(cfg);
+    Vector out;
+    const double tau = model.step(vec(state, S), VectorConstructor(actuation), &out);
+    for (size_t i = 0; i < out.size(); ++i) next[i] = out[i];
+    return tau;
+  }
+  catch (std::exception &e) { fprintf(stderr, "refag_model_step: %s\n", e.what()); return -1; }
 }
 
 }  /* extern "C" */

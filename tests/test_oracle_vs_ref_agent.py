@@ -33,7 +33,7 @@ def ref():
     dp = C.POINTER(C.c_double)
     L.refag_prepare.restype = None
     L.refag_create.restype = C.c_void_p
-    L.refag_create.argtypes = [C.POINTER(O.Config)]
+    L.refag_create.argtypes = [C.POINTER(O.Config), C.c_long]
     L.refag_destroy.argtypes = [C.c_void_p]
     L.refag_start.argtypes = [C.c_void_p, C.c_int, dp, dp]
     L.refag_step.argtypes = [C.c_void_p, C.c_int, dp, C.c_double, C.c_int, dp]
@@ -64,8 +64,7 @@ def _run_both(ref, cfg, seed, steps):
     L.orc_destroy(a)
 
     # 2. the reference's objects on the oracle's observations
-    L.orc_glibc_seed(seed)
-    h = ref.refag_create(C.byref(cfg))
+    h = ref.refag_create(C.byref(cfg), seed)        # srand48(seed) inside, at the point grld's construction starts
     assert h, "the reference's configure() threw"
     OBS = cfg.obs_dims
     act = C.c_double()
@@ -118,6 +117,29 @@ def test_pendulum_sarsa_small_table_collisions_and_accumulating_trace(ref):
     _run_both(ref, cfg, 3, 800)
 
 
+@pytest.mark.parametrize("safe,memory", [(1, 32768), (2, 32768), (2, 65536)])
+def test_collision_claim_table_equals_the_reference_sources(ref, safe, memory):
+    # projector/tile_coding safe = 1 | 2: the claim table of tile_coding.h:116-148 (linear probing; safe = 2 claims on reads too).
+    # The table must not fill up: the reference then probes forever (tile_coding.h:127-137 has no lap guard).
+    cfg = O.pendulum_config(memory=memory, test_interval=4, randomization=1.0, safe=safe)
+    _run_both(ref, cfg, 9, 2500)
+
+
+@pytest.mark.parametrize("algo,kw", [(O.ALGO_Q, {}), (O.ALGO_EXPECTED_SARSA, dict(target_epsilon=-1.0)),
+                                     (O.ALGO_EXPECTED_SARSA, dict(target_epsilon=0.1))])
+def test_q_learning_and_expected_sarsa_equal_the_reference_sources(ref, algo, kw):
+    # predictor/critic/q (advantage.cpp:71-110) and predictor/critic/expected_sarsa (sarsa.cpp:167-194; greedy or
+    # epsilon-greedy target policy)
+    cfg = O.pendulum_config(memory=65536, test_interval=5, randomization=1.0, algo=algo, **kw)
+    _run_both(ref, cfg, 4, 3000)
+
+
+def test_softmax_sampler_equals_the_reference_sources(ref):
+    # sampler/softmax as the learning policy's sampler (softmax.cpp:48-101, utils.h:227-240)
+    cfg = O.pendulum_config(memory=65536, test_interval=5, randomization=1.0, sampler=O.SAMPLER_SOFTMAX, softmax_tau=0.5)
+    _run_both(ref, cfg, 6, 3000)
+
+
 def test_cart_pole_sarsa_agent_equals_the_reference_sources(ref):
     # absorbing end-stops: Agent::end with an empty action (sarsa.cpp:104-109)
     cfg = O.cart_pole_config(memory=262144, test_interval=5, randomization=1.0)
@@ -141,8 +163,7 @@ def test_projector_alone_equals_the_reference_sources(ref):
     L = O.lib()
     cfg = O.pendulum_config(memory=65536)
     cfg.rng = O.RNG_GLIBC
-    L.orc_glibc_seed(11)
-    h = ref.refag_create(C.byref(cfg))
+    h = ref.refag_create(C.byref(cfg), 11)
     rng = np.random.default_rng(0)
     dims, T = cfg.obs_dims + 1, cfg.tilings
     res = (C.c_double * dims)(*[cfg.resolution[i] for i in range(dims)])
@@ -155,3 +176,27 @@ def test_projector_alone_equals_the_reference_sources(ref):
         assert ref.refag_project(h, 0, v, dims, got) == T
         assert list(got) == list(want), x
     ref.refag_destroy(h)
+
+
+@pytest.mark.parametrize("dyn,S,tau,umax", [(O.DYN_PENDULUM, 3, 0.03, 3.0), (O.DYN_CART_POLE, 5, 0.05, 15.0),
+                                            (O.DYN_CART_DOUBLE_POLE, 7, 0.05, 20.0)])
+def test_rk4_model_step_equals_the_reference_sources(ref, dyn, S, tau, umax):
+    # DynamicalModel::step (modeled.cpp:254-276) of the reference's own modeled.cpp around its own dynamics, against orc_rk4:
+    # same libm, same order of operations -> the same bits, for all three systems (the 7-state one has no golden vector)
+    L = O.lib()
+    dp = C.POINTER(C.c_double)
+    ref.refag_model_step.restype = C.c_double
+    ref.refag_model_step.argtypes = [C.c_int, C.c_double, C.c_int, dp, C.c_double, dp]
+    rng = np.random.default_rng(dyn)
+    worst = 0
+    for k in range(3000):
+        x = rng.normal(0, 1.5, S)
+        if dyn != O.DYN_PENDULUM:
+            x[0] = rng.uniform(-2.6, 2.6)           # both sides of the end stops at +-2.4
+        x[S - 1] = rng.uniform(0, 5)                # time
+        u = float(rng.uniform(-umax, umax))
+        xs = (C.c_double * S)(*x)
+        want, got = (C.c_double * S)(), (C.c_double * S)()
+        L.orc_rk4(dyn, tau, 5, xs, u, want)
+        assert ref.refag_model_step(dyn, tau, 5, xs, u, got) == tau
+        assert np.array_equal(_bits(list(got)), _bits(list(want))), (k, list(x), u, list(got), list(want))
