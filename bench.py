@@ -161,6 +161,57 @@ def cpu_oracle_rate(args, steps_per_proc, procs=None):
     return total / slowest, procs, wall
 
 
+REF_AGENT_LIB = os.path.join(ROOT, "oracle", "_ref", "libgrlref_agent.so")
+
+
+def _ref_sources_worker(wargs):
+    args, agent_id, n_steps = wargs
+    import _oracle as O
+    R = C.CDLL(REF_AGENT_LIB)
+    dp = C.POINTER(C.c_double)
+    R.refag_create.restype = C.c_void_p
+    R.refag_create.argtypes = [C.POINTER(O.Config), C.c_long]
+    R.refag_run.argtypes = [C.c_void_p, C.c_long, dp, dp]
+    R.refag_destroy.argtypes = [C.c_void_p]
+    R.refag_prepare()
+    cfg = make_config(O, args)
+    h = R.refag_create(C.byref(cfg), 1 + agent_id)
+    if not h:
+        return 0, 1.0
+    out, st = (C.c_double * 3)(), (C.c_double * 8)()
+    R.refag_run(h, 2000, out, st)
+    t0 = time.perf_counter()
+    R.refag_run(h, n_steps, out, st)
+    dt = time.perf_counter() - t0
+    R.refag_destroy(h)
+    return n_steps, dt
+
+
+def ref_sources_rate(args, seconds=3.0):
+    """The reference's OWN classes (tile coding, linear representation, traces, samplers, policies, predictors, agents, RK4
+    model, tasks) compiled from /root/reference against a stand-in Eigen (oracle/_ref/libgrlref_agent.so),
+    one closed loop per host core.  Reported next to the oracle port for information: the stand-in's vectors live on the heap
+    where Eigen's are in-place, so real grld is expected between this figure and the port's.  None where the library was not built."""
+    if not os.path.exists(REF_AGENT_LIB):
+        return None
+    try:
+        procs = os.cpu_count() or 1
+        with mp.get_context("fork").Pool(procs) as pool:
+            res = pool.map(_ref_sources_worker, [(args, i, 20000) for i in range(procs)])
+            per_proc = max(int(20000 / max(r[1] for r in res) * seconds), 5000)
+            res = pool.map(_ref_sources_worker, [(args, i, per_proc) for i in range(procs)])
+        total, slowest = sum(r[0] for r in res), max(r[1] for r in res)
+        if total == 0:
+            return None
+        return {"value": total / slowest, "unit": "agent-steps/s", "cores": procs,
+                "sample": "%d processes x %d agent-steps" % (procs, per_proc),
+                "what": "the reference's own agent / model / task classes compiled against a stand-in Eigen (heap vectors): "
+                        "real grld is expected between this figure and the oracle port's; per-agent sweep parameters not applied"}
+    except Exception as exc:           # information only: never fail the bench line over it
+        sys.stderr.write("bench: reference-sources timing skipped (%s)\n" % exc)
+        return None
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -182,7 +233,8 @@ def reference_arm(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * wall / max(args.steps, 1),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, max(args.gpus, 1)),
-        "cpu_baseline": {"value": value, "unit": "agent-steps/s", "cores": procs, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "agent-steps/s", "cores": procs, "kind": "port", "sample": sample,
+                         "reference_sources": ref_sources_rate(args)},
         "e2e": {"value": value, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "note": "reference grld cannot be built (needs Eigen 3, absent): the timed CPU implementation is the "
@@ -418,7 +470,8 @@ def ours(args):
             rate, procs, wall = cpu_oracle_rate(args, per_proc)
             line["cpu_baseline"] = {"value": rate, "unit": "agent-steps/s", "cores": procs, "kind": "port",
                                     "sample": "%d oracle processes (one per core) x %d agent-steps, memory=%d, %.1f s"
-                                              % (procs, per_proc, args.memory, wall)}
+                                              % (procs, per_proc, args.memory, wall),
+                                    "reference_sources": ref_sources_rate(args)}
         print(json.dumps(line), flush=True)
     batch.close()
     if world > 1:

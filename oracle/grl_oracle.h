@@ -45,8 +45,9 @@
  *       (pendulum, cart-pole; replacing / accumulating / no trace; test episodes; hash collisions) and for the actor-critic
  *       agent on all three dynamics; likewise Q-learning, expected SARSA, sampler/softmax, the safe = 1|2 claim table, and
  *       DynamicalModel::step of the reference's own modeled.cpp for the 3-, 5- and 7-state systems against orc_rk4
- *       (tests/test_oracle_vs_ref_agent.py).  That run corrected ac_step: the reference does not clear the critic's trace
- *       between episodes.
+ *       (tests/test_oracle_vs_ref_agent.py); and the closed loop of the reference's own tasks, model and agents (refag_run)
+ *       against orc_step free-running from the same seed: states, counters and tables the same bits.  That run corrected
+ *       ac_step: the reference does not clear the critic's trace between episodes.
  * PARITY UNPINNED: the summation order inside Eigen's Matrix3d::inverse() and 3x3 products (cart-double-pole; the
  * stand-in shares the oracle's assumption); the sequencing of ModeledEnvironment::step and of the experiment loop of
  * online_learning.cpp is pinned only through (a) and (b).

@@ -90,7 +90,15 @@ struct RefAgent
   /* agents */
   TDAgent agent;
   FixedAgent test_agent;
-  RefAgent() : trace(NULL) { }
+  /* environment pieces for the closed loop (refag_run) */
+  PendulumDynamics pd; CartPoleDynamics cpd; CartDoublePoleDynamics cdpd;
+  PendulumSwingupTask pt; CartPoleSwingupTask cpt; CartDoublePoleBalancingTask cdpt;
+  DynamicalModel model;
+  Task *task;
+  Vector state;
+  bool in_episode; int test; uint64_t tt, ss; double total_reward;
+  Action action;
+  RefAgent() : trace(NULL), task(NULL), in_episode(false), test(0), tt(0), ss(0), total_reward(0) { }
   ~RefAgent() { delete trace; }
 };
 
@@ -382,6 +390,72 @@ int refag_project(void *h, int actor, const double *in, int dims, uint32_t *inde
   if (!ip) return -1;
   for (size_t i = 0; i < ip->indices.size(); ++i) index[i] = (uint32_t)ip->indices[i];
   return (int)ip->indices.size();
+}
+
+/* Closed loop over the reference's own pieces: task start / actuate / observe / evaluate (environments/*.cpp),
+ * DynamicalModel::step (modeled.cpp:254-276) and the agents above.  What is RESTATED here, because ModeledEnvironment and
+ * OnlineLearningExperiment read their configuration through the YAML-side configurator tree: the order of calls inside
+ * ModeledEnvironment::start / step (modeled.cpp:132-213: actuate, model step, observe, evaluate; discrete_time = 1 -> tau 1)
+ * and the episode loop of online_learning.cpp:154-222 (test episode every test_interval + 1 trials; terminal == 2 ->
+ * Agent::end, else Agent::step).  Runs n_steps agent-steps (test steps included), as orc_run_total does.
+ * out[0] = learning steps, out[1] = trials, out[2] = return of the last finished episode; state_out = the environment state. */
+int refag_run(void *h, long n_steps, double *out, double *state_out)
+{
+  RefAgent *a = (RefAgent *)h;
+  const orc_config &c = a->c;
+  try
+  {
+    if (!a->task)
+    {
+      Configuration cfg;
+      cfg.set("timeout", c.timeout); cfg.set("randomization", c.randomization);
+      cfg.set("end_stop", 1);
+      cfg.set("shaping", 0); cfg.set("gamma", 1.0); cfg.set("action_penalty", 0); cfg.set("end_stop_penalty", c.end_stop_penalty);
+      cfg.set("wrap_angle", 1);
+      Dynamics *d;
+      if (c.dynamics == ORC_DYN_PENDULUM) { a->pd.configure(cfg); a->pt.configure(cfg); d = &a->pd; a->task = &a->pt; }
+      else if (c.dynamics == ORC_DYN_CART_POLE) { a->cpd.configure(cfg); a->cpt.configure(cfg); d = &a->cpd; a->task = &a->cpt; }
+      else { a->cdpd.configure(cfg); a->cdpt.configure(cfg); d = &a->cdpd; a->task = &a->cdpt; }
+      Configuration mc;
+      mc.set("dynamics", (void *)static_cast<Configurable *>(d));
+      mc.set("control_step", c.control_step);
+      mc.set("integration_steps", c.integration_steps);
+      a->model.configure(mc);
+    }
+    double last_return = 0;
+    for (long k = 0; k < n_steps; ++k)
+    {
+      if (!a->in_episode)
+      {
+        a->test = c.test_interval >= 0 && a->tt % (uint64_t)(c.test_interval + 1) == (uint64_t)c.test_interval;
+        int terminal;
+        a->task->start(a->test, &a->state);
+        Observation obs;
+        a->task->observe(a->state, &obs, &terminal);
+        if (a->test) a->test_agent.start(obs, &a->action); else a->agent.start(obs, &a->action);
+        a->total_reward = 0;
+        a->in_episode = true;
+      }
+      Agent *ag = a->test ? (Agent *)&a->test_agent : (Agent *)&a->agent;
+      Vector next, actuation;
+      int terminal;
+      double reward;
+      a->task->actuate(a->state, a->state, a->action, &actuation);
+      a->model.step(a->state, actuation, &next);
+      Observation obs;
+      a->task->observe(next, &obs, &terminal);
+      a->task->evaluate(a->state, a->action, next, &reward);
+      a->state = next;
+      a->total_reward += reward;
+      if (terminal == 2) ag->end(1., obs, reward); else ag->step(1., obs, reward, &a->action);
+      if (!a->test) a->ss++;
+      if (terminal) { a->in_episode = false; a->tt++; last_return = a->total_reward; }
+    }
+    out[0] = (double)a->ss; out[1] = (double)a->tt; out[2] = last_return;
+    for (size_t i = 0; i < a->state.size(); ++i) state_out[i] = a->state[i];
+    return 0;
+  }
+  catch (std::exception &e) { fprintf(stderr, "refag_run: %s\n", e.what()); return 1; }
 }
 
 /* DynamicalModel::step (modeled.cpp:254-276: RK4 over the dynamics' eom) of the reference's own modeled.cpp around its own

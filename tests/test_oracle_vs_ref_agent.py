@@ -200,3 +200,48 @@ def test_rk4_model_step_equals_the_reference_sources(ref, dyn, S, tau, umax):
         L.orc_rk4(dyn, tau, 5, xs, u, want)
         assert ref.refag_model_step(dyn, tau, 5, xs, u, got) == tau
         assert np.array_equal(_bits(list(got)), _bits(list(want))), (k, list(x), u, list(got), list(want))
+
+
+@pytest.mark.parametrize("name,steps", [("pendulum_config", 6000), ("cart_pole_config", 6000), ("cart_double_pole_config", 4000),
+                                        ("cart_double_pole_ac_config", 6000), ("pendulum_ac_config", 4000),
+                                        ("cart_pole_ac_config", 4000)])
+def test_closed_loop_of_reference_pieces_equals_the_free_running_oracle(ref, name, steps):
+    # The whole loop with nothing fed: the reference's own task (start / actuate / observe / evaluate), its own
+    # DynamicalModel::step and its own agents in a closed loop (refag_run; only the call order of ModeledEnvironment::step and of
+    # the experiment's episode loop is restated in the harness) against orc_step free-running in glibc RNG mode from the same
+    # seed.  Same libm on both sides: environment states, counters and weight tables must be the same bits.
+    L = O.lib()
+    cfg = getattr(O, name)(test_interval=6, randomization=1.0)
+    cfg.rng = O.RNG_GLIBC
+    ac = cfg.algo == O.ALGO_AC
+    seed = 21
+    L.orc_glibc_seed(seed)
+    a = L.orc_create(C.byref(cfg), 0)
+    for _ in range(steps):
+        L.orc_step(a, None)
+    n_steps, n_eps = C.c_uint64(), C.c_uint64()
+    L.orc_stats(a, C.byref(n_steps), C.byref(n_eps), None, None, None)
+    state = (C.c_double * O.MAX_STATE)()
+    L.orc_get_state.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_void_p, C.c_void_p, C.c_void_p]
+    L.orc_get_state(a, state, None, None, None)
+    table = np.ctypeslib.as_array(L.orc_table(a), shape=(cfg.memory,)).copy()
+    actor = np.ctypeslib.as_array(L.orc_actor_table(a), shape=(cfg.memory,)).copy() if ac else None
+    L.orc_destroy(a)
+
+    dp = C.POINTER(C.c_double)
+    ref.refag_run.argtypes = [C.c_void_p, C.c_long, dp, dp]
+    h = ref.refag_create(C.byref(cfg), seed)
+    assert h
+    out, st = (C.c_double * 3)(), (C.c_double * O.MAX_STATE)()
+    assert ref.refag_run(h, steps, out, st) == 0
+    S = L.orc_state_dims(cfg.dynamics)
+    assert int(out[0]) == n_steps.value and int(out[1]) == n_eps.value, (list(out), n_steps.value, n_eps.value)
+    assert np.array_equal(_bits(list(st)[:S]), _bits(list(state)[:S])), (list(st)[:S], list(state)[:S])
+    got = np.empty(cfg.memory)
+    ref.refag_table(h, 0, got.ctypes.data_as(dp))
+    assert np.array_equal(_bits(got), _bits(table)), int((_bits(got) != _bits(table)).sum())
+    if ac:
+        ref.refag_table(h, 1, got.ctypes.data_as(dp))
+        assert np.array_equal(_bits(got), _bits(actor))
+    assert n_eps.value >= 5
+    ref.refag_destroy(h)
