@@ -197,9 +197,10 @@ def ref_sources_rate(args, seconds=3.0):
     try:
         procs = os.cpu_count() or 1
         with mp.get_context("fork").Pool(procs) as pool:
-            res = pool.map(_ref_sources_worker, [(args, i, 20000) for i in range(procs)])
+            # (bounded waits: a worker that died would otherwise leave map() waiting for ever)
+            res = pool.map_async(_ref_sources_worker, [(args, i, 20000) for i in range(procs)]).get(timeout=60)
             per_proc = max(int(20000 / max(r[1] for r in res) * seconds), 5000)
-            res = pool.map(_ref_sources_worker, [(args, i, per_proc) for i in range(procs)])
+            res = pool.map_async(_ref_sources_worker, [(args, i, per_proc) for i in range(procs)]).get(timeout=60 + 10 * seconds)
         total, slowest = sum(r[0] for r in res), max(r[1] for r in res)
         if total == 0:
             return None
