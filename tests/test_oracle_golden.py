@@ -36,3 +36,47 @@ def test_pendulum_sarsa_tc_golden_curve(orc):
     finally:
         orc.orc_destroy(a)
     assert rows == [tuple(g) for g in golden]
+
+
+REF_CLASSES = os.path.join(os.path.dirname(__file__), "golden", "ref_classes_closed_loop.json")
+
+
+def _ref_class_cases():
+    import json
+    with open(REF_CLASSES) as f:
+        return json.load(f)["cases"]
+
+
+import pytest  # noqa: E402
+
+
+@pytest.mark.parametrize("case", _ref_class_cases(), ids=lambda c: c["name"])
+def test_oracle_reproduces_reference_class_vectors(orc, case):
+    """tests/golden/ref_classes_closed_loop.json was written by tools/make_ref_agent_golden.py from a closed loop of the
+    reference's OWN task / model / agent classes (compiled from /root/reference against a stand-in Eigen).
+    The oracle in glibc-RNG mode, from the same srand48 seed, must arrive at the same step and trial counts, the same
+    environment state bits and the same weight tables (SHA-256 of their bytes) -- on any machine, with no reference around."""
+    import hashlib
+    import numpy as np
+    cfg = getattr(O, case["config"])(**case["overrides"])
+    cfg.rng = O.RNG_GLIBC
+    orc.orc_glibc_seed(case["seed"])
+    a = orc.orc_create(C.byref(cfg), 0)
+    try:
+        for _ in range(case["steps"]):
+            orc.orc_step(a, None)
+        n_steps, n_eps = C.c_uint64(), C.c_uint64()
+        orc.orc_stats(a, C.byref(n_steps), C.byref(n_eps), None, None, None)
+        assert (n_steps.value, n_eps.value) == (case["learning_steps"], case["trials"])
+        state = (C.c_double * O.MAX_STATE)()
+        orc.orc_get_state.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_void_p, C.c_void_p, C.c_void_p]
+        orc.orc_get_state(a, state, None, None, None)
+        S = orc.orc_state_dims(cfg.dynamics)
+        assert ["%016x" % b for b in np.array(list(state)[:S]).view(np.uint64)] == case["state_bits"]
+        tab = np.ctypeslib.as_array(orc.orc_table(a), shape=(cfg.memory,))
+        assert hashlib.sha256(tab.tobytes()).hexdigest() == case["table_sha256"]
+        if "actor_table_sha256" in case:
+            act = np.ctypeslib.as_array(orc.orc_actor_table(a), shape=(cfg.memory,))
+            assert hashlib.sha256(act.tobytes()).hexdigest() == case["actor_table_sha256"]
+    finally:
+        orc.orc_destroy(a)
