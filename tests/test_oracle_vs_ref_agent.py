@@ -245,3 +245,11 @@ def test_closed_loop_of_reference_pieces_equals_the_free_running_oracle(ref, nam
         assert np.array_equal(_bits(got), _bits(actor))
     assert n_eps.value >= 5
     ref.refag_destroy(h)
+
+
+@pytest.mark.parametrize("lam,alpha,eps", [(0.0, 0.4, 0.1), (0.2, 0.05, 0.01), (0.9, 0.1, 0.02), (0.75, 0.2, 0.05)])
+def test_sweep_corner_hyperparameters_equal_the_reference_sources(ref, lam, alpha, eps):
+    # BASELINE's configs[4] sweeps alpha x lambda x epsilon: lambda = 0 makes the trace's decay 0 < 0.01, i.e. clear() and a
+    # one-entry trace swept with e = 0 (trace.h:220-226); lambda = 0.9 is the longest ring (gamma*lambda = 0.873, 34 entries)
+    cfg = O.pendulum_config(memory=32768, test_interval=-1, randomization=1.0, lambda_=lam, alpha=alpha, epsilon=eps)
+    _run_both(ref, cfg, 12, 3000)
