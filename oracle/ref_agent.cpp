@@ -1,6 +1,6 @@
 /* oracle/ref_agent.cpp -- harness around the reference's OWN agent-side classes.  TEST INFRASTRUCTURE ONLY.
  *
- * oracle/Makefile (target `ref_agent`) compiles, from where they lie under /root/reference/base/src,
+ * oracle/Makefile (target `ref`) compiles, from where they lie under /root/reference/base/src,
  *   projectors/tile_coding.cpp  representations/linear.cpp  traces/enumerated.cpp  discretizers/uniform.cpp
  *   samplers/greedy.cpp  policies/q.cpp  policies/action.cpp  predictor.cpp  predictors/sarsa.cpp  predictors/td.cpp
  *   predictors/ac.cpp  agents/td.cpp  agents/fixed.cpp  environments/modeled.cpp  environments/{pendulum,cart_pole,cart_double_pole}.cpp
