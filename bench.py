@@ -161,55 +161,68 @@ def cpu_oracle_rate(args, steps_per_proc, procs=None):
     return total / slowest, procs, wall
 
 
-REF_AGENT_LIB = os.path.join(ROOT, "oracle", "_ref", "libgrlref_agent.so")
+GRLD_REF = os.path.join(ROOT, "oracle", "_ref", "grld_ref")
 
 
-def _ref_sources_worker(wargs):
-    args, agent_id, n_steps = wargs
+def _grld_batch(args, procs, trials, top, limit=300.0):
+    """`procs` concurrent `grld_ref -s <1+i> cfg.yaml` processes, each in its own directory (one grld per host
+    core, test_interval -1).  Returns (learning steps done by all, wall seconds from the first launch to the last exit)."""
     import _oracle as O
-    R = C.CDLL(REF_AGENT_LIB)
-    dp = C.POINTER(C.c_double)
-    R.refag_create.restype = C.c_void_p
-    R.refag_create.argtypes = [C.POINTER(O.Config), C.c_long]
-    R.refag_run.argtypes = [C.c_void_p, C.c_long, dp, dp]
-    R.refag_destroy.argtypes = [C.c_void_p]
-    R.refag_prepare()
-    cfg = make_config(O, args)
-    h = R.refag_create(C.byref(cfg), 1 + agent_id)
-    if not h:
-        return 0, 1.0
-    out, st = (C.c_double * 3)(), (C.c_double * 8)()
-    R.refag_run(h, 2000, out, st)
+    runs = []
+    for i in range(procs):
+        d = os.path.join(top, "p%d_%d" % (i, trials))
+        os.makedirs(d, exist_ok=True)
+        cfg = make_config(O, args)
+        if args.workload == "sweep":
+            al, la, ep = sweep_hyper(i * 32, 1)                # block i: lambda cycles through the grid
+            cfg.alpha, cfg.lambda_, cfg.epsilon = float(al[0]), float(la[0]), float(ep[0])
+        with open(os.path.join(d, "cfg.yaml"), "w") as f:
+            f.write(O.grld_yaml(cfg, trials, "curve"))
+        runs.append(d)
     t0 = time.perf_counter()
-    R.refag_run(h, n_steps, out, st)
-    dt = time.perf_counter() - t0
-    R.refag_destroy(h)
-    return n_steps, dt
+    ps = [subprocess.Popen([GRLD_REF, "-s", str(1 + i), "cfg.yaml"], cwd=d, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+          for i, d in enumerate(runs)]
+    try:
+        for p in ps:
+            if p.wait(timeout=max(limit - (time.perf_counter() - t0), 1.0)) != 0:
+                raise RuntimeError("grld_ref exited with %d" % p.returncode)
+    finally:
+        for p in ps:
+            if p.poll() is None:
+                p.kill()
+    wall = time.perf_counter() - t0
+    steps = 0
+    for d in runs:
+        rows = [ln.split() for ln in open(os.path.join(d, "curve-0.txt")) if ln.strip()]
+        steps += int(rows[-1][1])                              # column 2: learning steps so far (online_learning.cpp:252)
+    return steps, wall
 
 
-def ref_sources_rate(args, seconds=3.0):
-    """The reference's OWN classes (tile coding, linear representation, traces, samplers, policies, predictors, agents, RK4
-    model, tasks) compiled from /root/reference against a stand-in Eigen (oracle/_ref/libgrlref_agent.so),
-    one closed loop per host core.  Reported next to the oracle port for information: the stand-in's vectors live on the heap
-    where Eigen's are in-place, so real grld is expected between this figure and the port's.  None where the library was not built."""
-    if not os.path.exists(REF_AGENT_LIB):
+def grld_rate(args, seconds):
+    """The reference's OWN deployer -- oracle/_ref/grld_ref: grld built from the reference's translation units with its own
+    headers, flags and vendored yaml-cpp, Eigen being a stand-in -- one process per host core on the
+    workload's configuration, about `seconds` of work.  None where the binary is absent or does not run."""
+    if not os.path.exists(GRLD_REF):
         return None
+    import tempfile
     try:
         procs = os.cpu_count() or 1
-        with mp.get_context("fork").Pool(procs) as pool:
-            # (bounded waits: a worker that died would otherwise leave map() waiting for ever)
-            res = pool.map_async(_ref_sources_worker, [(args, i, 20000) for i in range(procs)]).get(timeout=60)
-            per_proc = max(int(20000 / max(r[1] for r in res) * seconds), 5000)
-            res = pool.map_async(_ref_sources_worker, [(args, i, per_proc) for i in range(procs)]).get(timeout=60 + 10 * seconds)
-        total, slowest = sum(r[0] for r in res), max(r[1] for r in res)
-        if total == 0:
-            return None
-        return {"value": total / slowest, "unit": "agent-steps/s", "cores": procs,
-                "sample": "%d processes x %d agent-steps" % (procs, per_proc),
-                "what": "the reference's own agent / model / task classes compiled against a stand-in Eigen (heap vectors): "
-                        "real grld is expected between this figure and the oracle port's; per-agent sweep parameters not applied"}
-    except Exception as exc:           # information only: never fail the bench line over it
-        sys.stderr.write("bench: reference-sources timing skipped (%s)\n" % exc)
+        with tempfile.TemporaryDirectory() as top:
+            # two short runs separate the start-up (YAML, instantiation, table initialisation) from the per-step cost
+            s0, w0 = _grld_batch(args, procs, 100, top, limit=60.0)
+            s1, w1 = _grld_batch(args, procs, 600, top, limit=120.0)
+            # (never trust a difference of two noisy wall times alone: bounded below by a quarter of the plain average)
+            per_trial = max((w1 - w0) / 500.0, w1 / 600.0 / 4.0, 1e-6)
+            trials = max(int(seconds / per_trial), 1000)
+            steps, wall = _grld_batch(args, procs, trials, top, limit=30.0 + 20.0 * seconds)
+        value = (steps - s1) / max(wall - w1, 1e-6)                # differential against the (warm) 600-trial run: start-up excluded
+        return {"value": value, "unit": "agent-steps/s", "cores": procs, "kind": "reference",
+                "sample": "%d grld_ref processes (one per core, -s 1..%d) x %d trials = %d agent-steps in %.1f s, rate taken as the "
+                          "difference to a 600-trial run of the same processes (%d agent-steps in %.2f s) so that start-up does not "
+                          "count; memory=%d, test_interval -1; grld built from the reference's own sources, Eigen replaced by a "
+                          "stand-in with the same in-place storage" % (procs, procs, trials, steps, wall, s1, w1, args.memory)}
+    except Exception as exc:
+        sys.stderr.write("bench: grld_ref not usable (%s); the oracle port is timed instead\n" % exc)
         return None
 
 
@@ -217,29 +230,53 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    # size the sample so K+W steps finish within a few minutes: calibrate with a short run
+    # the reference's own deployer where it was built (oracle/_ref/grld_ref), one process per core; else the oracle port
+    samples, t0 = [], time.perf_counter()
+    for k in range(args.warmup + args.steps):
+        if k == args.warmup:
+            t0 = time.perf_counter()
+        r = grld_rate(args, 4.0)                                # ~4 s of CPU work per bench step (+ two short sizing runs)
+        if r is None:
+            samples = None
+            break
+        if k >= args.warmup:
+            samples.append(r)
+    ref_wall = time.perf_counter() - t0
+    # the port, always: the other end of the bracket (no per-step heap traffic)
     rate0, procs, _ = cpu_oracle_rate(args, 50000)
-    per_proc = max(int(rate0 / procs * 4.0), 10000)           # ~4 s of CPU work per step
-    for _ in range(args.warmup):
-        cpu_oracle_rate(args, per_proc // 4)
-    rates, t0 = [], time.perf_counter()
-    for _ in range(args.steps):
-        r, procs, _ = cpu_oracle_rate(args, per_proc)
-        rates.append(r)
-    wall = time.perf_counter() - t0
-    value = sum(rates) / len(rates)
-    sample = "%d oracle processes x %d agent-steps per bench step, memory=%d" % (procs, per_proc, args.memory)
+    per_proc = max(int(rate0 / procs * 4.0), 10000)
+    if samples:
+        port_rate, procs, _ = cpu_oracle_rate(args, per_proc)
+        wall = ref_wall
+        value = sum(x["value"] for x in samples) / len(samples)
+        baseline = dict(samples[-1], value=value,
+                        port={"value": port_rate, "unit": "agent-steps/s", "cores": procs,
+                              "sample": "%d oracle processes x %d agent-steps, memory=%d" % (procs, per_proc, args.memory)})
+        note = ("the timed CPU implementation is the reference's own deployer built from its own sources (oracle/_ref/grld_ref; "
+                "the one stand-in is Eigen, absent here), whose learning curves the oracle reproduces "
+                "(tests/test_oracle_vs_grld_ref.py); cpu_baseline.port is the oracle port on the same cores")
+    else:
+        for _ in range(args.warmup):
+            cpu_oracle_rate(args, per_proc // 4)
+        rates, t0 = [], time.perf_counter()
+        for _ in range(args.steps):
+            r, procs, _ = cpu_oracle_rate(args, per_proc)
+            rates.append(r)
+        wall = time.perf_counter() - t0
+        value = sum(rates) / len(rates)
+        baseline = {"value": value, "unit": "agent-steps/s", "cores": procs, "kind": "port",
+                    "sample": "%d oracle processes x %d agent-steps per bench step, memory=%d" % (procs, per_proc, args.memory)}
+        note = ("oracle/_ref/grld_ref is not here (it is built where /root/reference exists): the timed CPU implementation is "
+                "the oracle port, pinned to the reference's golden curve (tests/test_oracle_golden.py)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "agent-steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * wall / max(args.steps, 1),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, max(args.gpus, 1)),
-        "cpu_baseline": {"value": value, "unit": "agent-steps/s", "cores": procs, "kind": "port", "sample": sample,
-                         "reference_sources": ref_sources_rate(args)},
+        "cpu_baseline": baseline,
         "e2e": {"value": value, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-        "note": "reference grld cannot be built (needs Eigen 3, absent): the timed CPU implementation is the "
-                "oracle port, pinned to the reference's golden curve (tests/test_oracle_golden.py)",
+        "note": note,
     }
     print(json.dumps(line), flush=True)
 
@@ -469,10 +506,11 @@ def ours(args):
             rate0, procs, _ = cpu_oracle_rate(args, 50000)
             per_proc = max(int(rate0 / procs * 12.0), 10000)
             rate, procs, wall = cpu_oracle_rate(args, per_proc)
-            line["cpu_baseline"] = {"value": rate, "unit": "agent-steps/s", "cores": procs, "kind": "port",
-                                    "sample": "%d oracle processes (one per core) x %d agent-steps, memory=%d, %.1f s"
-                                              % (procs, per_proc, args.memory, wall),
-                                    "reference_sources": ref_sources_rate(args)}
+            port = {"value": rate, "unit": "agent-steps/s", "cores": procs, "kind": "port",
+                    "sample": "%d oracle processes (one per core) x %d agent-steps, memory=%d, %.1f s"
+                              % (procs, per_proc, args.memory, wall)}
+            ref = grld_rate(args, 10.0)                         # the reference's own deployer, where it was built
+            line["cpu_baseline"] = dict(ref, port=port) if ref else port
         print(json.dumps(line), flush=True)
     batch.close()
     if world > 1:

@@ -28,8 +28,8 @@
  *   src/agents/td.cpp:50-81, src/agents/fixed.cpp:48-62
  *   src/experiments/online_learning.cpp:154-222
  *
- * PARITY PIN STATUS (details: DESIGN.md section 3).  The reference as a whole cannot be compiled in the authoring
- * container (it needs Eigen 3, neither vendored nor installed).  The oracle is pinned by
+ * PARITY PIN STATUS (details: DESIGN.md section 3).  The reference needs Eigen 3, which is neither vendored nor installed in
+ * the authoring container; everything else of it compiles there against a stand-in Eigen.  The oracle is pinned by
  *   (a) the reference's seeded learning curve tests/template/pendulum-sarsa-tc-0.txt, all 181 rows
  *       (tests/test_oracle_golden.py): RK4, pendulum task, hash, Q read, samplers, SARSA(lambda) write, replacing trace;
  *   (b) the reference's tests/template/cart_pole_balancing-pid-0.txt, all 10 rows (grl_oracle_pin.c,
@@ -48,9 +48,11 @@
  *       (tests/test_oracle_vs_ref_agent.py); and the closed loop of the reference's own tasks, model and agents (refag_run)
  *       against orc_step free-running from the same seed: states, counters and tables the same bits.  That run corrected
  *       ac_step: the reference does not clear the critic's trace between episodes.
+ *   (f) grld itself built from the reference's translation units (deployer, YAML configurator, experiment loop, modeled
+ *       environment, ...; vendored yaml-cpp; stand-in Eigen) into oracle/_ref/grld_ref: it writes the reference's golden curve
+ *       of (a), and the rows it writes for 12 configurations equal this oracle's (tests/test_oracle_vs_grld_ref.py).
  * PARITY UNPINNED: the summation order inside Eigen's Matrix3d::inverse() and 3x3 products (cart-double-pole; the
- * stand-in shares the oracle's assumption); the sequencing of ModeledEnvironment::step and of the experiment loop of
- * online_learning.cpp is pinned only through (a) and (b).
+ * stand-in shares the oracle's assumption).  Nothing else.
  */
 #ifndef GRL_ORACLE_H_
 #define GRL_ORACLE_H_

@@ -47,17 +47,12 @@ def test_byte_model_matches_survey_8d():
     assert bench.table_bytes_per_step("cart_double_pole_ac", 5.0) == 848
 
 
-def test_reference_sources_rate_is_reported_where_the_library_exists():
-    # information next to cpu_baseline: the reference's own classes in a closed loop (oracle/_ref/libgrlref_agent.so)
+def test_reference_deployer_rate_where_it_was_built():
+    # bench.py --impl reference / cpu_baseline time oracle/_ref/grld_ref (the reference's own deployer) where it exists
     import argparse
-    if not os.path.exists(bench.REF_AGENT_LIB):
-        assert bench.ref_sources_rate(None) is None
-        return
     args = argparse.Namespace(workload="pendulum", agents=4, memory=65536, cohort=0)
-    try:
-        import _oracle as O
-        bench.make_config(O, args)
-    except Exception as exc:                       # make_config wants more fields than this test knows about
-        pytest.skip("bench.make_config signature changed: %s" % exc)
-    r = bench.ref_sources_rate(args, seconds=0.2)
-    assert r and r["value"] > 1e3 and r["cores"] >= 1
+    if not os.path.exists(bench.GRLD_REF):
+        assert bench.grld_rate(args, 0.2) is None
+        return
+    r = bench.grld_rate(args, 0.3)
+    assert r and r["kind"] == "reference" and r["value"] > 1e3 and r["cores"] >= 1

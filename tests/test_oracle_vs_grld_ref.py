@@ -23,159 +23,7 @@ GRLD = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "grld_ref")
 pytestmark = pytest.mark.skipif(not os.path.exists(GRLD),
                                 reason="oracle/_ref/grld_ref is built where /root/reference exists (make -C oracle ref)")
 
-DYN = {O.DYN_PENDULUM: ("dynamics/pendulum", "task/pendulum/swingup"),
-       O.DYN_CART_POLE: ("dynamics/cart_pole", "task/cart_pole/swingup"),
-       O.DYN_CART_DOUBLE_POLE: ("dynamics/cart_double_pole", "task/cart_double_pole/balancing")}
-
-
-def _vec(a, n):
-    return "[" + ", ".join(repr(float(a[i])) for i in range(n)) + "]"
-
-
-def _environment(c):
-    dyn, task = DYN[c.dynamics]
-    extra = ""
-    if c.dynamics == O.DYN_CART_POLE:
-        extra = ", end_stop_penalty: %d" % c.end_stop_penalty
-    # (task/cart_pole/swingup declares `randomization` as an integer, task/pendulum/swingup as a real number)
-    rand = "" if c.dynamics == O.DYN_CART_DOUBLE_POLE and c.randomization == 0 else ", randomization: %s" % (
-        "%d" % int(c.randomization) if c.dynamics == O.DYN_CART_POLE else repr(c.randomization))
-    return """  environment:
-    type: environment/modeled
-    model:
-      type: model/dynamical
-      control_step: %r
-      integration_steps: %d
-      dynamics: {type: %s}
-    task: {type: %s, timeout: %r%s%s}
-""" % (c.control_step, c.integration_steps, dyn, task, c.timeout, rand, extra)
-
-
-def _trace(c):
-    return {O.TRACE_REPLACING: "{type: trace/enumerated/replacing}", O.TRACE_ACCUMULATING: "{type: trace/enumerated/accumulating}",
-            O.TRACE_NONE: "0"}[c.trace]
-
-
-def yaml_for(c, trials, output):
-    """A configuration file of the shape of the reference's cfg/pendulum/sarsa_tc.yaml / cfg/cart_double_pole/ac.yaml
-    (visualisation left out), generated from the oracle's configuration so that both sides always run the same thing."""
-    head = """experiment:
-  type: experiment/online_learning
-  runs: 1
-  trials: %d
-  steps: 0
-  rate: 0
-  test_interval: %d
-  output: %s
-%s""" % (trials, c.test_interval, output, _environment(c))
-    if c.algo == O.ALGO_AC:
-        n = c.obs_dims
-        return head + """  agent:
-    type: agent/td
-    policy:
-      type: mapping/policy/action
-      sigma: [%r]
-      output_min: experiment/environment/task/action_min
-      output_max: experiment/environment/task/action_max
-      projector:
-        type: projector/tile_coding
-        tilings: %d
-        memory: %d
-        safe: 0
-        resolution: %s
-        wrapping: %s
-      representation:
-        type: representation/parameterized/linear
-        init_min: [%r]
-        init_max: [%r]
-        memory: experiment/agent/policy/projector/memory
-        outputs: experiment/environment/task/action_dims
-        output_min: experiment/environment/task/action_min
-        output_max: experiment/environment/task/action_max
-    predictor:
-      type: predictor/ac/action
-      alpha: %r
-      update_method: proportional
-      step_limit: []
-      critic:
-        type: predictor/critic/td
-        alpha: %r
-        gamma: %r
-        lambda: %r
-        projector: {type: projector/tile_coding, tilings: %d, memory: %d, safe: 0, resolution: %s, wrapping: %s}
-        representation:
-          type: representation/parameterized/linear
-          init_min: [%r]
-          init_max: [%r]
-          memory: experiment/agent/predictor/critic/projector/memory
-          outputs: 1
-          output_min: []
-          output_max: []
-        trace: %s
-      projector: experiment/agent/policy/projector
-      representation: experiment/agent/policy/representation
-  test_agent:
-    type: agent/fixed
-    policy:
-      type: mapping/policy/action
-      sigma: []
-      output_min: experiment/environment/task/action_min
-      output_max: experiment/environment/task/action_max
-      projector: experiment/agent/policy/projector
-      representation: experiment/agent/policy/representation
-  save_every: never
-""" % (c.sigma, c.tilings, c.memory, _vec(c.actor_resolution, n), _vec(c.actor_wrapping, n), c.init_min, c.init_max,
-       c.actor_alpha, c.alpha, c.gamma, c.lambda_, c.tilings, c.memory, _vec(c.resolution, n), _vec(c.wrapping, n),
-       c.init_min, c.init_max, _trace(c))
-    n = c.obs_dims + 1
-    sampler = ("{type: sampler/softmax, tau: %r}" % c.softmax_tau if c.sampler == O.SAMPLER_SOFTMAX
-               else "{type: sampler/epsilon_greedy, epsilon: %r}" % c.epsilon)
-    predictor = {O.ALGO_SARSA: "predictor/critic/sarsa", O.ALGO_Q: "predictor/critic/q"}[c.algo]
-    extra = "      discretizer: experiment/agent/policy/discretizer\n" if c.algo == O.ALGO_Q else ""
-    return head + """  agent:
-    type: agent/td
-    policy:
-      type: mapping/policy/discrete/value/q
-      discretizer:
-        type: discretizer/uniform
-        min: experiment/environment/task/action_min
-        max: experiment/environment/task/action_max
-        steps: [%d]
-      projector:
-        type: projector/tile_coding
-        tilings: %d
-        memory: %d
-        safe: %d
-        resolution: %s
-        wrapping: %s
-      representation:
-        type: representation/parameterized/linear
-        init_min: [%r]
-        init_max: [%r]
-        memory: experiment/agent/policy/projector/memory
-        outputs: 1
-        output_min: []
-        output_max: []
-      sampler: %s
-    predictor:
-      type: %s
-      alpha: %r
-      gamma: %r
-      lambda: %r
-%s      projector: experiment/agent/policy/projector
-      representation: experiment/agent/policy/representation
-      trace: %s
-  test_agent:
-    type: agent/fixed
-    policy:
-      type: mapping/policy/discrete/value/q
-      discretizer: experiment/agent/policy/discretizer
-      projector: experiment/agent/policy/projector
-      representation: experiment/agent/policy/representation
-      sampler: {type: sampler/greedy}
-  save_every: never
-""" % (c.n_actions, c.tilings, c.memory, c.safe, _vec(c.resolution, n), _vec(c.wrapping, n), c.init_min, c.init_max,
-       sampler, predictor, c.alpha, c.gamma, c.lambda_, extra, _trace(c))
+yaml_for = O.grld_yaml
 
 
 def oracle_rows(orc, c, seed, trials):
