@@ -80,3 +80,26 @@ def test_oracle_reproduces_reference_class_vectors(orc, case):
             assert hashlib.sha256(act.tobytes()).hexdigest() == case["actor_table_sha256"]
     finally:
         orc.orc_destroy(a)
+
+
+GRLD_CURVES = os.path.join(os.path.dirname(__file__), "golden", "grld_ref_curves.json")
+
+
+def _grld_curve_cases():
+    import json
+    with open(GRLD_CURVES) as f:
+        return json.load(f)["cases"]
+
+
+@pytest.mark.parametrize("case", _grld_curve_cases(), ids=lambda c: c["name"])
+def test_oracle_reproduces_reference_deployer_curves(orc, case):
+    """tests/golden/grld_ref_curves.json holds the rows the reference's OWN deployer wrote (oracle/_ref/grld_ref: grld built from
+    the reference's translation units; generator: tools/make_grld_ref_golden.py).  The oracle in glibc-RNG mode
+    from the same seed must write the same rows: trial, learning steps so far, return to the 3 decimals printed, episode time."""
+    from test_oracle_vs_grld_ref import oracle_rows
+    cfg = getattr(O, case["config"])(**case["overrides"])
+    want = [(int(r[0]), int(r[1]), float(r[2]), float(r[3])) for r in case["rows"]]
+    got = oracle_rows(orc, cfg, case["seed"], case["trials"])
+    assert len(got) == len(want) >= 10
+    for g, w in zip(got, want):
+        assert (g[0], g[1], g[3]) == (w[0], w[1], w[3]) and abs(g[2] - w[2]) <= 0.00051, (g, w)
