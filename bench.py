@@ -9,7 +9,8 @@ memory=65,536 entries (32 GiB of tables: far larger than L2, so nothing is cache
   value  : device-resident throughput (inputs already in HBM), CUDA events on the launching stream
   e2e    : the same through grlcu_run_host with HOST buffers (H2D start states + D2H results inside)
   roofline: algorithmic table bytes (640 + 16*V per agent-step, V measured on device) / run-kernel time
-  cpu_baseline: the CPU oracle (port of the reference; real grld needs Eigen, absent) on all host cores
+  cpu_baseline: the reference's own deployer built from its sources (oracle/_ref/grld_ref; Eigen, absent here, is a stand-in),
+            one process per host core; the CPU oracle (port of the reference) beside it, and instead of it where the binary is absent
 
 --impl reference times that CPU implementation alone, with the same JSON line layout.
 """
