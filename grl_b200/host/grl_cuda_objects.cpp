@@ -229,7 +229,11 @@ void CudaLinearRepresentation::reconfigure(const Configuration &config)
   // representation.h:201-263: raw little-endian doubles, `file` + path with '/' -> '_' + ".dat".  Agent 0 uses
   // exactly that name (so reference grld can load it); agent k > 0 appends "-agent<k>" before ".dat".
   std::string base = config.has("file") ? config["file"].str() : std::string();
+  // The reference's object paths start at the root, "/experiment/agent/policy/representation", so its file names carry a
+  // leading '_' ("<file>_experiment_agent_policy_representation.dat"; seen in the files the reference's own deployer
+  // writes, oracle/_ref/grld_ref with save_every: run).  This host's paths have no leading slash.
   std::string cfg_path = path();
+  if (cfg_path.empty() || cfg_path[0] != '/') cfg_path = "/" + cfg_path;
   std::replace(cfg_path.begin(), cfg_path.end(), '/', '_');
   const int count = std::min(path_->agents, config.has("agents") ? (int)config["agents"] : 1);
   std::vector<double> p(memory_);

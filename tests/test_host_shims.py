@@ -289,7 +289,7 @@ def test_grld_matches_ctypes_harness(grld, tmp_path):
         assert int(row[2]) == r["steps"][a] and int(row[3]) == r["episodes"][a]
         assert float(row[4]) == r["last_return"][a] and float(row[5]) == r["last_test_return"][a]
     # checkpoint in the reference's format (representation.h:201-263): raw doubles, path-derived name
-    ck = np.fromfile(str(tmp_path / "out") + "-run0-experiment_agent_policy_representation.dat", dtype=np.float64)
+    ck = np.fromfile(str(tmp_path / "out") + "-run0-_experiment_agent_policy_representation.dat", dtype=np.float64)
     assert np.array_equal(ck, b.get_table(0))
     b.close()
 
@@ -327,7 +327,7 @@ def test_grld_actor_critic_matches_ctypes_harness(grld, tmp_path, yaml, mk, amax
         for a, row in enumerate(rows):
             assert int(row[2]) == r["steps"][a] and int(row[3]) == r["episodes"][a]
             assert float(row[4]) == r["last_return"][a] and float(row[5]) == r["last_test_return"][a]
-        stem = str(tmp_path / "ac") + "-run0-experiment_agent_"
+        stem = str(tmp_path / "ac") + "-run0-_experiment_agent_"
         actor = np.fromfile(stem + "policy_representation.dat", dtype=np.float64)
         critic = np.fromfile(stem + "predictor_critic_representation.dat", dtype=np.float64)
         assert np.array_equal(actor, b.get_actor_table(0)) and np.array_equal(critic, b.get_table(0))
@@ -506,7 +506,7 @@ def test_load_file_round_trip_from_reference_format(grld, tmp_path, orc):
         t = np.ctypeslib.as_array(L.orc_table(a), shape=(mem,)).copy()
         L.orc_destroy(a)
         tables.append(t)
-        t.tofile("%s-experiment_agent_policy_representation%s.dat" % (stem, "" if i == 0 else "-agent%d" % i))
+        t.tofile("%s-_experiment_agent_policy_representation%s.dat" % (stem, "" if i == 0 else "-agent%d" % i))
     base = open(os.path.join(ROOT, "cfg/pendulum/sarsa_tc_cuda.yaml")).read()
     y = base.replace("agents: 65536", "agents: %d" % n).replace("steps: 10000", "steps: 300") \
             .replace("memory: 65536", "memory: %d" % mem) \
@@ -528,7 +528,7 @@ def test_load_file_round_trip_from_reference_format(grld, tmp_path, orc):
         for a, row in enumerate(rows):
             assert int(row[2]) == r["steps"][a] and float(row[4]) == r["last_return"][a]
         # save_every: trial wrote a checkpoint after every report, named by the finished episodes (online_learning.cpp:281-291)
-        ck = np.fromfile(str(tmp_path / "out") + "-run0-trial3-experiment_agent_policy_representation-agent5.dat", dtype=np.float64)
+        ck = np.fromfile(str(tmp_path / "out") + "-run0-trial3-_experiment_agent_policy_representation-agent5.dat", dtype=np.float64)
         assert np.array_equal(ck, b.get_table(5))
         # a reserved bit pattern must not get in through a checkpoint
         bad = tables[0].copy()

@@ -89,3 +89,33 @@ def test_learning_curve_equals_the_reference_deployer(orc, tmp_path, name, fn, k
         assert g[0] == w[0] and g[1] == w[1], (g, w)                 # trial, learning steps so far
         assert abs(g[2] - w[2]) <= 0.00051, (g, w)                   # episode return, printed with 3 decimals
         assert g[3] == w[3], (g, w)                                  # episode time = steps (discrete_time: 1)
+
+
+def test_checkpoint_written_by_the_reference_deployer(orc, tmp_path):
+    """`save_every: run` of the reference's own deployer (representation.h:201-263, online_learning.cpp:281-302): the file
+    name the host shims must use to be interchangeable with the reference -- note the '_' that the root of the object path
+    contributes -- its size, and its content: the oracle's Q table after the same seeded run, bit for bit."""
+    import numpy as np
+    c = O.pendulum_config(memory=4096, test_interval=-1, randomization=1.0)
+    trials, seed = 25, 3
+    (tmp_path / "cfg.yaml").write_text(O.grld_yaml(c, trials, "ck").replace("save_every: never", "save_every: run"))
+    r = subprocess.run([GRLD, "-s", str(seed), "cfg.yaml"], cwd=tmp_path, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-1500:]
+    name = tmp_path / "ck-run0-_experiment_agent_policy_representation.dat"
+    assert name.exists(), sorted(p.name for p in tmp_path.iterdir())
+    table = np.fromfile(str(name), dtype=np.float64)
+    assert table.size == c.memory
+    c.rng = O.RNG_GLIBC
+    orc.orc_glibc_seed(seed)
+    a = orc.orc_create(C.byref(c), 0)
+    rec = O.Record()
+    done = 0
+    while done < trials:
+        orc.orc_step(a, C.byref(rec))
+        done += rec.episode_done
+    want = np.ctypeslib.as_array(orc.orc_table(a), shape=(c.memory,)).copy()
+    orc.orc_destroy(a)
+    assert np.array_equal(table.view(np.uint64), want.view(np.uint64))
+    # the name the C++ shim composes (grl_b200/host/grl_cuda_objects.cpp: file + path with '/' -> '_' + ".dat", path rooted at '/')
+    src = open(os.path.join(os.path.dirname(HERE), "grl_b200", "host", "grl_cuda_objects.cpp")).read()
+    assert 'cfg_path = "/" + cfg_path' in src
