@@ -282,8 +282,14 @@ def grld_yaml(c, trials, output):
     n = c.obs_dims + 1
     sampler = ("{type: sampler/softmax, tau: %r}" % c.softmax_tau if c.sampler == SAMPLER_SOFTMAX
                else "{type: sampler/epsilon_greedy, epsilon: %r}" % c.epsilon)
-    predictor = {ALGO_SARSA: "predictor/critic/sarsa", ALGO_Q: "predictor/critic/q"}[c.algo]
+    predictor = {ALGO_SARSA: "predictor/critic/sarsa", ALGO_Q: "predictor/critic/q",
+                 ALGO_EXPECTED_SARSA: "predictor/critic/expected_sarsa"}[c.algo]
     extra = "      discretizer: experiment/agent/policy/discretizer\n" if c.algo == ALGO_Q else ""
+    if c.algo == ALGO_EXPECTED_SARSA:
+        # the target policy is the agent's own (epsilon-greedy) policy object: no further sampler is constructed, so the
+        # random streams stay where the oracle's glibc mode puts them
+        assert c.target_epsilon == c.epsilon and c.sampler == SAMPLER_EPSILON_GREEDY
+        extra = "      policy: experiment/agent/policy\n"
     return head + """  agent:
     type: agent/td
     policy:

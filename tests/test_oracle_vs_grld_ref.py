@@ -73,6 +73,8 @@ CASES = [
     ("pendulum_ac", "pendulum_ac_config", dict(memory=65536), 7, 220),
     ("cart_pole_ac", "cart_pole_ac_config", dict(memory=262144), 8, 110),
     ("pendulum_q_learning", "pendulum_config", dict(memory=65536, algo=O.ALGO_Q, randomization=1.0), 9, 330),
+    ("pendulum_expected_sarsa", "pendulum_config", dict(memory=65536, algo=O.ALGO_EXPECTED_SARSA, target_epsilon=0.05,
+                                                        randomization=1.0), 13, 220),
     ("pendulum_softmax", "pendulum_config", dict(memory=65536, sampler=O.SAMPLER_SOFTMAX, softmax_tau=0.5), 10, 220),
     ("pendulum_accumulating_trace", "pendulum_config", dict(memory=65536, trace=O.TRACE_ACCUMULATING), 11, 220),
     ("pendulum_safe_2", "pendulum_config", dict(memory=65536, safe=2), 12, 220),
