@@ -33,6 +33,8 @@ void CudaBatchedEnvironment::request(ConfigurationRequest *config)
   config->push_back(CRP("action_dims", "int.action_dims", "Number of action dimensions", CRP::Provided));
   config->push_back(CRP("action_min", "vector.action_min", "Lower limit on actions", CRP::Provided));
   config->push_back(CRP("action_max", "vector.action_max", "Upper limit on actions", CRP::Provided));
+  config->push_back(CRP("reward_min", "vector.reward_min", "Lower limit on immediate reward", CRP::Provided));
+  config->push_back(CRP("reward_max", "vector.reward_max", "Upper limit on immediate reward", CRP::Provided));
 }
 
 void CudaBatchedEnvironment::configure(Configuration &config)
@@ -55,6 +57,8 @@ void CudaBatchedEnvironment::configure(Configuration &config)
   config.set("action_dims", 1);
   config.set("action_min", task_->action_min);
   config.set("action_max", task_->action_max);
+  config.set("reward_min", task_->reward_min);          // modeled.cpp:112-113
+  config.set("reward_max", task_->reward_max);
 }
 
 void CudaBatchedEnvironment::reconfigure(const Configuration &) { }
@@ -161,7 +165,7 @@ void CudaLinearRepresentation::request(const std::string &, ConfigurationRequest
   config->push_back(CRP("output_max", "Upper output limit", Vector(), CRP::System));
   config->push_back(CRP("limit", "Limit parameters to same range as outputs", limit_, CRP::Configuration, 0, 1));
   config->push_back(CRP("interval", "Target representation update interval", 0, CRP::Configuration));
-  config->push_back(CRP("tau", "Target representation update rate", Vector{1.}, CRP::Configuration));
+  config->push_back(CRP("tau", "Target representation update strength", 1., CRP::Configuration));     // a double in the reference (representation.h:181)
   config->push_back(CRP("file_suffix", "Checkpoint file suffix (default: configuration path)", "", CRP::Configuration));
 }
 

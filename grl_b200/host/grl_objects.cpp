@@ -62,6 +62,7 @@ static void provide_limits(Configuration &config, Task &t, int obs_dims, double 
   config.set("action_max", t.action_max);
   config.set("reward_min", reward_min);
   config.set("reward_max", reward_max);
+  t.reward_min = reward_min; t.reward_max = reward_max;
 }
 
 static void request_limits(ConfigurationRequest *config)
@@ -100,7 +101,7 @@ void CartPoleSwingupTask::request(ConfigurationRequest *config)
 {
   request_limits(config);
   config->push_back(CRP("timeout", "Episode timeout", 9.99, CRP::Configuration, 0., DBL_MAX));
-  config->push_back(CRP("randomization", "Start state randomization", 0., CRP::Online, 0., 1.));
+  config->push_back(CRP("randomization", "Start state randomization", 0, CRP::Online, 0, 1));     // an int in the reference (cart_pole.cpp:114)
   config->push_back(CRP("shaping", "Whether to use reward shaping", 0, CRP::Configuration, 0, 1));
   config->push_back(CRP("gamma", "Discount rate for reward shaping", 1., CRP::Configuration, 0., 1.));
   config->push_back(CRP("end_stop_penalty", "Terminate episode with penalty when end stop is reached", 1, CRP::Configuration, 0, 1));
@@ -124,7 +125,7 @@ void CartPoleSwingupTask::configure(Configuration &config)
 void CartDoublePoleBalancingTask::request(ConfigurationRequest *config)
 {
   request_limits(config);
-  config->push_back(CRP("timeout", "Episode timeout", 4.99, CRP::Configuration, 0., DBL_MAX));
+  config->push_back(CRP("timeout", "Episode timeout", 9.99, CRP::Configuration, 0., DBL_MAX));     // the reference's default (cart_double_pole.cpp:236); its cfg files set 4.99
 }
 void CartDoublePoleBalancingTask::configure(Configuration &config)
 {

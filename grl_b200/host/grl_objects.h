@@ -78,6 +78,7 @@ struct Task : Configurable
   int dynamics_id = -1; double timeout = 0, randomization = 0;
   int end_stop_penalty = 1;      // task/cart_pole/swingup only (cart_pole.h:75)
   Vector observation_min, observation_max, action_min, action_max;
+  double reward_min = 0, reward_max = 0;      // re-exported by the environment (modeled.cpp:112-113)
 };
 struct PendulumSwingupTask : Task
 {

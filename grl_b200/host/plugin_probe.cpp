@@ -18,6 +18,33 @@ int main(int argc, char **argv)
   const int loaded = grl::loadPlugins(dir);
   printf("plugins %d types_before %zu types_after %zu\n", loaded, before, grl::ConfigurableFactory::types().size());
   int missing = 0;
+  // --requests <type>...: the parameters each type requests (Configurable::request), one line per parameter in the format of
+  // the reference-side dump (oracle/ref_agent.cpp, refag_requests): "<type>: name|type|default|mutability|optional"
+  if (argc > 1 && std::string(argv[1]) == "--requests")
+  {
+    for (int i = 2; i < argc; ++i)
+    {
+      try
+      {
+        grl::Configurable *obj = grl::ConfigurableFactory::create(argv[i]);
+        grl::ConfigurationRequest req;
+        obj->request("", &req);
+        for (const grl::CRP &p : req)
+        {
+          const char m = p.mutability == grl::CRP::Provided ? 'P' : p.mutability == grl::CRP::System ? 'S'
+                       : p.mutability == grl::CRP::Online ? 'O' : 'C';
+          printf("%s: %s|%s|%s|%c|%d\n", argv[i], p.name.c_str(), p.type.c_str(), p.is_object ? "0" : p.value.c_str(), m, p.optional ? 1 : 0);
+        }
+        delete obj;
+      }
+      catch (grl::Exception &e)
+      {
+        printf("%s MISSING (%s)\n", argv[i], e.what());
+        ++missing;
+      }
+    }
+    return missing ? 1 : 0;
+  }
   for (int i = 1; i < argc; ++i)
   {
     try

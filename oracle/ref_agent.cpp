@@ -458,6 +458,29 @@ int refag_run(void *h, long n_steps, double *out, double *state_out)
   catch (std::exception &e) { fprintf(stderr, "refag_run: %s\n", e.what()); return 1; }
 }
 
+/* The parameters a registered type of the reference requests (Configurable::request, configurable.h:738-742), one line per
+ * parameter: name|type|default value|mutability (P rovided, S ystem, C onfiguration, O nline)|optional.  For the host shims'
+ * API-surface test (tests/test_host_request_parity.py).  Returns the number of characters written, -1 for an unknown type. */
+int refag_requests(const char *type, char *out, int cap)
+{
+  try
+  {
+    Configurable *obj = ConfigurableFactory::create(type);
+    if (!obj) return -1;
+    ConfigurationRequest req;
+    obj->request("", &req);
+    std::ostringstream oss;
+    for (size_t i = 0; i < req.size(); ++i)
+      oss << req[i].name << "|" << req[i].type << "|" << req[i].value << "|" << "PSCO"[(int)req[i].mutability] << "|" << (req[i].optional ? 1 : 0) << "\n";
+    delete obj;
+    const std::string s = oss.str();
+    if ((int)s.size() + 1 > cap) return -2;
+    memcpy(out, s.c_str(), s.size() + 1);
+    return (int)s.size();
+  }
+  catch (std::exception &e) { fprintf(stderr, "refag_requests: %s\n", e.what()); return -3; }
+}
+
 /* DynamicalModel::step (modeled.cpp:254-276: RK4 over the dynamics' eom) of the reference's own modeled.cpp around its own
  * dynamics classes: dyn 0 pendulum (3 states), 1 cart-pole (5), 2 cart-double-pole (7).  Returns tau, or -1. */
 double refag_model_step(int dyn, double control_step, int integration_steps, const double *state, double actuation, double *next)
